@@ -1,0 +1,418 @@
+// See unet_ops.cuh.  Reference sites: mpd/models/layers/layers.py:225-297,327-361 and
+// mpd/models/layers/layers_attention_mini.py:38-65,83-149 (forward math); backward formulas are the
+// analytic input-gradients that torch.autograd.grad evaluates at UnetInference.py:23-27.
+#include "unet_ops.cuh"
+
+namespace ramp {
+
+static __device__ __forceinline__ void store_split(bf16* hi, bf16* lo, size_t idx, float v) {
+  bf16 h, l;
+  split_bf16(v, h, l);
+  hi[idx] = h;
+  lo[idx] = l;
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void prep_input_kernel(const float* __restrict__ x, int n_samples, int n_pad, int L, int D, bf16* hi,
+                                  bf16* lo) {
+  const size_t total = (size_t)n_pad * L * 16;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i & 15);
+    const size_t row = i >> 4;
+    const size_t n = row / L;
+    float v = (c < D && n < (size_t)n_samples) ? x[row * D + c] : 0.f;
+    store_split(hi, lo, i, v);
+  }
+}
+int prep_input(const float* x, int n_samples, int n_pad, int L, int D, bf16* hi, bf16* lo, cudaStream_t s) {
+  const size_t total = (size_t)n_pad * L * 16;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  prep_input_kernel<<<blocks, 256, 0, s>>>(x, n_samples, n_pad, L, D, hi, lo);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// GroupNorm: one warp per (sample, group); 8 groups -> 8 warps per CTA, one CTA per sample.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gn_forward_kernel(GnArgs a) {
+  const int n = blockIdx.x, g = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cg = a.C / 8, m = a.L * cg;
+  const float* xs = a.x + (size_t)n * a.L * a.ldX + g * cg;
+  float s = 0.f;
+  for (int i = lane; i < m; i += 32) s += xs[(size_t)(i / cg) * a.ldX + (i % cg)];
+  const float mean = warp_sum(s) / m;
+  float v = 0.f;
+  for (int i = lane; i < m; i += 32) {
+    float d = xs[(size_t)(i / cg) * a.ldX + (i % cg)] - mean;
+    v += d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(v) / m + a.eps);
+  for (int i = lane; i < m; i += 32) {
+    const int l = i / cg, c = g * cg + (i % cg);
+    const size_t row = (size_t)n * a.L + l;
+    float y = (a.x[row * a.ldX + c] - mean) * rstd * a.gamma[c] + a.beta[c];
+    if (a.mish) y = mish_f(y);
+    if (a.cond) y += a.cond[c];
+    if (a.add) y += a.add[row * a.ldAdd + c];
+    if (a.out_f32) a.out_f32[row * a.ldO + c] = y;
+    if (a.out_hi) store_split(a.out_hi, a.out_lo, row * a.ldS + c, y);
+  }
+}
+int gn_forward(const GnArgs& a, cudaStream_t s) {
+  RAMP_CHECK(a.C % 8 == 0, "gn: C must be a multiple of 8");
+  gn_forward_kernel<<<a.n_samples, 256, 0, s>>>(a);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+__global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
+  const int n = blockIdx.x, g = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cg = a.C / 8, m = a.L * cg;
+  const float* xs = a.x + (size_t)n * a.L * a.ldX + g * cg;
+  float s = 0.f;
+  for (int i = lane; i < m; i += 32) s += xs[(size_t)(i / cg) * a.ldX + (i % cg)];
+  const float mean = warp_sum(s) / m;
+  float v = 0.f;
+  for (int i = lane; i < m; i += 32) {
+    float d = xs[(size_t)(i / cg) * a.ldX + (i % cg)] - mean;
+    v += d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(v) / m + a.eps);
+  float s1 = 0.f, s2 = 0.f;
+  for (int i = lane; i < m; i += 32) {
+    const int l = i / cg, c = g * cg + (i % cg);
+    const size_t row = (size_t)n * a.L + l;
+    const float xh = (a.x[row * a.ldX + c] - mean) * rstd;
+    float dyh = a.dy[row * a.ldDy + c] * a.gamma[c];
+    if (a.mish) dyh *= mish_grad_f(xh * a.gamma[c] + a.beta[c]);
+    s1 += dyh;
+    s2 += dyh * xh;
+  }
+  s1 = warp_sum(s1) / m;
+  s2 = warp_sum(s2) / m;
+  for (int i = lane; i < m; i += 32) {
+    const int l = i / cg, c = g * cg + (i % cg);
+    const size_t row = (size_t)n * a.L + l;
+    const float xh = (a.x[row * a.ldX + c] - mean) * rstd;
+    float dyh = a.dy[row * a.ldDy + c] * a.gamma[c];
+    if (a.mish) dyh *= mish_grad_f(xh * a.gamma[c] + a.beta[c]);
+    float dx = rstd * (dyh - s1 - xh * s2);
+    if (a.add) dx += a.add[row * a.ldAdd + c];
+    if (a.out_f32) a.out_f32[row * a.ldO + c] = dx;
+    if (a.out_hi) store_split(a.out_hi, a.out_lo, row * a.ldS + c, dx);
+  }
+}
+int gn_backward(const GnBwdArgs& a, cudaStream_t s) {
+  RAMP_CHECK(a.C % 8 == 0, "gn: C must be a multiple of 8");
+  gn_backward_kernel<<<a.n_samples, 256, 0, s>>>(a);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm over 256 channels: one warp per token, 8 channels per lane (two float4).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ln_forward_kernel(const float* __restrict__ x, int rows,
+                                                         const float* __restrict__ gamma,
+                                                         const float* __restrict__ beta, bf16* hi, bf16* lo) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * 256);
+  float4 a = xr[lane], b = xr[32 + lane];
+  float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += v[i];
+  const float mean = warp_sum(s) * (1.f / 256.f);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { v[i] -= mean; q += v[i] * v[i]; }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / 256.f) + 1e-5f);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int c0 = h * 128 + lane * 4;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = c0 + i;
+      store_split(hi, lo, (size_t)row * 256 + c, v[h * 4 + i] * rstd * gamma[c] + beta[c]);
+    }
+  }
+}
+int ln_forward(const float* x, int rows, int C, const float* gamma, const float* beta, bf16* out_hi, bf16* out_lo,
+               cudaStream_t s) {
+  RAMP_CHECK(C == 256, "ln: C must be 256");
+  ln_forward_kernel<<<(rows + 7) / 8, 256, 0, s>>>(x, rows, gamma, beta, out_hi, out_lo);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+__global__ void __launch_bounds__(256) ln_backward_kernel(const float* __restrict__ x, int rows,
+                                                          const float* __restrict__ gamma,
+                                                          const float* __restrict__ dy, const float* __restrict__ add,
+                                                          float* out, bf16* hi, bf16* lo) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * 256);
+  const float4* dr = reinterpret_cast<const float4*>(dy + (size_t)row * 256);
+  float4 a = xr[lane], b = xr[32 + lane], da = dr[lane], db = dr[32 + lane];
+  float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  float d[8] = {da.x, da.y, da.z, da.w, db.x, db.y, db.z, db.w};
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += v[i];
+  const float mean = warp_sum(s) * (1.f / 256.f);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { v[i] -= mean; q += v[i] * v[i]; }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / 256.f) + 1e-5f);
+  float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+  for (int h = 0; h < 2; ++h)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int k = h * 4 + i;
+      v[k] *= rstd;                               // xhat
+      d[k] *= gamma[h * 128 + lane * 4 + i];      // dyhat
+      s1 += d[k];
+      s2 += d[k] * v[k];
+    }
+  s1 = warp_sum(s1) * (1.f / 256.f);
+  s2 = warp_sum(s2) * (1.f / 256.f);
+#pragma unroll
+  for (int h = 0; h < 2; ++h)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int k = h * 4 + i;
+      const size_t idx = (size_t)row * 256 + h * 128 + lane * 4 + i;
+      float dx = rstd * (d[k] - s1 - v[k] * s2);
+      if (add) dx += add[idx];
+      if (out) out[idx] = dx;
+      if (hi) store_split(hi, lo, idx, dx);
+    }
+}
+int ln_backward(const float* x, int rows, int C, const float* gamma, const float* dy, const float* add, float* out_f32,
+                bf16* out_hi, bf16* out_lo, cudaStream_t s) {
+  RAMP_CHECK(C == 256, "ln: C must be 256");
+  ln_backward_kernel<<<(rows + 7) / 8, 256, 0, s>>>(x, rows, gamma, dy, add, out_f32, out_hi, out_lo);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Self-attention core, 4 heads x 64, L <= 64 tokens: one CTA per (sample, head), operands in smem.
+// ------------------------------------------------------------------------------------------------
+static constexpr int AH = 64;       // head dim
+static constexpr int AP = AH + 1;   // padded smem row
+
+__device__ __forceinline__ void attn_load_head(const float* __restrict__ src, int ld, int L, float* dst) {
+  for (int i = threadIdx.x; i < L * AH; i += blockDim.x) dst[(i / AH) * AP + (i % AH)] = src[(size_t)(i / AH) * ld + (i % AH)];
+}
+// S = softmax(scale * Q K^T) into P [L][L+1]
+__device__ __forceinline__ void attn_probs(const float* Q, const float* K, float* P, int L) {
+  const int LP = L + 1;
+  for (int idx = threadIdx.x; idx < L * L; idx += blockDim.x) {
+    const int i = idx / L, j = idx - i * L;
+    float acc = 0.f;
+#pragma unroll 16
+    for (int d = 0; d < AH; ++d) acc = fmaf(Q[i * AP + d], K[j * AP + d], acc);
+    P[i * LP + j] = acc * 0.125f;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int i = warp; i < L; i += nw) {
+    float m = -INFINITY;
+    for (int j = lane; j < L; j += 32) m = fmaxf(m, P[i * LP + j]);
+    m = warp_max(m);
+    float s = 0.f;
+    for (int j = lane; j < L; j += 32) { float e = expf(P[i * LP + j] - m); P[i * LP + j] = e; s += e; }
+    s = 1.f / warp_sum(s);
+    for (int j = lane; j < L; j += 32) P[i * LP + j] *= s;
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(128) attn_forward_kernel(const float* __restrict__ qkv, int L, bf16* hi, bf16* lo) {
+  extern __shared__ float sm[];
+  const int n = blockIdx.x >> 2, h = blockIdx.x & 3;
+  float* Q = sm; float* K = Q + L * AP; float* V = K + L * AP; float* P = V + L * AP;
+  const float* base = qkv + (size_t)n * L * 768 + h * AH;
+  attn_load_head(base, 768, L, Q);
+  attn_load_head(base + 256, 768, L, K);
+  attn_load_head(base + 512, 768, L, V);
+  __syncthreads();
+  attn_probs(Q, K, P, L);
+  const int LP = L + 1;
+  for (int idx = threadIdx.x; idx < L * AH; idx += blockDim.x) {
+    const int i = idx / AH, d = idx - i * AH;
+    float acc = 0.f;
+    for (int j = 0; j < L; ++j) acc = fmaf(P[i * LP + j], V[j * AP + d], acc);
+    store_split(hi, lo, ((size_t)n * L + i) * 256 + h * AH + d, acc);
+  }
+}
+static size_t attn_smem(int L, bool bwd) { return sizeof(float) * ((bwd ? 4 : 3) * L * AP + (bwd ? 2 : 1) * L * (L + 1)); }
+int attn_forward(const float* qkv, int n_samples, int L, bf16* out_hi, bf16* out_lo, cudaStream_t s) {
+  RAMP_CHECK(L <= 64, "attention: L must be <= 64");
+  static bool attr = false;
+  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem(64, false))); attr = true; }
+  attn_forward_kernel<<<n_samples * 4, 128, attn_smem(L, false), s>>>(qkv, L, out_hi, out_lo);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+__global__ void __launch_bounds__(128) attn_backward_kernel(const float* __restrict__ qkv,
+                                                            const float* __restrict__ d_out, int L, bf16* hi, bf16* lo) {
+  extern __shared__ float sm[];
+  const int n = blockIdx.x >> 2, h = blockIdx.x & 3;
+  const int LP = L + 1;
+  float* Q = sm; float* K = Q + L * AP; float* V = K + L * AP; float* dO = V + L * AP;
+  float* P = dO + L * AP; float* dS = P + L * LP;
+  const float* base = qkv + (size_t)n * L * 768 + h * AH;
+  attn_load_head(base, 768, L, Q);
+  attn_load_head(base + 256, 768, L, K);
+  attn_load_head(base + 512, 768, L, V);
+  attn_load_head(d_out + (size_t)n * L * 256 + h * AH, 256, L, dO);
+  __syncthreads();
+  attn_probs(Q, K, P, L);
+  // dP = dO V^T
+  for (int idx = threadIdx.x; idx < L * L; idx += blockDim.x) {
+    const int i = idx / L, j = idx - i * L;
+    float acc = 0.f;
+#pragma unroll 16
+    for (int d = 0; d < AH; ++d) acc = fmaf(dO[i * AP + d], V[j * AP + d], acc);
+    dS[i * LP + j] = acc;
+  }
+  __syncthreads();
+  // dS = P * (dP - rowsum(P * dP)) * scale
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int i = warp; i < L; i += nw) {
+    float s = 0.f;
+    for (int j = lane; j < L; j += 32) s += P[i * LP + j] * dS[i * LP + j];
+    s = warp_sum(s);
+    for (int j = lane; j < L; j += 32) dS[i * LP + j] = P[i * LP + j] * (dS[i * LP + j] - s) * 0.125f;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < L * AH; idx += blockDim.x) {
+    const int i = idx / AH, d = idx - i * AH;   // i doubles as the key index j for dK / dV
+    float dq = 0.f, dk = 0.f, dv = 0.f;
+    for (int j = 0; j < L; ++j) {
+      dq = fmaf(dS[i * LP + j], K[j * AP + d], dq);
+      dk = fmaf(dS[j * LP + i], Q[j * AP + d], dk);
+      dv = fmaf(P[j * LP + i], dO[j * AP + d], dv);
+    }
+    const size_t o = ((size_t)n * L + i) * 768 + h * AH + d;
+    store_split(hi, lo, o, dq);
+    store_split(hi, lo, o + 256, dk);
+    store_split(hi, lo, o + 512, dv);
+  }
+}
+int attn_backward(const float* qkv, const float* d_out, int n_samples, int L, bf16* dq_hi, bf16* dq_lo, cudaStream_t s) {
+  RAMP_CHECK(L <= 64, "attention: L must be <= 64");
+  static bool attr = false;
+  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem(64, true))); attr = true; }
+  attn_backward_kernel<<<n_samples * 4, 128, attn_smem(L, true), s>>>(qkv, d_out, L, dq_hi, dq_lo);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// GEGLU (layers_attention_mini.py:38-45)
+// ------------------------------------------------------------------------------------------------
+__global__ void geglu_forward_kernel(const float* __restrict__ u, size_t rows, int inner, bf16* hi, bf16* lo) {
+  const size_t total = rows * inner;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t r = i / inner; const int c = (int)(i - r * inner);
+    const float a = u[r * 2 * inner + c], g = u[r * 2 * inner + inner + c];
+    store_split(hi, lo, i, a * gelu_f(g));
+  }
+}
+__global__ void geglu_backward_kernel(const float* __restrict__ u, const float* __restrict__ dg, size_t rows, int inner,
+                                      bf16* hi, bf16* lo) {
+  const size_t total = rows * inner;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t r = i / inner; const int c = (int)(i - r * inner);
+    const float a = u[r * 2 * inner + c], g = u[r * 2 * inner + inner + c], d = dg[i];
+    store_split(hi, lo, r * 2 * inner + c, d * gelu_f(g));
+    store_split(hi, lo, r * 2 * inner + inner + c, d * a * gelu_grad_f(g));
+  }
+}
+static int ew_blocks(size_t total) {
+  size_t b = (total + 255) / 256;
+  return (int)(b > 148 * 16 ? 148 * 16 : b);
+}
+int geglu_forward(const float* u, int rows, int inner, bf16* out_hi, bf16* out_lo, cudaStream_t s) {
+  geglu_forward_kernel<<<ew_blocks((size_t)rows * inner), 256, 0, s>>>(u, rows, inner, out_hi, out_lo);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+int geglu_backward(const float* u, const float* dg, int rows, int inner, bf16* du_hi, bf16* du_lo, cudaStream_t s) {
+  geglu_backward_kernel<<<ew_blocks((size_t)rows * inner), 256, 0, s>>>(u, dg, rows, inner, du_hi, du_lo);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Time embedding (layers.py:233-259) + cond_mlp of every residual block (layers.py:338-346)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) time_cond_kernel(const float* __restrict__ tw, float t, const CondBlock* blocks) {
+  __shared__ float pe[32], hid[128], emb[32];
+  const int tid = threadIdx.x;
+  if (tid < 16) {
+    const float f = expf((float)tid * -(logf(10000.f) / 15.f));
+    pe[tid] = sinf(t * f);
+    pe[tid + 16] = cosf(t * f);
+  }
+  __syncthreads();
+  {
+    const float* w = tw + tid * 32;
+    float acc = tw[128 * 32 + tid];
+    for (int k = 0; k < 32; ++k) acc = fmaf(w[k], pe[k], acc);
+    hid[tid] = mish_f(acc);
+  }
+  __syncthreads();
+  if (tid < 32) {
+    const float* w = tw + 128 * 32 + 128 + tid * 128;
+    float acc = tw[128 * 32 + 128 + 32 * 128 + tid];
+    for (int k = 0; k < 128; ++k) acc = fmaf(w[k], hid[k], acc);
+    emb[tid] = acc / (1.f + expf(-acc));   // SiLU feeds every cond_mlp
+  }
+  __syncthreads();
+  const CondBlock b = blocks[blockIdx.x];
+  for (int c = tid; c < b.cout; c += blockDim.x) {
+    float acc = b.b[c];
+    for (int k = 0; k < 32; ++k) acc = fmaf(b.w[c * 32 + k], emb[k], acc);
+    b.out[c] = acc;
+  }
+}
+int time_cond(const float* tw, float t, const CondBlock* blocks_dev, int n_blocks, cudaStream_t s) {
+  time_cond_kernel<<<n_blocks, 128, 0, s>>>(tw, t, blocks_dev);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// attn2 (single context token) per-scene constants
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) scene_const_kernel(const SceneBlock* blocks, const float* __restrict__ latents,
+                                                          int n_scenes, int ctx_dim) {
+  __shared__ float v[256];
+  const SceneBlock b = blocks[blockIdx.x];
+  const int sidx = blockIdx.y, tid = threadIdx.x;
+  const float* lat = latents + (size_t)sidx * ctx_dim;
+  float acc = 0.f;
+  for (int k = 0; k < ctx_dim; ++k) acc = fmaf(b.wv[(size_t)tid * ctx_dim + k], lat[k], acc);
+  v[tid] = acc;
+  __syncthreads();
+  acc = b.bo2[tid] + b.bo1[tid];
+  for (int k = 0; k < 256; ++k) acc = fmaf(b.wo[tid * 256 + k], v[k], acc);
+  b.tab[(size_t)sidx * 256 + tid] = acc;
+}
+int scene_constants(const SceneBlock* blocks_dev, int n_blocks, const float* latents, int n_scenes, int ctx_dim,
+                    cudaStream_t s) {
+  scene_const_kernel<<<dim3(n_blocks, n_scenes), 256, 0, s>>>(blocks_dev, latents, n_scenes, ctx_dim);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace ramp

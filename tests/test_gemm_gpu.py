@@ -1,0 +1,105 @@
+"""tcgen05 multi-tap GEMM vs torch (fp64) on the same bf16 hi/lo operands — through the C ABI."""
+import ctypes
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _split(x):
+    hi = x.to(torch.bfloat16)
+    lo = (x - hi.float()).to(torch.bfloat16)
+    return hi.contiguous(), lo.contiguous()
+
+
+def _gemm(a, w, taps, L_out, a_pstride=1, bias=None, bias_tab=None, row2scene=None, residual=None, precision=3,
+          o_L=None, o_stride=1, o_off=0, out_rows=None, K=None, want_split=False):
+    """a: [n, L_in, ldA] fp32 cuda; w: [n_wtaps, Nout, Kw]."""
+    from ramp_b200._lib import lib, check, ptr, stream_ptr
+    n, L_in, ldA = a.shape
+    n_wt, Nout, Kw = w.shape
+    K = K or Kw
+    ah, al = _split(a)
+    wh, wl = _split(w)
+    o_L = o_L or L_out
+    out_rows = out_rows or n * o_L
+    out = torch.zeros(out_rows, Nout, device=a.device)
+    oh = torch.zeros(out_rows, Nout, device=a.device, dtype=torch.bfloat16) if want_split else None
+    ol = torch.zeros_like(oh) if want_split else None
+    tp = (ctypes.c_int * (3 * len(taps)))(*[v for t in taps for v in t])
+    check(lib().ramp_gemm(ptr(ah), ptr(al), n, L_in, ldA, K, a_pstride, L_out, len(taps), tp, ptr(wh), ptr(wl), Nout, Kw,
+                          n_wt, ptr(bias), ptr(bias_tab), ptr(row2scene), ptr(residual), Nout, ptr(out), Nout,
+                          ptr(oh), ptr(ol), Nout, o_L, o_stride, o_off, precision, stream_ptr()), "ramp_gemm")
+    torch.cuda.synchronize()
+    ar = ah.double() + (al.double() if precision == 3 else 0)
+    wr = wh.double() + (wl.double() if precision == 3 else 0)
+    return out, (oh, ol), ar, wr
+
+
+@pytest.mark.parametrize("n,L,K,Nout", [(2, 64, 64, 32), (16, 8, 256, 256), (4, 32, 256, 768), (3, 64, 2048, 256),
+                                        (5, 16, 32, 2048), (2, 64, 16, 32), (2, 64, 32, 16), (33, 8, 768, 256)])
+@pytest.mark.parametrize("precision", [3, 1])
+def test_linear(cuda, n, L, K, Nout, precision):
+    g = torch.Generator(device="cpu").manual_seed(n * 131 + K)
+    a = torch.randn(n, L, K, generator=g).to(cuda)
+    w = (torch.randn(1, Nout, K, generator=g) / K ** 0.5).to(cuda)
+    bias = torch.randn(Nout, generator=g).to(cuda)
+    res = torch.randn(n * L, Nout, generator=g).to(cuda)
+    out, _, ar, wr = _gemm(a, w, [(0, 0, 0)], L, bias=bias, residual=res, precision=precision)
+    ref = ar.reshape(-1, K) @ wr[0].T + bias.double() + res.double()
+    err = (out.double() - ref).abs().max().item()
+    # dropped lo*lo term and fp32 accumulation
+    assert err < (2e-5 if precision == 3 else 2e-4) * max(1.0, ref.abs().max().item()), err
+
+
+def test_split_output_and_scene_bias(cuda):
+    g = torch.Generator(device="cpu").manual_seed(7)
+    n, L, K, Nout = 6, 32, 256, 256
+    a = torch.randn(n, L, K, generator=g).to(cuda)
+    w = (torch.randn(1, Nout, K, generator=g) / 16).to(cuda)
+    tab = torch.randn(3, Nout, generator=g).to(cuda)
+    r2s = torch.tensor([0, 1, 2, 2, 1, 0], dtype=torch.int32, device=cuda)
+    out, (oh, ol), ar, wr = _gemm(a, w, [(0, 0, 0)], L, bias_tab=tab, row2scene=r2s, want_split=True)
+    ref = (ar.reshape(-1, K) @ wr[0].T).reshape(n, L, Nout) + tab.double()[r2s.long()][:, None, :]
+    assert (out.double().reshape(n, L, Nout) - ref).abs().max().item() < 5e-5
+    assert (oh.float() + ol.float() - out).abs().max().item() < 1e-4
+
+
+@pytest.mark.parametrize("n,L,Cin,Cout", [(2, 64, 32, 32), (4, 32, 64, 64), (16, 8, 512, 128), (3, 16, 128, 128), (2, 64, 16, 32)])
+def test_conv5(cuda, n, L, Cin, Cout):
+    g = torch.Generator(device="cpu").manual_seed(L + Cin)
+    a = torch.randn(n, L, Cin, generator=g).to(cuda)
+    wt = (torch.randn(Cout, Cin, 5, generator=g) / (5 * Cin) ** 0.5)
+    w = wt.permute(2, 0, 1).contiguous().to(cuda)      # [tap, Cout, Cin]
+    bias = torch.randn(Cout, generator=g).to(cuda)
+    out, _, ar, wr = _gemm(a, w, [(0, k - 2, k) for k in range(5)], L, bias=bias)
+    ref = F.conv1d(ar.transpose(1, 2), wr.permute(1, 2, 0), bias.double(), padding=2).transpose(1, 2)
+    assert (out.double().reshape(n, L, Cout) - ref).abs().max().item() < 5e-5
+
+
+def test_stride2_down(cuda):
+    """Conv1d k3 s2 p1 (layers.py:262-268) through the parity view of the input."""
+    g = torch.Generator(device="cpu").manual_seed(3)
+    n, L, C = 4, 32, 64
+    a = torch.randn(n, L, C, generator=g).to(cuda)
+    wt = torch.randn(C, C, 3, generator=g) / (3 * C) ** 0.5
+    w = wt.permute(2, 0, 1).contiguous().to(cuda)
+    out, _, ar, wr = _gemm(a, w, [(1, -1, 0), (0, 0, 1), (1, 0, 2)], L // 2, a_pstride=2)
+    ref = F.conv1d(ar.transpose(1, 2), wr.permute(1, 2, 0), stride=2, padding=1).transpose(1, 2)
+    assert (out.double().reshape(n, L // 2, C) - ref).abs().max().item() < 5e-5
+
+
+def test_transposed_up(cuda):
+    """ConvTranspose1d k4 s2 p1 (layers.py:271-277) as two parity GEMMs with interleaved output rows."""
+    g = torch.Generator(device="cpu").manual_seed(4)
+    n, L, C = 4, 16, 128
+    a = torch.randn(n, L, C, generator=g).to(cuda)
+    wt = torch.randn(C, C, 4, generator=g) / (2 * C) ** 0.5          # [Cin, Cout, k]
+    w = wt.permute(2, 1, 0).contiguous().to(cuda)                     # [k, Cout, Cin]
+    ev, _, ar, wr = _gemm(a, w, [(0, 0, 1), (0, -1, 3)], L, o_L=2 * L, o_stride=2, o_off=0, out_rows=n * 2 * L)
+    od, _, _, _ = _gemm(a, w, [(0, 1, 0), (0, 0, 2)], L, o_L=2 * L, o_stride=2, o_off=1, out_rows=n * 2 * L)
+    out = (ev + od).double().reshape(n, 2 * L, C)
+    ref = F.conv_transpose1d(ar.transpose(1, 2), wr.permute(2, 1, 0), stride=2, padding=1).transpose(1, 2)
+    assert (out - ref).abs().max().item() < 5e-5
