@@ -35,6 +35,33 @@ int ramp_gemm(const void* a_hi, const void* a_lo, int n_samples, int L_in, int l
 /* fp32 -> bf16 hi/lo planes */
 int ramp_split_bf16(const float* x, size_t n, void* hi, void* lo, void* stream);
 
+/* ---- score network: TemporalUnetInference energy gradient ------------------------------------
+ * Replaces TemporalUnetInference.forward / forward_no_energy / EnergyGradFunction
+ * (mpd/models/diffusion_models/UnetInference.py:19-37,157-224): eps = d/dx 0.5*sum f(x)^2, with the
+ * backward sweep written out analytically (no autograd). */
+typedef struct ramp_unet_config {
+  int state_dim;   /* D: 4 (2-D models) or 6 (3-D) */
+  int horizon;     /* H: multiple of 8, 8..64 */
+  int ctx_dim;     /* 320 (ObstacleEncoderSet) or 256 (ObstacleEncoder) */
+  int precision;   /* 3 = split-bf16 x3 (fp32-equivalent, the parity mode); 1 = plain bf16 */
+  int max_rows;    /* most network rows per call */
+  int max_scenes;  /* most distinct conditioning latents */
+} ramp_unet_config;
+int ramp_unet_create(const ramp_unet_config* cfg, void** handle);
+int ramp_unet_destroy(void* handle);
+/* name = reference state-dict key without the leading "model." (e.g. "downs.0.0.blocks.0.block.0.weight");
+ * data = fp32, host or device, copied. */
+int ramp_unet_set_param(void* handle, const char* name, const float* data, size_t numel);
+int ramp_unet_finalize(void* handle, void* stream);      /* packs weights, allocates the workspace */
+size_t ramp_unet_workspace_bytes(void* handle);
+/* latents [n_scenes, ctx_dim]: cached scene-encoder outputs (UnetInference.py:146-156); an all-zero row is
+ * the unconditional branch (UnetInference.py:190-197). */
+int ramp_unet_set_scenes(void* handle, const float* latents, int n_scenes, void* stream);
+/* x [n_rows, H, D]; t = the (batch-uniform) diffusion timestep; row2scene [n_rows] int32;
+ * eps_out / f_out [n_rows, H, D], either may be NULL (f_out = forward_no_energy output). */
+int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, float t, const int32_t* row2scene, float* eps_out,
+                          float* f_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -2,6 +2,7 @@
 #include "../../include/ramp_b200.h"
 #include "common.cuh"
 #include "unet_ops.cuh"
+#include "unet_engine.cuh"
 
 namespace ramp {
 static thread_local std::string g_err;
@@ -49,6 +50,35 @@ int ramp_gemm(const void* a_hi, const void* a_lo, int n_samples, int L_in, int l
   d.out_f32 = out_f32; d.ldO = ldO; d.out_hi = (bf16*)out_hi; d.out_lo = (bf16*)out_lo; d.ldS = ldS;
   d.o_L = o_L; d.o_stride = o_stride; d.o_off = o_off; d.precision = precision;
   return gemm_launch(d, (cudaStream_t)stream);
+}
+
+int ramp_unet_create(const ramp_unet_config* cfg, void** handle) {
+  RAMP_CHECK(cfg && handle, "ramp_unet_create: null argument");
+  UnetConfig c{cfg->state_dim, cfg->horizon, cfg->ctx_dim, cfg->precision, cfg->max_rows, cfg->max_scenes};
+  *handle = new UnetEngine(c);
+  return 0;
+}
+int ramp_unet_destroy(void* handle) {
+  delete (UnetEngine*)handle;
+  return 0;
+}
+int ramp_unet_set_param(void* handle, const char* name, const float* data, size_t numel) {
+  RAMP_CHECK(handle && name && data, "ramp_unet_set_param: null argument");
+  return ((UnetEngine*)handle)->set_param(name, data, numel);
+}
+int ramp_unet_finalize(void* handle, void* stream) {
+  RAMP_CHECK(handle, "ramp_unet_finalize: null handle");
+  return ((UnetEngine*)handle)->finalize((cudaStream_t)stream);
+}
+size_t ramp_unet_workspace_bytes(void* handle) { return handle ? ((UnetEngine*)handle)->workspace_bytes() : 0; }
+int ramp_unet_set_scenes(void* handle, const float* latents, int n_scenes, void* stream) {
+  RAMP_CHECK(handle && latents, "ramp_unet_set_scenes: null argument");
+  return ((UnetEngine*)handle)->set_scenes(latents, n_scenes, (cudaStream_t)stream);
+}
+int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, float t, const int32_t* row2scene, float* eps_out,
+                          float* f_out, void* stream) {
+  RAMP_CHECK(handle && x, "ramp_unet_energy_grad: null argument");
+  return ((UnetEngine*)handle)->energy_grad(x, n_rows, t, row2scene, eps_out, f_out, (cudaStream_t)stream);
 }
 
 }  // extern "C"

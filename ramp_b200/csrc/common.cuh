@@ -86,7 +86,7 @@ struct GemmDesc {
   const bf16* a_hi; const bf16* a_lo;
   int n_samples; int L_in; int ldA; int K;         // K channels are read from column 0..K-1
   int a_pstride;                                    // 1 (dense) or 2 (stride-2 view)
-  int L_out;                                        // rows per sample produced by this GEMM (divides 128)
+  int L_out;                                        // rows per sample produced by this GEMM (<= 128)
   int ntaps; GemmTap taps[5];
   // B operand (weights), [n_wtaps, Nout, Kw] bf16 hi/lo, Kw = weight row length (>= K, multiple of 8)
   const bf16* w_hi; const bf16* w_lo; int Nout; int Kw; int n_wtaps;
@@ -95,6 +95,7 @@ struct GemmDesc {
   const float* bias_tab;        // [n_scenes, Nout] or null, added per row via row2scene[sample]
   const int* row2scene;
   const float* residual; int ldR;
+  const float* residual2; int ldR2;   // optional second fp32 addend (same row mapping)
   float* out_f32; int ldO;
   bf16* out_hi; bf16* out_lo; int ldS;
   int o_L, o_stride, o_off;

@@ -30,6 +30,7 @@ struct GemmParams {
   int tap_par[5], tap_joff[5], tap_wrow[5];   // tap_wrow = wtap * Nout
   const float* bias; const float* bias_tab; const int* row2scene; int Nout;
   const float* residual; int ldR;
+  const float* residual2; int ldR2;
   float* out_f32; int ldO;
   bf16* out_hi; bf16* out_lo; int ldS;
   int o_L, o_stride, o_off;
@@ -143,6 +144,14 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
       r[i] += b.x; r[i + 1] += b.y; r[i + 2] += b.z; r[i + 3] += b.w;
     }
   }
+  if (p.residual2) {
+    const float* rs = p.residual2 + out_row * p.ldR2 + col0;
+#pragma unroll
+    for (int i = 0; i < W; i += 4) {
+      float4 b = *reinterpret_cast<const float4*>(rs + i);
+      r[i] += b.x; r[i + 1] += b.y; r[i + 2] += b.z; r[i + 3] += b.w;
+    }
+  }
   if (p.out_f32) {
     float* o = p.out_f32 + out_row * p.ldO + col0;
 #pragma unroll
@@ -209,7 +218,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
           mbar_wait(empty0 + 8 * s, ph ^ 1);
           const uint32_t st = smem_base + s * stage_bytes;
           const uint32_t fb = full0 + 8 * s;
-          mbar_expect_tx(fb, (uint32_t)stage_bytes);
+          mbar_expect_tx(fb, (uint32_t)(p.nplanes * (p.nb * p.L_out * BK * 2 + b_tile_bytes)));
           const int c3 = tile_m * p.nb;
           tma_load_4d(st, &mapAhi, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3);
           uint32_t off = A_TILE_BYTES;
@@ -259,7 +268,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
     const int r = q * 32 + lane;
     const int n_local = r / p.L_out, l = r - n_local * p.L_out;
     const int sample = tile_m * p.nb + n_local;
-    const bool row_ok = sample < p.n_samples;
+    const bool row_ok = n_local < p.nb && sample < p.n_samples;
     const size_t out_row = (size_t)sample * p.o_L + (size_t)l * p.o_stride + p.o_off;
     const uint32_t taddr = tmem_acc + ((uint32_t)(q * 32) << 16);
     const int colbase = tile_n * p.BN;
@@ -366,7 +375,7 @@ static int pick_bn(int Nout, int m_tiles) {
 
 int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   if (gemm_init() != 0) return -1;
-  RAMP_CHECK(d.L_out > 0 && BM % d.L_out == 0, "gemm: L_out must divide 128");
+  RAMP_CHECK(d.L_out > 0 && d.L_out <= BM, "gemm: L_out must be in 1..128");
   RAMP_CHECK(d.ldA % 8 == 0 && d.Kw % 8 == 0, "gemm: leading dimensions must be multiples of 8 bf16");
   RAMP_CHECK(d.Nout % 16 == 0, "gemm: Nout must be a multiple of 16");
   RAMP_CHECK(d.ntaps >= 1 && d.ntaps <= 5, "gemm: 1..5 taps");
@@ -389,7 +398,7 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
     p.tap_par[t] = d.taps[t].par; p.tap_joff[t] = d.taps[t].joff; p.tap_wrow[t] = d.taps[t].wtap * d.Nout;
   }
   p.bias = d.bias; p.bias_tab = d.bias_tab; p.row2scene = d.row2scene; p.Nout = d.Nout;
-  p.residual = d.residual; p.ldR = d.ldR; p.out_f32 = d.out_f32; p.ldO = d.ldO;
+  p.residual = d.residual; p.ldR = d.ldR; p.residual2 = d.residual2; p.ldR2 = d.ldR2; p.out_f32 = d.out_f32; p.ldO = d.ldO;
   p.out_hi = d.out_hi; p.out_lo = d.out_lo; p.ldS = d.ldS;
   p.o_L = d.o_L; p.o_stride = d.o_stride; p.o_off = d.o_off;
 

@@ -1,0 +1,289 @@
+// See unet_engine.cuh.  Part 1: parameters, weight packing, workspace.
+#include "unet_engine.cuh"
+#include "unet_ops.cuh"
+
+namespace ramp {
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+UnetEngine::~UnetEngine() {
+  for (void* p : owned_) cudaFree(p);
+  if (arena_) cudaFree(arena_);
+}
+
+void* UnetEngine::dev_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, align_up(bytes, 256)) != cudaSuccess) return nullptr;
+  cudaMemset(p, 0, align_up(bytes, 256));
+  owned_.push_back(p);
+  return p;
+}
+
+int UnetEngine::set_param(const std::string& name, const float* data, size_t numel) {
+  RAMP_CHECK(!finalized_, "set_param after finalize");
+  float* d = (float*)dev_alloc(numel * sizeof(float));
+  RAMP_CHECK(d != nullptr, "cudaMalloc failed for parameter " + name);
+  RAMP_CUDA_OK(cudaMemcpy(d, data, numel * sizeof(float), cudaMemcpyDefault));
+  params_[name] = Param{d, numel};
+  return 0;
+}
+
+static std::string g_missing;
+const float* UnetEngine::P(const std::string& name, size_t numel) {
+  auto it = params_.find(name);
+  if (it == params_.end() || it->second.numel != numel) {
+    if (g_missing.empty()) g_missing = name + (it == params_.end() ? " (missing)" : " (wrong size)");
+    return nullptr;
+  }
+  return it->second.ptr;
+}
+
+// dst[t][noff + n][koff + k] = src[t*st + n*sn + k*sk]
+__global__ void pack_weight_kernel(const float* __restrict__ src, bf16* hi, bf16* lo, int T, int Nd, int Kd, int Ns,
+                                   int Ks, long st, long sn, long sk, int noff, int koff) {
+  const long total = (long)T * Ns * Ks;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % Ks);
+    const int n = (int)((i / Ks) % Ns);
+    const int t = (int)(i / ((long)Ks * Ns));
+    bf16 h, l;
+    split_bf16(src[t * st + n * sn + k * sk], h, l);
+    const size_t o = ((size_t)t * Nd + noff + n) * Kd + koff + k;
+    hi[o] = h;
+    lo[o] = l;
+  }
+}
+
+int UnetEngine::pack(PackedW& w, const std::string& name, int T, int Nd, int Kd, int Ns, int Ks, long st, long sn,
+                     long sk, int noff, int koff, bool alloc) {
+  if (alloc) {
+    const size_t n = (size_t)T * Nd * Kd;
+    w.hi = (bf16*)dev_alloc(n * 2);
+    w.lo = (bf16*)dev_alloc(n * 2);
+    RAMP_CHECK(w.hi && w.lo, "cudaMalloc failed while packing " + name);
+    w.ntaps = T; w.Nout = Nd; w.Kw = Kd; w.K = Kd;
+  }
+  const float* src = P(name, (size_t)0 + (size_t)T * Ns * Ks);
+  if (!src) return 0;   // reported by finalize()
+  const long total = (long)T * Ns * Ks;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 1184) blocks = 1184;
+  pack_weight_kernel<<<blocks, 256>>>(src, w.hi, w.lo, T, Nd, Kd, Ns, Ks, st, sn, sk, noff, koff);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+static inline int pad16(int c) { return (c + 15) / 16 * 16; }
+
+// Conv1d weight [cout, cin, kw]  (transposed: ConvTranspose1d weight [cin, cout, kw]); Linear = kw 1.
+int UnetEngine::load_conv(ConvW& c, const std::string& prefix, int cin, int cout, int kw, bool transposed) {
+  c.cin = cin; c.cout = cout; c.kw = kw;
+  const int cinp = pad16(cin), coutp = pad16(cout);
+  int rc;
+  if (!transposed) {
+    rc = pack(c.f, prefix + "weight", kw, coutp, cinp, cout, cin, 1, (long)cin * kw, kw);
+    if (rc) return rc;
+    rc = pack(c.b, prefix + "weight", kw, cinp, coutp, cin, cout, 1, kw, (long)cin * kw);
+  } else {
+    rc = pack(c.f, prefix + "weight", kw, coutp, cinp, cout, cin, 1, kw, (long)cout * kw);
+    if (rc) return rc;
+    rc = pack(c.b, prefix + "weight", kw, cinp, coutp, cin, cout, 1, (long)cout * kw, kw);
+  }
+  if (rc) return rc;
+  c.f.K = cinp; c.b.K = coutp;
+  const float* b = P(prefix + "bias", cout);
+  if (b && coutp != cout) {   // zero-padded copy
+    float* bp = (float*)dev_alloc(coutp * sizeof(float));
+    RAMP_CHECK(bp, "cudaMalloc failed");
+    RAMP_CUDA_OK(cudaMemcpy(bp, b, cout * sizeof(float), cudaMemcpyDeviceToDevice));
+    b = bp;
+  }
+  c.bias = b;
+  return 0;
+}
+
+int UnetEngine::load_res(ResW& r, const std::string& p, int cin, int cout, int cin_true) {
+  r.cin = cin; r.cout = cout;
+  int rc = load_conv(r.c1, p + "blocks.0.block.0.", cin_true, cout, 5);
+  if (rc) return rc;
+  rc = load_conv(r.c2, p + "blocks.1.block.0.", cout, cout, 5);
+  if (rc) return rc;
+  r.g1 = P(p + "blocks.0.block.2.weight", cout); r.b1 = P(p + "blocks.0.block.2.bias", cout);
+  r.g2 = P(p + "blocks.1.block.2.weight", cout); r.b2 = P(p + "blocks.1.block.2.bias", cout);
+  r.has_res = cin_true != cout;
+  if (r.has_res) { rc = load_conv(r.res, p + "residual_conv.", cin_true, cout, 1); if (rc) return rc; }
+  r.cond = (float*)dev_alloc(cout * sizeof(float));
+  RAMP_CHECK(r.cond, "cudaMalloc failed");
+  return 0;
+}
+
+int UnetEngine::load_st(STW& st, const std::string& p, int C) {
+  st.C = C;
+  st.gn_g = P(p + "norm.weight", C); st.gn_b = P(p + "norm.bias", C);
+  int rc = load_conv(st.pin, p + "proj_in.", C, 256, 1);
+  if (rc) return rc;
+  rc = load_conv(st.pout, p + "proj_out.", 256, C, 1);
+  if (rc) return rc;
+  for (int b = 0; b < 2; ++b) {
+    TBlockW& t = st.blk[b];
+    const std::string q = p + "transformer_blocks." + std::to_string(b) + ".";
+    // fused q|k|v projection [768, 256] and its transpose [256, 768]
+    const char* names[3] = {"attn1.to_q.weight", "attn1.to_k.weight", "attn1.to_v.weight"};
+    for (int j = 0; j < 3; ++j) {
+      rc = pack(t.qkv_f, q + names[j], 1, 768, 256, 256, 256, 0, 256, 1, j * 256, 0, j == 0);
+      if (rc) return rc;
+      rc = pack(t.qkv_b, q + names[j], 1, 256, 768, 256, 256, 0, 1, 256, 0, j * 256, j == 0);
+      if (rc) return rc;
+    }
+    rc = pack(t.o_f, q + "attn1.to_out.0.weight", 1, 256, 256, 256, 256, 0, 256, 1); if (rc) return rc;
+    rc = pack(t.o_b, q + "attn1.to_out.0.weight", 1, 256, 256, 256, 256, 0, 1, 256); if (rc) return rc;
+    rc = pack(t.ff1_f, q + "ff.net.0.proj.weight", 1, 2048, 256, 2048, 256, 0, 256, 1); if (rc) return rc;
+    rc = pack(t.ff1_b, q + "ff.net.0.proj.weight", 1, 256, 2048, 256, 2048, 0, 1, 256); if (rc) return rc;
+    rc = pack(t.ff2_f, q + "ff.net.2.weight", 1, 256, 1024, 256, 1024, 0, 1024, 1); if (rc) return rc;
+    rc = pack(t.ff2_b, q + "ff.net.2.weight", 1, 1024, 256, 1024, 256, 0, 1, 1024); if (rc) return rc;
+    t.ln1g = P(q + "norm1.weight", 256); t.ln1b = P(q + "norm1.bias", 256);
+    t.ln3g = P(q + "norm3.weight", 256); t.ln3b = P(q + "norm3.bias", 256);
+    t.ff1_bias = P(q + "ff.net.0.proj.bias", 2048); t.ff2_bias = P(q + "ff.net.2.bias", 256);
+    // touched so that a checkpoint lacking them is reported: unused by the math (single-key softmax == 1)
+    P(q + "attn2.to_q.weight", 256 * 256); P(q + "attn2.to_k.weight", (size_t)256 * cfg_.ctx_dim);
+    P(q + "norm2.weight", 256); P(q + "norm2.bias", 256);
+    t.bias_tab = (float*)dev_alloc((size_t)cfg_.max_scenes * 256 * sizeof(float));
+    RAMP_CHECK(t.bias_tab, "cudaMalloc failed");
+  }
+  all_st_.push_back(&st);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+float* UnetEngine::allocf(size_t n) { return (float*)alloc_bytes(n * sizeof(float)); }
+Split UnetEngine::allocs(size_t n) {
+  Split s;
+  s.hi = (bf16*)alloc_bytes(n * 2);
+  s.lo = (bf16*)alloc_bytes(n * 2);
+  return s;
+}
+void* UnetEngine::alloc_bytes(size_t n) {
+  const size_t off = arena_off_;
+  arena_off_ += align_up(n, 256);
+  if (dry_) return (void*)(uintptr_t)(256 + off);   // non-null placeholder, never dereferenced
+  return arena_ + off;
+}
+
+int UnetEngine::finalize(cudaStream_t s) {
+  RAMP_CHECK(!finalized_, "finalize called twice");
+  RAMP_CHECK(cfg_.horizon % 8 == 0 && cfg_.horizon <= 64 && cfg_.horizon >= 8, "horizon must be a multiple of 8 in [8, 64]");
+  RAMP_CHECK(cfg_.state_dim >= 1 && cfg_.state_dim <= 16, "state_dim must be in 1..16");
+  RAMP_CHECK(cfg_.precision == 1 || cfg_.precision == 3, "precision must be 1 or 3");
+  RAMP_CHECK(cfg_.max_rows >= 1 && cfg_.max_scenes >= 1, "max_rows / max_scenes must be positive");
+  if (gemm_init()) return -1;
+  g_missing.clear();
+  const int D = cfg_.state_dim;
+  int rc = 0;
+  for (int i = 0; i < 4 && !rc; ++i) {
+    const int cin = i == 0 ? 16 : (32 << (i - 1)), cin_true = i == 0 ? D : cin, cout = 32 << i;
+    const std::string p = "downs." + std::to_string(i) + ".";
+    rc = load_res(down_rb_[i][0], p + "0.", cin, cout, cin_true);
+    if (!rc) rc = load_res(down_rb_[i][1], p + "1.", cout, cout, cout);
+    if (!rc) rc = load_st(down_st_[i], p + "3.", cout);
+    if (!rc && i < 3) rc = load_conv(down_conv_[i], p + "4.conv.", cout, cout, 3);
+  }
+  if (!rc) rc = load_res(mid_rb_[0], "mid_block1.", 256, 256, 256);
+  if (!rc) rc = load_st(mid_st_, "mid_attention.", 256);
+  if (!rc) rc = load_res(mid_rb_[1], "mid_block2.", 256, 256, 256);
+  for (int j = 0; j < 3 && !rc; ++j) {
+    const int cout = 128 >> j, cin = 4 * cout;
+    const std::string p = "ups." + std::to_string(j) + ".";
+    rc = load_res(up_rb_[j][0], p + "0.", cin, cout, cin);
+    if (!rc) rc = load_res(up_rb_[j][1], p + "1.", cout, cout, cout);
+    if (!rc) rc = load_st(up_st_[j], p + "3.", cout);
+    if (!rc) rc = load_conv(up_conv_[j], p + "4.conv.", cout, cout, 4, true);
+  }
+  if (!rc) rc = load_conv(final_c5_, "final_conv.0.block.0.", 32, 32, 5);
+  if (!rc) rc = load_conv(final_c1_, "final_conv.1.", 32, D, 1);
+  if (rc) return rc;
+  final_g_ = P("final_conv.0.block.2.weight", 32); final_b_ = P("final_conv.0.block.2.bias", 32);
+
+  // time MLP packed as [W1 | b1 | W2 | b2]
+  {
+    const float* w1 = P("time_mlp.encoder.1.weight", 128 * 32); const float* b1 = P("time_mlp.encoder.1.bias", 128);
+    const float* w2 = P("time_mlp.encoder.3.weight", 32 * 128); const float* b2 = P("time_mlp.encoder.3.bias", 32);
+    time_w_ = (float*)dev_alloc((128 * 32 + 128 + 32 * 128 + 32) * sizeof(float));
+    RAMP_CHECK(time_w_, "cudaMalloc failed");
+    if (w1 && b1 && w2 && b2) {
+      RAMP_CUDA_OK(cudaMemcpy(time_w_, w1, 128 * 32 * 4, cudaMemcpyDeviceToDevice));
+      RAMP_CUDA_OK(cudaMemcpy(time_w_ + 128 * 32, b1, 128 * 4, cudaMemcpyDeviceToDevice));
+      RAMP_CUDA_OK(cudaMemcpy(time_w_ + 128 * 32 + 128, w2, 32 * 128 * 4, cudaMemcpyDeviceToDevice));
+      RAMP_CUDA_OK(cudaMemcpy(time_w_ + 128 * 32 + 128 + 32 * 128, b2, 32 * 4, cudaMemcpyDeviceToDevice));
+    }
+  }
+  // cond_mlp table (16 residual blocks) and attn2 collapse table (16 transformer blocks)
+  {
+    std::vector<CondBlock> cb;
+    std::vector<std::pair<ResW*, std::string>> rbs;
+    for (int i = 0; i < 4; ++i) for (int k = 0; k < 2; ++k) rbs.push_back({&down_rb_[i][k], "downs." + std::to_string(i) + "." + std::to_string(k) + "."});
+    rbs.push_back({&mid_rb_[0], "mid_block1."}); rbs.push_back({&mid_rb_[1], "mid_block2."});
+    for (int j = 0; j < 3; ++j) for (int k = 0; k < 2; ++k) rbs.push_back({&up_rb_[j][k], "ups." + std::to_string(j) + "." + std::to_string(k) + "."});
+    for (auto& pr : rbs) {
+      CondBlock c;
+      c.w = P(pr.second + "cond_mlp.1.weight", (size_t)pr.first->cout * 32);
+      c.b = P(pr.second + "cond_mlp.1.bias", pr.first->cout);
+      c.out = pr.first->cond; c.cout = pr.first->cout;
+      cb.push_back(c);
+    }
+    cond_blocks_dev_ = dev_alloc(cb.size() * sizeof(CondBlock));
+    RAMP_CHECK(cond_blocks_dev_, "cudaMalloc failed");
+    RAMP_CUDA_OK(cudaMemcpy(cond_blocks_dev_, cb.data(), cb.size() * sizeof(CondBlock), cudaMemcpyHostToDevice));
+
+    std::vector<SceneBlock> sb;
+    std::vector<std::string> stp;
+    for (int i = 0; i < 4; ++i) stp.push_back("downs." + std::to_string(i) + ".3.");
+    stp.push_back("mid_attention.");
+    for (int j = 0; j < 3; ++j) stp.push_back("ups." + std::to_string(j) + ".3.");
+    for (size_t k = 0; k < stp.size(); ++k) {
+      for (int b = 0; b < 2; ++b) {
+        const std::string q = stp[k] + "transformer_blocks." + std::to_string(b) + ".";
+        SceneBlock blk;
+        blk.wv = P(q + "attn2.to_v.weight", (size_t)256 * cfg_.ctx_dim);
+        blk.wo = P(q + "attn2.to_out.0.weight", 256 * 256);
+        blk.bo2 = P(q + "attn2.to_out.0.bias", 256);
+        blk.bo1 = P(q + "attn1.to_out.0.bias", 256);
+        blk.tab = all_st_[k]->blk[b].bias_tab;
+        sb.push_back(blk);
+      }
+    }
+    scene_blocks_dev_ = dev_alloc(sb.size() * sizeof(SceneBlock));
+    RAMP_CHECK(scene_blocks_dev_, "cudaMalloc failed");
+    RAMP_CUDA_OK(cudaMemcpy(scene_blocks_dev_, sb.data(), sb.size() * sizeof(SceneBlock), cudaMemcpyHostToDevice));
+  }
+  RAMP_CHECK(g_missing.empty(), "state dict is incomplete or mis-shaped: " + g_missing);
+  RAMP_CUDA_OK(cudaDeviceSynchronize());
+
+  // size the workspace with a dry run at max_rows
+  dry_ = true; arena_off_ = 0;
+  rc = run(nullptr, cfg_.max_rows, 0.f, nullptr, nullptr, nullptr, s);
+  dry_ = false;
+  if (rc) return rc;
+  arena_bytes_ = arena_off_ + 256;
+  RAMP_CUDA_OK(cudaMalloc((void**)&arena_, arena_bytes_));
+  RAMP_CUDA_OK(cudaMemset(arena_, 0, arena_bytes_));
+  finalized_ = true;
+  return 0;
+}
+
+int UnetEngine::set_scenes(const float* latents_dev, int n_scenes, cudaStream_t s) {
+  RAMP_CHECK(finalized_, "set_scenes before finalize");
+  RAMP_CHECK(n_scenes >= 1 && n_scenes <= cfg_.max_scenes, "n_scenes out of range");
+  n_scenes_ = n_scenes;
+  return scene_constants((const SceneBlock*)scene_blocks_dev_, 16, latents_dev, n_scenes, cfg_.ctx_dim, s);
+}
+
+int UnetEngine::energy_grad(const float* x, int n_rows, float t, const int* row2scene, float* eps_out, float* f_out,
+                            cudaStream_t s) {
+  RAMP_CHECK(finalized_, "energy_grad before finalize");
+  RAMP_CHECK(n_scenes_ > 0, "energy_grad before set_scenes");
+  RAMP_CHECK(n_rows >= 1 && n_rows <= cfg_.max_rows, "n_rows exceeds max_rows of this engine");
+  arena_off_ = 0;
+  return run(x, n_rows, t, row2scene, eps_out, f_out, s);
+}
+
+}  // namespace ramp

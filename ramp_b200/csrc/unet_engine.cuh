@@ -1,0 +1,114 @@
+// Score-network engine: TemporalUnet forward + analytic input-gradient (energy gradient) on the GPU.
+// Mirrors TemporalUnetInference.forward / forward_no_energy / EnergyGradFunction
+// (mpd/models/diffusion_models/UnetInference.py:19-37,157-224).
+#pragma once
+#include "common.cuh"
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+namespace ramp {
+
+struct UnetConfig {
+  int state_dim;     // D (4 in 2-D, 6 in 3-D)
+  int horizon;       // H, multiple of 8, <= 64
+  int ctx_dim;       // 320 (2-D scene encoder) / 256 (3-D)
+  int precision;     // 1 or 3 (see gemm_tc.cu)
+  int max_rows;      // largest number of network rows per call (workspace is sized for this)
+  int max_scenes;    // largest number of distinct conditioning latents
+};
+
+struct PackedW {     // [ntaps][Nout][Kw] bf16 hi/lo planes
+  bf16* hi = nullptr; bf16* lo = nullptr; int ntaps = 0, Nout = 0, Kw = 0, K = 0;
+};
+struct ConvW {       // a conv / linear layer: forward and input-gradient packings
+  PackedW f, b; const float* bias = nullptr; int cin = 0, cout = 0, kw = 0;
+};
+struct ResW {
+  ConvW c1, c2, res; bool has_res = false;
+  const float *g1, *b1, *g2, *b2; float* cond = nullptr; int cin = 0, cout = 0;
+};
+struct TBlockW {
+  PackedW qkv_f, qkv_b, o_f, o_b, ff1_f, ff1_b, ff2_f, ff2_b;
+  const float *ln1g, *ln1b, *ln3g, *ln3b, *ff1_bias, *ff2_bias;
+  float* bias_tab = nullptr;   // [max_scenes, 256]: attn1.to_out bias + collapsed attn2 output per scene
+};
+struct STW {
+  const float *gn_g, *gn_b; ConvW pin, pout; TBlockW blk[2]; int C = 0;
+};
+
+// forward activations kept for the backward sweep
+struct ResSave { float* c1; float* c2; };
+struct TBlockSave { float* zin; float* qkv; float* z1; float* u; };
+struct STSave { const float* x; int ldx; TBlockSave blk[2]; };
+
+class UnetEngine {
+ public:
+  explicit UnetEngine(const UnetConfig& cfg) : cfg_(cfg) {}
+  ~UnetEngine();
+  int set_param(const std::string& name, const float* data, size_t numel);
+  int finalize(cudaStream_t s);
+  int set_scenes(const float* latents_dev, int n_scenes, cudaStream_t s);
+  // eps_out / f_out: [n_rows, H, D] (either may be null)
+  int energy_grad(const float* x, int n_rows, float t, const int* row2scene, float* eps_out, float* f_out,
+                  cudaStream_t s);
+  size_t workspace_bytes() const { return arena_bytes_; }
+  const UnetConfig& cfg() const { return cfg_; }
+
+ private:
+  struct Param { float* ptr; size_t numel; };
+  UnetConfig cfg_;
+  std::unordered_map<std::string, Param> params_;
+  std::vector<void*> owned_;
+  bool finalized_ = false;
+  int n_scenes_ = 0;
+
+  // weights
+  ResW down_rb_[4][2], mid_rb_[2], up_rb_[3][2];
+  STW down_st_[4], mid_st_, up_st_[3];
+  ConvW down_conv_[3], up_conv_[3], final_c5_, final_c1_;
+  const float *final_g_, *final_b_;
+  float* time_w_ = nullptr;          // packed time MLP
+  void* cond_blocks_dev_ = nullptr;  // CondBlock[16]
+  void* scene_blocks_dev_ = nullptr; // SceneBlock[16]
+  std::vector<STW*> all_st_;
+
+  // workspace arena (bump allocator; `dry_` = size-measuring pass)
+  char* arena_ = nullptr; size_t arena_bytes_ = 0, arena_off_ = 0; bool dry_ = false;
+  float* allocf(size_t n);
+  Split allocs(size_t n);
+  void* alloc_bytes(size_t n);
+
+  // helpers
+  const float* P(const std::string& name, size_t numel);
+  int pack(PackedW& w, const std::string& name, int T, int Nd, int Kd, int Ns, int Ks, long st, long sn, long sk,
+           int noff = 0, int koff = 0, bool alloc = true);
+  int load_conv(ConvW& c, const std::string& prefix, int cin, int cout, int kw, bool transposed = false);
+  int load_res(ResW& r, const std::string& prefix, int cin, int cout, int cin_true);
+  int load_st(STW& st, const std::string& prefix, int C);
+  void* dev_alloc(size_t bytes);
+
+  struct Act {  // channels-last activation view
+    const float* f = nullptr; int ldf = 0;
+    const bf16* hi = nullptr; const bf16* lo = nullptr; int lds = 0;
+    int C = 0;
+  };
+  struct OutSpec {  // where a layer should write its result
+    bool want_f = true;
+    bf16* hi = nullptr; bf16* lo = nullptr; int lds = 0;   // external split destination (e.g. concat buffer), or
+    bool want_s = true;                                       // allocate a private one
+  };
+  int run(const float* x, int n_rows, float t, const int* row2scene, float* eps_out, float* f_out, cudaStream_t s);
+  int gemm(const Act& a, int K, const PackedW& w, const GemmTap* taps, int ntaps, int L_in, int L_out, int pstride,
+           const float* bias, const float* bias_tab, const float* res, int ldr, const float* res2, int ldr2,
+           float* of, int ldo, bf16* oh, bf16* ol, int lds, int o_L, int o_stride, int o_off);
+  int res_fwd(const ResW& w, const Act& x, int L, const OutSpec& o, Act& y, ResSave& sv);
+  int res_bwd(const ResW& w, const ResSave& sv, const Act& dy, int L, const float* extra, int ldextra, Act& dx,
+              bool want_split);
+  int st_fwd(const STW& w, const Act& x, int L, const OutSpec& o, Act& y, STSave& sv);
+  int st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act& dx);
+
+  int n_ = 0, npad_ = 0; const int* r2s_ = nullptr; cudaStream_t s_ = nullptr;
+};
+
+}  // namespace ramp

@@ -1,0 +1,412 @@
+// See unet_engine.cuh.  Part 2: the forward sweep and the analytic input-gradient sweep.
+#include "unet_engine.cuh"
+#include "unet_ops.cuh"
+
+namespace ramp {
+
+#define TRY(expr) do { int _rc = (expr); if (_rc) return _rc; } while (0)
+
+static const GemmTap TAP_1X1[1] = {{0, 0, 0}};
+static const GemmTap TAP_C5_F[5] = {{0, -2, 0}, {0, -1, 1}, {0, 0, 2}, {0, 1, 3}, {0, 2, 4}};
+static const GemmTap TAP_C5_B[5] = {{0, 2, 0}, {0, 1, 1}, {0, 0, 2}, {0, -1, 3}, {0, -2, 4}};
+// Conv1d k3 s2 p1 (layers.py:262-268): y[l] = sum_k W_k x[2l + k - 1]
+static const GemmTap TAP_DOWN_F[3] = {{1, -1, 0}, {0, 0, 1}, {1, 0, 2}};
+static const GemmTap TAP_DOWN_B_EVEN[1] = {{0, 0, 1}};
+static const GemmTap TAP_DOWN_B_ODD[2] = {{0, 1, 0}, {0, 0, 2}};
+// ConvTranspose1d k4 s2 p1 (layers.py:271-277): y[2i - 1 + k] += W_k x[i]
+static const GemmTap TAP_UP_F_EVEN[2] = {{0, 0, 1}, {0, -1, 3}};
+static const GemmTap TAP_UP_F_ODD[2] = {{0, 1, 0}, {0, 0, 2}};
+static const GemmTap TAP_UP_B[4] = {{1, -1, 0}, {0, 0, 1}, {1, 0, 2}, {0, 1, 3}};
+
+__global__ void extract_kernel(const float* __restrict__ src, int n_rows, int H, int D, float* __restrict__ dst) {
+  const size_t total = (size_t)n_rows * H * D;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = i / D;
+    dst[i] = src[row * 16 + (i - row * D)];
+  }
+}
+
+int UnetEngine::gemm(const Act& a, int K, const PackedW& w, const GemmTap* taps, int ntaps, int L_in, int L_out,
+                     int pstride, const float* bias, const float* bias_tab, const float* res, int ldr,
+                     const float* res2, int ldr2, float* of, int ldo, bf16* oh, bf16* ol, int lds, int o_L,
+                     int o_stride, int o_off) {
+  if (dry_) return 0;
+  GemmDesc d{};
+  d.a_hi = a.hi; d.a_lo = a.lo; d.n_samples = npad_; d.L_in = L_in; d.ldA = a.lds; d.K = K; d.a_pstride = pstride;
+  d.L_out = L_out; d.ntaps = ntaps;
+  for (int t = 0; t < ntaps; ++t) d.taps[t] = taps[t];
+  d.w_hi = w.hi; d.w_lo = w.lo; d.Nout = w.Nout; d.Kw = w.Kw; d.n_wtaps = w.ntaps;
+  d.bias = bias; d.bias_tab = bias_tab; d.row2scene = r2s_; d.residual = res; d.ldR = ldr; d.residual2 = res2;
+  d.ldR2 = ldr2; d.out_f32 = of; d.ldO = ldo; d.out_hi = oh; d.out_lo = ol; d.ldS = lds;
+  d.o_L = o_L; d.o_stride = o_stride; d.o_off = o_off; d.precision = cfg_.precision;
+  return gemm_launch(d, s_);
+}
+
+// ResidualTemporalBlock (layers.py:327-361)
+int UnetEngine::res_fwd(const ResW& w, const Act& x, int L, const OutSpec& o, Act& y, ResSave& sv) {
+  const size_t M = (size_t)npad_ * L;
+  const int co = w.cout;
+  sv.c1 = allocf(M * co);
+  TRY(gemm(x, w.c1.f.K, w.c1.f, TAP_C5_F, 5, L, L, 1, w.c1.bias, nullptr, nullptr, 0, nullptr, 0, sv.c1, co, nullptr,
+           nullptr, 0, L, 1, 0));
+  Split h1 = allocs(M * co);
+  if (!dry_) {
+    GnArgs g{}; g.x = sv.c1; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g1; g.beta = w.b1;
+    g.eps = 1e-5f; g.mish = 1; g.cond = w.cond; g.out_hi = h1.hi; g.out_lo = h1.lo; g.ldS = co;
+    TRY(gn_forward(g, s_));
+  }
+  sv.c2 = allocf(M * co);
+  Act h1a; h1a.hi = h1.hi; h1a.lo = h1.lo; h1a.lds = co; h1a.C = co;
+  TRY(gemm(h1a, co, w.c2.f, TAP_C5_F, 5, L, L, 1, w.c2.bias, nullptr, nullptr, 0, nullptr, 0, sv.c2, co, nullptr,
+           nullptr, 0, L, 1, 0));
+  const float* addp = x.f; int ldadd = x.ldf;
+  if (w.has_res) {
+    float* r = allocf(M * co);
+    TRY(gemm(x, w.res.f.K, w.res.f, TAP_1X1, 1, L, L, 1, w.res.bias, nullptr, nullptr, 0, nullptr, 0, r, co, nullptr,
+             nullptr, 0, L, 1, 0));
+    addp = r; ldadd = co;
+  } else {
+    RAMP_CHECK(dry_ || x.f != nullptr, "internal: identity residual needs the fp32 input");
+  }
+  y = Act(); y.C = co;
+  if (o.want_f) { y.f = allocf(M * co); y.ldf = co; }
+  bf16 *oh = o.hi, *ol = o.lo; int lds = o.lds;
+  if (!oh && o.want_s) { Split s = allocs(M * co); oh = s.hi; ol = s.lo; lds = co; }
+  y.hi = oh; y.lo = ol; y.lds = lds;
+  if (!dry_) {
+    GnArgs g{}; g.x = sv.c2; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g2; g.beta = w.b2;
+    g.eps = 1e-5f; g.mish = 1; g.add = addp; g.ldAdd = ldadd; g.out_f32 = const_cast<float*>(y.f); g.ldO = co;
+    g.out_hi = oh; g.out_lo = ol; g.ldS = lds;
+    TRY(gn_forward(g, s_));
+  }
+  return 0;
+}
+
+int UnetEngine::res_bwd(const ResW& w, const ResSave& sv, const Act& dy, int L, const float* extra, int ldextra,
+                        Act& dx, bool want_split) {
+  const size_t M = (size_t)npad_ * L;
+  const int co = w.cout, ci = w.c1.b.Nout;
+  Split t1 = allocs(M * co);
+  if (!dry_) {
+    GnBwdArgs g{}; g.x = sv.c2; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g2; g.beta = w.b2;
+    g.eps = 1e-5f; g.mish = 1; g.dy = dy.f; g.ldDy = dy.ldf; g.out_hi = t1.hi; g.out_lo = t1.lo; g.ldS = co;
+    TRY(gn_backward(g, s_));
+  }
+  float* dh1 = allocf(M * co);
+  Act t1a; t1a.hi = t1.hi; t1a.lo = t1.lo; t1a.lds = co;
+  TRY(gemm(t1a, co, w.c2.b, TAP_C5_B, 5, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dh1, co, nullptr, nullptr,
+           0, L, 1, 0));
+  Split t2 = allocs(M * co);
+  if (!dry_) {
+    GnBwdArgs g{}; g.x = sv.c1; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g1; g.beta = w.b1;
+    g.eps = 1e-5f; g.mish = 1; g.dy = dh1; g.ldDy = co; g.out_hi = t2.hi; g.out_lo = t2.lo; g.ldS = co;
+    TRY(gn_backward(g, s_));
+  }
+  const float* res = dy.f; int ldr = dy.ldf;
+  if (w.has_res) {
+    RAMP_CHECK(dry_ || dy.hi != nullptr, "internal: residual-conv backward needs the split gradient");
+    float* r = allocf(M * ci);
+    TRY(gemm(dy, co, w.res.b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, r, ci, nullptr, nullptr, 0,
+             L, 1, 0));
+    res = r; ldr = ci;
+  }
+  dx = Act(); dx.C = ci;
+  float* dxf = allocf(M * ci);
+  dx.f = dxf; dx.ldf = ci;
+  Split ds{nullptr, nullptr};
+  if (want_split) { ds = allocs(M * ci); dx.hi = ds.hi; dx.lo = ds.lo; dx.lds = ci; }
+  Act t2a; t2a.hi = t2.hi; t2a.lo = t2.lo; t2a.lds = co;
+  TRY(gemm(t2a, co, w.c1.b, TAP_C5_B, 5, L, L, 1, nullptr, nullptr, res, ldr, extra, ldextra, dxf, ci, ds.hi, ds.lo, ci,
+           L, 1, 0));
+  return 0;
+}
+
+// SpatialTransformer (layers_attention_mini.py:152-202) with two BasicTransformerBlocks (:130-149)
+int UnetEngine::st_fwd(const STW& w, const Act& x, int L, const OutSpec& o, Act& y, STSave& sv) {
+  const size_t M = (size_t)npad_ * L;
+  const int C = w.C;
+  RAMP_CHECK(dry_ || x.f != nullptr, "internal: transformer needs the fp32 input");
+  sv.x = x.f; sv.ldx = x.ldf;
+  Split xn = allocs(M * C);
+  if (!dry_) {
+    GnArgs g{}; g.x = x.f; g.ldX = x.ldf; g.n_samples = npad_; g.L = L; g.C = C; g.gamma = w.gn_g; g.beta = w.gn_b;
+    g.eps = 1e-6f; g.mish = 0; g.out_hi = xn.hi; g.out_lo = xn.lo; g.ldS = C;
+    TRY(gn_forward(g, s_));
+  }
+  float* z = allocf(M * 256);
+  Act xna; xna.hi = xn.hi; xna.lo = xn.lo; xna.lds = C;
+  TRY(gemm(xna, C, w.pin.f, TAP_1X1, 1, L, L, 1, w.pin.bias, nullptr, nullptr, 0, nullptr, 0, z, 256, nullptr, nullptr, 0,
+           L, 1, 0));
+  Split zs{nullptr, nullptr};
+  for (int b = 0; b < 2; ++b) {
+    const TBlockW& t = w.blk[b];
+    TBlockSave& ts = sv.blk[b];
+    ts.zin = z;
+    Split a = allocs(M * 256);
+    if (!dry_) TRY(ln_forward(z, (int)M, 256, t.ln1g, t.ln1b, a.hi, a.lo, s_));
+    ts.qkv = allocf(M * 768);
+    Act aa; aa.hi = a.hi; aa.lo = a.lo; aa.lds = 256;
+    TRY(gemm(aa, 256, t.qkv_f, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, ts.qkv, 768, nullptr,
+             nullptr, 0, L, 1, 0));
+    Split ao = allocs(M * 256);
+    if (!dry_) TRY(attn_forward(ts.qkv, npad_, L, ao.hi, ao.lo, s_));
+    ts.z1 = allocf(M * 256);
+    Act aoa; aoa.hi = ao.hi; aoa.lo = ao.lo; aoa.lds = 256;
+    TRY(gemm(aoa, 256, t.o_f, TAP_1X1, 1, L, L, 1, nullptr, t.bias_tab, z, 256, nullptr, 0, ts.z1, 256, nullptr, nullptr,
+             0, L, 1, 0));
+    Split f = allocs(M * 256);
+    if (!dry_) TRY(ln_forward(ts.z1, (int)M, 256, t.ln3g, t.ln3b, f.hi, f.lo, s_));
+    ts.u = allocf(M * 2048);
+    Act fa; fa.hi = f.hi; fa.lo = f.lo; fa.lds = 256;
+    TRY(gemm(fa, 256, t.ff1_f, TAP_1X1, 1, L, L, 1, t.ff1_bias, nullptr, nullptr, 0, nullptr, 0, ts.u, 2048, nullptr,
+             nullptr, 0, L, 1, 0));
+    Split g = allocs(M * 1024);
+    if (!dry_) TRY(geglu_forward(ts.u, (int)M, 1024, g.hi, g.lo, s_));
+    float* z2 = allocf(M * 256);
+    if (b == 1) zs = allocs(M * 256);
+    Act ga; ga.hi = g.hi; ga.lo = g.lo; ga.lds = 1024;
+    TRY(gemm(ga, 1024, t.ff2_f, TAP_1X1, 1, L, L, 1, t.ff2_bias, nullptr, ts.z1, 256, nullptr, 0, z2, 256,
+             b == 1 ? zs.hi : nullptr, b == 1 ? zs.lo : nullptr, 256, L, 1, 0));
+    z = z2;
+  }
+  y = Act(); y.C = C;
+  float* yf = nullptr;
+  if (o.want_f) { yf = allocf(M * C); y.f = yf; y.ldf = C; }
+  bf16 *oh = o.hi, *ol = o.lo; int lds = o.lds;
+  if (!oh && o.want_s) { Split s = allocs(M * C); oh = s.hi; ol = s.lo; lds = C; }
+  y.hi = oh; y.lo = ol; y.lds = lds;
+  Act zsa; zsa.hi = zs.hi; zsa.lo = zs.lo; zsa.lds = 256;
+  TRY(gemm(zsa, 256, w.pout.f, TAP_1X1, 1, L, L, 1, w.pout.bias, nullptr, x.f, x.ldf, nullptr, 0, yf, C, oh, ol, lds, L, 1,
+           0));
+  return 0;
+}
+
+int UnetEngine::st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act& dx) {
+  const size_t M = (size_t)npad_ * L;
+  const int C = w.C;
+  RAMP_CHECK(dry_ || (dy.f && dy.hi), "internal: transformer backward needs fp32 and split gradients");
+  float* dz = allocf(M * 256);
+  Split dzs = allocs(M * 256);
+  TRY(gemm(dy, C, w.pout.b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dz, 256, dzs.hi, dzs.lo, 256, L,
+           1, 0));
+  for (int b = 1; b >= 0; --b) {
+    const TBlockW& t = w.blk[b];
+    const TBlockSave& ts = sv.blk[b];
+    float* dg = allocf(M * 1024);
+    Act dza; dza.hi = dzs.hi; dza.lo = dzs.lo; dza.lds = 256;
+    TRY(gemm(dza, 256, t.ff2_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dg, 1024, nullptr, nullptr,
+             0, L, 1, 0));
+    Split du = allocs(M * 2048);
+    if (!dry_) TRY(geglu_backward(ts.u, dg, (int)M, 1024, du.hi, du.lo, s_));
+    float* df = allocf(M * 256);
+    Act dua; dua.hi = du.hi; dua.lo = du.lo; dua.lds = 2048;
+    TRY(gemm(dua, 2048, t.ff1_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, df, 256, nullptr, nullptr,
+             0, L, 1, 0));
+    float* dz1 = allocf(M * 256);
+    Split dz1s = allocs(M * 256);
+    if (!dry_) TRY(ln_backward(ts.z1, (int)M, 256, t.ln3g, df, dz, dz1, dz1s.hi, dz1s.lo, s_));
+    float* dout = allocf(M * 256);
+    Act d1a; d1a.hi = dz1s.hi; d1a.lo = dz1s.lo; d1a.lds = 256;
+    TRY(gemm(d1a, 256, t.o_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dout, 256, nullptr, nullptr,
+             0, L, 1, 0));
+    Split dqkv = allocs(M * 768);
+    if (!dry_) TRY(attn_backward(ts.qkv, dout, npad_, L, dqkv.hi, dqkv.lo, s_));
+    float* da = allocf(M * 256);
+    Act dqa; dqa.hi = dqkv.hi; dqa.lo = dqkv.lo; dqa.lds = 768;
+    TRY(gemm(dqa, 768, t.qkv_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, da, 256, nullptr, nullptr,
+             0, L, 1, 0));
+    dz = allocf(M * 256);
+    dzs = allocs(M * 256);
+    if (!dry_) TRY(ln_backward(ts.zin, (int)M, 256, t.ln1g, da, dz1, dz, dzs.hi, dzs.lo, s_));
+  }
+  float* dxn = allocf(M * C);
+  Act dza; dza.hi = dzs.hi; dza.lo = dzs.lo; dza.lds = 256;
+  TRY(gemm(dza, 256, w.pin.b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dxn, C, nullptr, nullptr, 0,
+           L, 1, 0));
+  dx = Act(); dx.C = C;
+  float* dxf = allocf(M * C);
+  Split ds = allocs(M * C);
+  dx.f = dxf; dx.ldf = C; dx.hi = ds.hi; dx.lo = ds.lo; dx.lds = C;
+  if (!dry_) {
+    GnBwdArgs g{}; g.x = sv.x; g.ldX = sv.ldx; g.n_samples = npad_; g.L = L; g.C = C; g.gamma = w.gn_g; g.beta = w.gn_b;
+    g.eps = 1e-6f; g.mish = 0; g.dy = dxn; g.ldDy = C; g.add = dy.f; g.ldAdd = dy.ldf; g.out_f32 = dxf; g.ldO = C;
+    g.out_hi = ds.hi; g.out_lo = ds.lo; g.ldS = C;
+    TRY(gn_backward(g, s_));
+  }
+  return 0;
+}
+
+// forward_no_energy + EnergyGradFunction (UnetInference.py:19-37,176-224)
+int UnetEngine::run(const float* x, int n_rows, float t, const int* row2scene, float* eps_out, float* f_out,
+                    cudaStream_t s) {
+  const int H = cfg_.horizon, D = cfg_.state_dim;
+  n_ = n_rows; npad_ = (n_rows + 15) / 16 * 16; s_ = s;
+  int* r2s = (int*)alloc_bytes((size_t)npad_ * sizeof(int));
+  r2s_ = r2s;
+  if (!dry_) {
+    RAMP_CUDA_OK(cudaMemsetAsync(r2s, 0, (size_t)npad_ * sizeof(int), s));
+    if (row2scene) RAMP_CUDA_OK(cudaMemcpyAsync(r2s, row2scene, (size_t)n_rows * sizeof(int), cudaMemcpyDeviceToDevice, s));
+    TRY(time_cond(time_w_, t, (const CondBlock*)cond_blocks_dev_, 16, s));
+  }
+  Split xin = allocs((size_t)npad_ * H * 16);
+  if (!dry_) TRY(prep_input(x, n_rows, npad_, H, D, xin.hi, xin.lo, s));
+  // concat buffers of the up path: cat[j] = [prev | skip], ld = 2*Cc, at L = H/8 << j
+  Split cat[3];
+  for (int j = 0; j < 3; ++j) cat[j] = allocs((size_t)npad_ * ((H / 8) << j) * (512 >> j));
+
+  ResSave rs_down[4][2], rs_mid[2], rs_up[3][2], rs_dummy;
+  STSave ss_down[4], ss_mid, ss_up[3];
+  (void)rs_dummy;
+
+  // ------------------------------- forward -------------------------------
+  Act cur; cur.hi = xin.hi; cur.lo = xin.lo; cur.lds = 16; cur.C = 16;
+  int L = H;
+  for (int i = 0; i < 4; ++i) {
+    const int C = 32 << i;
+    Act a0, a1, y;
+    OutSpec both;
+    TRY(res_fwd(down_rb_[i][0], cur, L, both, a0, rs_down[i][0]));
+    TRY(res_fwd(down_rb_[i][1], a0, L, both, a1, rs_down[i][1]));
+    OutSpec o;
+    o.want_f = (i == 3);
+    if (i >= 1) { o.hi = cat[3 - i].hi + C; o.lo = cat[3 - i].lo + C; o.lds = 2 * C; }
+    TRY(st_fwd(down_st_[i], a1, L, o, y, ss_down[i]));
+    if (i < 3) {
+      Split d = allocs((size_t)npad_ * (L / 2) * C);
+      TRY(gemm(y, C, down_conv_[i].f, TAP_DOWN_F, 3, L, L / 2, 2, down_conv_[i].bias, nullptr, nullptr, 0, nullptr, 0,
+               nullptr, 0, d.hi, d.lo, C, L / 2, 1, 0));
+      cur = Act(); cur.hi = d.hi; cur.lo = d.lo; cur.lds = C; cur.C = C;
+      L /= 2;
+    } else {
+      cur = y;
+    }
+  }
+  {
+    Act m1, m2, m3;
+    OutSpec both;
+    TRY(res_fwd(mid_rb_[0], cur, L, both, m1, rs_mid[0]));
+    TRY(st_fwd(mid_st_, m1, L, both, m2, ss_mid));
+    OutSpec o; o.want_f = false; o.hi = cat[0].hi; o.lo = cat[0].lo; o.lds = 512;
+    TRY(res_fwd(mid_rb_[1], m2, L, o, m3, rs_mid[1]));
+  }
+  Split u2{nullptr, nullptr};   // last upsample output [npad*H, 32]
+  for (int j = 0; j < 3; ++j) {
+    const int co = 128 >> j;
+    Act in; in.hi = cat[j].hi; in.lo = cat[j].lo; in.lds = 4 * co; in.C = 4 * co;
+    Act a0, a1, y;
+    OutSpec both;
+    TRY(res_fwd(up_rb_[j][0], in, L, both, a0, rs_up[j][0]));
+    TRY(res_fwd(up_rb_[j][1], a0, L, both, a1, rs_up[j][1]));
+    OutSpec o; o.want_f = false;
+    TRY(st_fwd(up_st_[j], a1, L, o, y, ss_up[j]));
+    bf16 *oh, *ol; int lds;
+    if (j < 2) { oh = cat[j + 1].hi; ol = cat[j + 1].lo; lds = 2 * co; }
+    else { u2 = allocs((size_t)npad_ * 2 * L * co); oh = u2.hi; ol = u2.lo; lds = co; }
+    TRY(gemm(y, co, up_conv_[j].f, TAP_UP_F_EVEN, 2, L, L, 1, up_conv_[j].bias, nullptr, nullptr, 0, nullptr, 0, nullptr,
+             0, oh, ol, lds, 2 * L, 2, 0));
+    TRY(gemm(y, co, up_conv_[j].f, TAP_UP_F_ODD, 2, L, L, 1, up_conv_[j].bias, nullptr, nullptr, 0, nullptr, 0, nullptr, 0,
+             oh, ol, lds, 2 * L, 2, 1));
+    L *= 2;
+  }
+  const size_t M = (size_t)npad_ * H;
+  float* cfin = allocf(M * 32);
+  {
+    Act ua; ua.hi = u2.hi; ua.lo = u2.lo; ua.lds = 32;
+    TRY(gemm(ua, 32, final_c5_.f, TAP_C5_F, 5, H, H, 1, final_c5_.bias, nullptr, nullptr, 0, nullptr, 0, cfin, 32, nullptr,
+             nullptr, 0, H, 1, 0));
+  }
+  Split hs = allocs(M * 32);
+  if (!dry_) {
+    GnArgs g{}; g.x = cfin; g.ldX = 32; g.n_samples = npad_; g.L = H; g.C = 32; g.gamma = final_g_; g.beta = final_b_;
+    g.eps = 1e-5f; g.mish = 1; g.out_hi = hs.hi; g.out_lo = hs.lo; g.ldS = 32;
+    TRY(gn_forward(g, s));
+  }
+  float* fo = allocf(M * 16);
+  Split fos = allocs(M * 16);
+  {
+    Act ha; ha.hi = hs.hi; ha.lo = hs.lo; ha.lds = 32;
+    TRY(gemm(ha, 32, final_c1_.f, TAP_1X1, 1, H, H, 1, final_c1_.bias, nullptr, nullptr, 0, nullptr, 0, fo, 16, fos.hi,
+             fos.lo, 16, H, 1, 0));
+  }
+  const int eb = (int)((((size_t)n_rows * H * D + 255) / 256) > 1184 ? 1184 : (((size_t)n_rows * H * D + 255) / 256));
+  if (!dry_ && f_out) {
+    extract_kernel<<<eb, 256, 0, s>>>(fo, n_rows, H, D, f_out);
+    RAMP_CUDA_OK(cudaGetLastError());
+  }
+  if (!dry_ && !eps_out) return 0;
+
+  // ------------------------------- backward: d(0.5*sum f^2)/dx, seed = f -------------------------------
+  float* dh = allocf(M * 32);
+  {
+    Act fa; fa.hi = fos.hi; fa.lo = fos.lo; fa.lds = 16;
+    TRY(gemm(fa, 16, final_c1_.b, TAP_1X1, 1, H, H, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dh, 32, nullptr, nullptr,
+             0, H, 1, 0));
+  }
+  Split dcs = allocs(M * 32);
+  if (!dry_) {
+    GnBwdArgs g{}; g.x = cfin; g.ldX = 32; g.n_samples = npad_; g.L = H; g.C = 32; g.gamma = final_g_; g.beta = final_b_;
+    g.eps = 1e-5f; g.mish = 1; g.dy = dh; g.ldDy = 32; g.out_hi = dcs.hi; g.out_lo = dcs.lo; g.ldS = 32;
+    TRY(gn_backward(g, s));
+  }
+  Act dy; dy.C = 32;
+  {
+    float* f = allocf(M * 32); Split sp = allocs(M * 32);
+    Act da; da.hi = dcs.hi; da.lo = dcs.lo; da.lds = 32;
+    TRY(gemm(da, 32, final_c5_.b, TAP_C5_B, 5, H, H, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, f, 32, sp.hi, sp.lo, 32,
+             H, 1, 0));
+    dy.f = f; dy.ldf = 32; dy.hi = sp.hi; dy.lo = sp.lo; dy.lds = 32;
+  }
+  L = H;
+  const float* dcat[3] = {nullptr, nullptr, nullptr};   // fp32 gradient of cat[j], ld = 512 >> j
+  for (int j = 2; j >= 0; --j) {
+    const int co = 128 >> j;
+    // ConvTranspose backward: stride-2 gather over the parity view of dy
+    Act dst; dst.C = co;
+    {
+      const size_t Mi = (size_t)npad_ * (L / 2);
+      float* f = allocf(Mi * co); Split sp = allocs(Mi * co);
+      TRY(gemm(dy, co, up_conv_[j].b, TAP_UP_B, 4, L, L / 2, 2, nullptr, nullptr, nullptr, 0, nullptr, 0, f, co, sp.hi,
+               sp.lo, co, L / 2, 1, 0));
+      dst.f = f; dst.ldf = co; dst.hi = sp.hi; dst.lo = sp.lo; dst.lds = co;
+    }
+    L /= 2;
+    Act d2, d1, d0;
+    TRY(st_bwd(up_st_[j], ss_up[j], dst, L, d2));
+    TRY(res_bwd(up_rb_[j][1], rs_up[j][1], d2, L, nullptr, 0, d1, true));
+    TRY(res_bwd(up_rb_[j][0], rs_up[j][0], d1, L, nullptr, 0, d0, j > 0));
+    dcat[j] = d0.f;
+    dy = Act(); dy.C = 2 * co; dy.f = d0.f; dy.ldf = 4 * co; dy.hi = d0.hi; dy.lo = d0.lo; dy.lds = 4 * co;
+  }
+  {
+    Act d2, d1, d0;
+    TRY(res_bwd(mid_rb_[1], rs_mid[1], dy, L, nullptr, 0, d2, true));
+    TRY(st_bwd(mid_st_, ss_mid, d2, L, d1));
+    TRY(res_bwd(mid_rb_[0], rs_mid[0], d1, L, dcat[0] + 256, 512, d0, true));
+    dy = d0;
+  }
+  for (int i = 3; i >= 0; --i) {
+    Act d2, d1, d0;
+    TRY(st_bwd(down_st_[i], ss_down[i], dy, L, d2));
+    TRY(res_bwd(down_rb_[i][1], rs_down[i][1], d2, L, nullptr, 0, d1, true));
+    TRY(res_bwd(down_rb_[i][0], rs_down[i][0], d1, L, nullptr, 0, d0, i > 0));
+    if (i > 0) {
+      const int Cp = 32 << (i - 1);
+      const size_t Mo = (size_t)npad_ * (2 * L);
+      float* f = allocf(Mo * Cp); Split sp = allocs(Mo * Cp);
+      const float* skip = nullptr; int ldskip = 0;
+      if (i - 1 >= 1) { skip = dcat[3 - (i - 1)] + Cp; ldskip = 2 * Cp; }
+      TRY(gemm(d0, Cp, down_conv_[i - 1].b, TAP_DOWN_B_EVEN, 1, L, L, 1, nullptr, nullptr, skip, ldskip, nullptr, 0, f,
+               Cp, sp.hi, sp.lo, Cp, 2 * L, 2, 0));
+      TRY(gemm(d0, Cp, down_conv_[i - 1].b, TAP_DOWN_B_ODD, 2, L, L, 1, nullptr, nullptr, skip, ldskip, nullptr, 0, f, Cp,
+               sp.hi, sp.lo, Cp, 2 * L, 2, 1));
+      dy = Act(); dy.C = Cp; dy.f = f; dy.ldf = Cp; dy.hi = sp.hi; dy.lo = sp.lo; dy.lds = Cp;
+      L *= 2;
+    } else if (!dry_) {
+      extract_kernel<<<eb, 256, 0, s>>>(d0.f, n_rows, H, D, eps_out);
+      RAMP_CUDA_OK(cudaGetLastError());
+    }
+  }
+  return 0;
+}
+
+}  // namespace ramp
