@@ -57,10 +57,63 @@ size_t ramp_unet_workspace_bytes(void* handle);
 /* latents [n_scenes, ctx_dim]: cached scene-encoder outputs (UnetInference.py:146-156); an all-zero row is
  * the unconditional branch (UnetInference.py:190-197). */
 int ramp_unet_set_scenes(void* handle, const float* latents, int n_scenes, void* stream);
-/* x [n_rows, H, D]; t = the (batch-uniform) diffusion timestep; row2scene [n_rows] int32;
+/* Network row n reads trajectory x[n / x_repeat] (x_repeat = G+1 evaluates every trajectory under each
+ * conditioning without materialising repeat_interleave, diffusion_model_static.py:142-145,192-206);
+ * x [ceil(n_rows/x_repeat), H, D]; t = the (batch-uniform) diffusion timestep; row2scene [n_rows] int32;
  * eps_out / f_out [n_rows, H, D], either may be NULL (f_out = forward_no_energy output). */
-int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, float t, const int32_t* row2scene, float* eps_out,
-                          float* f_out, void* stream);
+int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, int x_repeat, float t, const int32_t* row2scene,
+                          float* eps_out, float* f_out, void* stream);
+
+/* ---- fused sampler step (one launch per reverse-diffusion step) --------------------------------
+ * eps rows come from ramp_unet_energy_grad; row of (trajectory b, group g) = b*eps_bstride + g*eps_gstride,
+ * g == G is the unconditional row.  eps = eps_u + sum_g w_g (eps_g - eps_u)   [G == 1: (1+w) eps_c - w eps_u].
+ * mode 0 (DDPM, sample_functions.py:19-48 + diffusion_model_static.py:149-172):
+ *     x0 = clamp(sqrt_recip*x - sqrt_recipm1*eps, +-1); out = coef1*x0 + coef2*x + sigma*noise*noise_scale
+ * mode 1 (DDIM eta=0, diffusion_model_static.py:259-333): out = sa_prev*x0 + sdir*((x - sa_t*x0)/sb_t)
+ * mode 2: only x0_out / eps_out are written (the APF runs between the two halves of a DDIM step).
+ * Inpainting (sample_functions.py:5-10): waypoint h of every trajectory is overwritten by
+ * pin_val[b*pin_bstride + h*D ...] when pin_mask[h] != 0.  out may alias x. */
+typedef struct ramp_step_args {
+  const float* x; const float* eps; long eps_bstride; long eps_gstride;
+  int B, H, D, G; float w[8];
+  float sqrt_recip, sqrt_recipm1;
+  float coef1, coef2, sigma, noise_scale; const float* noise;
+  float sa_t, sb_t, sa_prev, sdir;
+  const unsigned char* pin_mask; const float* pin_val; long pin_bstride;
+  float* out; float* x0_out; float* eps_out; int mode;
+  int predict_epsilon;   /* 1: network output is noise (scripts); 0: it is x0 itself (diffusion_model_static.py:109-118) */
+} ramp_step_args;
+int ramp_step(const ramp_step_args* args, void* stream);
+int ramp_ddim_update(const float* x, const float* x0, int B, int H, int D, float sa_t, float sb_t, float sa_prev,
+                     float sdir, const unsigned char* pin_mask, const float* pin_val, long pin_bstride, float* out,
+                     void* stream);
+int ramp_inpaint(float* x, int B, int H, int D, const unsigned char* pin_mask, const float* pin_val, long pin_bstride,
+                 void* stream);
+/* q_sample (diffusion_model_dynamic.py:671-680); x0_bstride 0 broadcasts one trajectory over the batch */
+int ramp_q_sample(const float* x0, long x0_bstride, const float* noise, int B, int H, int D, float sqrt_ac,
+                  float sqrt_1mac, const unsigned char* pin_mask, const float* pin_val, long pin_bstride, float* out,
+                  void* stream);
+
+/* ---- point cloud: nearest point, APF, cost, selection ------------------------------------------
+ * ramp_cloud_pack: cloud [P, dim] fp32 -> packed buffer of ramp_cloud_packed_points(P) float4
+ * ramp_nn_query  : cKDTree.query(k=1, distance_upper_bound) (APFhelper.py:17-35): for q[i*qstride + 0..dim-1],
+ *                  out_dist = distance (inf if >= upper_bound), out_idx = index (P if none). */
+size_t ramp_cloud_packed_points(int P);
+int ramp_cloud_pack(const float* cloud, int P, int dim, void* packed, void* stream);
+int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int qstride, float upper_bound,
+                  float* out_dist, int32_t* out_idx, void* stream);
+/* avoidance (APFhelper.py:37-104): windowed Gaussian push away from the nearest point; out may alias x */
+int ramp_apf_static(const float* x, int B, int H, int D, int dim, const float* dist, const int32_t* idx,
+                    const void* packed, int P, float thr, float strength, int window, float* out, void* stream);
+/* avoidance (APFhelper_dynamic.py:107-142), in place; mode 0 = static boxes, 1 = pursuer disc (goal mixing) */
+int ramp_apf_dynamic(float* x, int B, int H, int D, const float* dist, const int32_t* idx, const void* packed, int P,
+                     int mode, int window, int affected, float strength, float thr_force, const float* goal,
+                     const unsigned char* active, void* stream);
+/* cost.py:3-54: terms[b] = (collision_free, path_length, smoothness); dist from ramp_nn_query(upper_bound = thr) */
+int ramp_cost_terms(const float* x, int B, int H, int D, int dim, const float* dist, float thr, float* terms,
+                    void* stream);
+/* cost.py:56-88 over n (all-gathered) trajectories: out8 = (best index or -1, best cost, n_free, len min/max, smooth min/max, 0) */
+int ramp_select_best(const float* terms, int n, float w_smooth, float w_len, float* out8, void* stream);
 
 #ifdef __cplusplus
 }

@@ -75,10 +75,10 @@ int ramp_unet_set_scenes(void* handle, const float* latents, int n_scenes, void*
   RAMP_CHECK(handle && latents, "ramp_unet_set_scenes: null argument");
   return ((UnetEngine*)handle)->set_scenes(latents, n_scenes, (cudaStream_t)stream);
 }
-int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, float t, const int32_t* row2scene, float* eps_out,
-                          float* f_out, void* stream) {
+int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, int x_repeat, float t, const int32_t* row2scene,
+                          float* eps_out, float* f_out, void* stream) {
   RAMP_CHECK(handle && x, "ramp_unet_energy_grad: null argument");
-  return ((UnetEngine*)handle)->energy_grad(x, n_rows, t, row2scene, eps_out, f_out, (cudaStream_t)stream);
+  return ((UnetEngine*)handle)->energy_grad(x, n_rows, x_repeat, t, row2scene, eps_out, f_out, (cudaStream_t)stream);
 }
 
 }  // extern "C"

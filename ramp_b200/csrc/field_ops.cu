@@ -1,0 +1,405 @@
+// Point-cloud kernels: exact nearest-point query, artificial-potential-field
+// pushes, trajectory cost terms and best-of-N selection.
+//   nearest point : scipy cKDTree.query(k=1, distance_upper_bound) at APFhelper.py:17-35, APFhelper_dynamic.py:99-105
+//   static APF    : APFhelper.py:37-104          dynamic APF : APFhelper_dynamic.py:107-142
+//   cost terms    : cost.py:3-7,19-54            selection   : cost.py:56-88
+// The reference's "potential field" is a k=1 nearest-neighbour push, so the hot loop is a min/argmin
+// over the cloud per waypoint: FP32-pipe bound.  Cloud tiles are staged in shared memory by TMA bulk
+// copies (double buffered, mbarrier completion); each thread keeps R waypoints in registers and
+// evaluates |p|^2 - 2 q.p with d FFMA per pair plus one 3-input min per two pairs; the argmin is
+// recovered by re-scanning only the winning 64-point chunk, and the returned distance is
+// re-derived exactly (direct form) for the winner.
+#include "../../include/ramp_b200.h"
+#include "common.cuh"
+#include <cfloat>
+
+namespace ramp {
+
+static constexpr int NN_CHUNK = 64;          // argmin recovery granularity (points)
+static constexpr int NN_TILE = 2048;         // points per shared-memory tile (32 KB)
+static constexpr int NN_THREADS = 128;
+
+// cloud [P, d] -> packed float4 (x, y, z|0, |p|^2), padded to a multiple of NN_TILE with +inf norms
+__global__ void nn_pack_kernel(const float* __restrict__ cloud, int P, int dim, int Ppad, float4* __restrict__ out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < Ppad; i += gridDim.x * blockDim.x) {
+    float4 v = make_float4(0.f, 0.f, 0.f, FLT_MAX);
+    if (i < P) {
+      v.x = cloud[(size_t)i * dim]; v.y = cloud[(size_t)i * dim + 1]; v.z = dim == 3 ? cloud[(size_t)i * dim + 2] : 0.f;
+      v.w = v.x * v.x + v.y * v.y + v.z * v.z;
+    }
+    out[i] = v;
+  }
+}
+
+__device__ __forceinline__ float min3f(float a, float b, float c) {
+  float d;
+  asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+__device__ __forceinline__ void nn_mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n.reg .pred p;\nW_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra D_%=;\nbra W_%=;\nD_%=:\n}\n"
+      ::"r"(bar), "r"(parity) : "memory");
+}
+
+template <int DIM>
+__device__ __forceinline__ float nn_key(const float4 p, float mx, float my, float mz) {
+  float k = fmaf(my, p.y, p.w);
+  if (DIM == 3) k = fmaf(mz, p.z, k);
+  return fmaf(mx, p.x, k);
+}
+
+template <int DIM, int R>
+__global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __restrict__ cloud4, int P, int Ppad,
+                                                              const float* __restrict__ q, int Q, int qstride, float thr,
+                                                              float* __restrict__ out_d, int* __restrict__ out_idx) {
+  extern __shared__ __align__(128) unsigned char nn_smem[];
+  float4* tile = reinterpret_cast<float4*>(nn_smem);                       // 2 x NN_TILE
+  __shared__ __align__(8) unsigned long long bars[2];
+  const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&bars[0]);
+  const uint32_t tile0 = (uint32_t)__cvta_generic_to_shared(tile);
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int ntiles = Ppad / NN_TILE;
+  auto issue = [&](int t) {
+    const uint32_t bar = bar0 + 8 * (t & 1);
+    const uint32_t dst = tile0 + (t & 1) * NN_TILE * 16;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(NN_TILE * 16) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(cloud4 + (size_t)t * NN_TILE), "r"(NN_TILE * 16), "r"(bar) : "memory");
+  };
+  if (tid == 0) issue(0);
+
+  float mx[R], my[R], mz[R], best[R];
+  int bchunk[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int qi = (blockIdx.x * R + r) * NN_THREADS + tid;
+    mx[r] = my[r] = mz[r] = 0.f;
+    if (qi < Q) {
+      mx[r] = -2.f * q[(size_t)qi * qstride];
+      my[r] = -2.f * q[(size_t)qi * qstride + 1];
+      if (DIM == 3) mz[r] = -2.f * q[(size_t)qi * qstride + 2];
+    }
+    best[r] = FLT_MAX; bchunk[r] = 0;
+  }
+  for (int t = 0; t < ntiles; ++t) {
+    if (tid == 0 && t + 1 < ntiles) issue(t + 1);
+    nn_mbar_wait(bar0 + 8 * (t & 1), (t >> 1) & 1);
+    const float4* tp = tile + (t & 1) * NN_TILE;
+    for (int c = 0; c < NN_TILE / NN_CHUNK; ++c) {
+      float cm[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) cm[r] = FLT_MAX;
+#pragma unroll 8
+      for (int j = 0; j < NN_CHUNK; j += 2) {
+        const float4 pa = tp[c * NN_CHUNK + j], pb = tp[c * NN_CHUNK + j + 1];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          cm[r] = min3f(cm[r], nn_key<DIM>(pa, mx[r], my[r], mz[r]), nn_key<DIM>(pb, mx[r], my[r], mz[r]));
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (cm[r] < best[r]) { best[r] = cm[r]; bchunk[r] = t * (NN_TILE / NN_CHUNK) + c; }
+    }
+    __syncthreads();
+  }
+  // recover the argmin inside the winning chunk (same FFMA sequence => bit-identical keys), exact distance
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int qi = (blockIdx.x * R + r) * NN_THREADS + tid;
+    if (qi >= Q) continue;
+    const float4* cp = cloud4 + (size_t)bchunk[r] * NN_CHUNK;
+    int arg = 0;
+    for (int j = NN_CHUNK - 1; j >= 0; --j)
+      if (nn_key<DIM>(cp[j], mx[r], my[r], mz[r]) == best[r]) arg = j;     // lowest index wins ties
+    const float4 p = cp[arg];
+    const float dx = q[(size_t)qi * qstride] - p.x, dy = q[(size_t)qi * qstride + 1] - p.y;
+    float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+    if (DIM == 3) { const float dz = q[(size_t)qi * qstride + 2] - p.z; d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
+    const float d = sqrtf(d2);
+    const int gi = bchunk[r] * NN_CHUNK + arg;
+    const bool hit = gi < P && d < thr;
+    out_d[qi] = hit ? d : INFINITY;
+    out_idx[qi] = hit ? gi : P;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// static APF (APFhelper.py:37-104): one CTA per trajectory
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) apf_static_kernel(const float* __restrict__ x, int H, int D, int dim,
+                                                         const float* __restrict__ dist, const int* __restrict__ idx,
+                                                         const float4* __restrict__ cloud4, int P, float thr,
+                                                         float strength, int window, float* __restrict__ out) {
+  __shared__ float fx[128], fy[128], fz[128];
+  const int b = blockIdx.x, t = threadIdx.x;
+  const float* xb = x + (size_t)b * H * D;
+  float px = 0.f, py = 0.f, pz = 0.f;
+  if (t < H) {
+    px = xb[t * D]; py = xb[t * D + 1]; if (dim == 3) pz = xb[t * D + 2];
+    const float d = dist[(size_t)b * H + t];
+    const int id = idx[(size_t)b * H + t];
+    float ax = 0.f, ay = 0.f, az = 0.f;
+    if (d < thr && id < P) {
+      const float4 p = cloud4[id];
+      float dx = px - p.x, dy = py - p.y, dz = dim == 3 ? pz - p.z : 0.f;
+      const float n = sqrtf(dx * dx + dy * dy + dz * dz) + 1e-8f;
+      const float mag = strength * expf(-d / thr);
+      ax = mag * (dx / n); ay = mag * (dy / n); az = mag * (dz / n);
+    }
+    fx[t] = ax; fy[t] = ay; fz[t] = az;
+  }
+  __syncthreads();
+  if (t < H) {
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+    const float inv = (window * 0.5f) * (window * 0.5f);
+    const int lo = max(0, t - window), hi = min(H - 1, t + window);
+    for (int s = lo; s <= hi; ++s) {
+      const int k = t - s;
+      const float w = expf(-0.5f * (float)(k * k) / inv);
+      sx += fx[s] * w; sy += fy[s] * w; sz += fz[s] * w;
+    }
+    float* ob = out + (size_t)b * H * D + (size_t)t * D;
+    ob[0] = px + sx; ob[1] = py + sy;
+    if (dim == 3) ob[2] = pz + sz;
+    for (int c = dim; c < D; ++c) ob[c] = xb[t * D + c];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// dynamic APF (APFhelper_dynamic.py:107-142): per trajectory, in place on the positions
+//   mode 0: push waypoints [c - w, min(H-1, c + w)) around the closest-approach index c
+//   mode 1: push waypoints [0, affected) away from the pursuer disc, mixed 0.9 / 0.1 with the goal direction
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) apf_dynamic_kernel(float* __restrict__ x, int H, int D,
+                                                          const float* __restrict__ dist, const int* __restrict__ idx,
+                                                          const float4* __restrict__ cloud4, int P, int mode, int window,
+                                                          int affected, float strength, float thr_force,
+                                                          const float* __restrict__ goal,
+                                                          const unsigned char* __restrict__ active) {
+  __shared__ float sd[128];
+  __shared__ int si[128];
+  const int b = blockIdx.x, t = threadIdx.x;
+  if (active && !active[b]) return;
+  float* xb = x + (size_t)b * H * D;
+  const int n = mode == 1 ? min(affected, H) : H;
+  sd[t] = (t < n) ? dist[(size_t)b * H + t] : INFINITY;
+  si[t] = t;
+  __syncthreads();
+  int lo = 0, hi = n;
+  if (mode == 0) {
+    for (int o = 64; o > 0; o >>= 1) {          // first index of the minimum (np.argmin)
+      if (t < o) {
+        const float a = sd[t], c = sd[t + o];
+        if (c < a || (c == a && si[t + o] < si[t])) { sd[t] = c; si[t] = si[t + o]; }
+      }
+      __syncthreads();
+    }
+    const int c = si[0];
+    lo = max(0, c - window); hi = min(H - 1, c + window);
+  }
+  if (t >= lo && t < hi) {
+    const int id = idx[(size_t)b * H + t];
+    if (id < P) {
+      const float d = dist[(size_t)b * H + t];
+      const float4 p = cloud4[id];
+      const float qx = xb[t * D], qy = xb[t * D + 1];
+      float ax = qx - p.x, ay = qy - p.y;
+      const float an = sqrtf(ax * ax + ay * ay) + 1e-8f;
+      ax /= an; ay /= an;
+      if (goal) {
+        float gx = goal[0] - qx, gy = goal[1] - qy;
+        const float gn = sqrtf(gx * gx + gy * gy) + 1e-8f;
+        gx /= gn; gy /= gn;
+        ax = 0.9f * ax + 0.1f * gx; ay = 0.9f * ay + 0.1f * gy;
+        const float cn = sqrtf(ax * ax + ay * ay) + 1e-8f;
+        ax /= cn; ay /= cn;
+      }
+      const float force = strength * expf(-d / thr_force);
+      xb[t * D] = qx + force * ax;
+      xb[t * D + 1] = qy + force * ay;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// cost terms (cost.py:3-7,19-54): one warp per trajectory
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) cost_terms_kernel(const float* __restrict__ x, int B, int H, int D, int dim,
+                                                         const float* __restrict__ dist, float thr,
+                                                         float* __restrict__ out /* [B,3]: free, length, smoothness */) {
+  const int b = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (b >= B) return;
+  const float* xb = x + (size_t)b * H * D;
+  float len = 0.f, sm = 0.f;
+  int hit = 0;
+  for (int t = lane; t < H; t += 32) {
+    if (dist[(size_t)b * H + t] < thr) hit = 1;
+    if (t + 1 < H) {
+      float a = 0.f, v = 0.f;
+      for (int c = 0; c < dim; ++c) { const float d = xb[(t + 1) * D + c] - xb[t * D + c]; a += d * d; }
+      for (int c = dim; c < D; ++c) { const float d = xb[(t + 1) * D + c] - xb[t * D + c]; v += d * d; }
+      len += sqrtf(a); sm += sqrtf(v);
+    }
+  }
+  len = warp_sum(len); sm = warp_sum(sm);
+  hit = __any_sync(0xffffffffu, hit);
+  if (lane == 0) { out[b * 3] = hit ? 0.f : 1.f; out[b * 3 + 1] = len; out[b * 3 + 2] = sm; }
+}
+
+// selection (cost.py:56-88) over n gathered trajectories: min-max normalise over survivors, weighted sum, argmin
+__global__ void __launch_bounds__(1024) select_best_kernel(const float* __restrict__ terms, int n, float w_smooth,
+                                                           float w_len, float* __restrict__ out /* [8] */) {
+  __shared__ float s0[1024], s1[1024], s2[1024], s3[1024];
+  __shared__ int si[1024];
+  const int t = threadIdx.x;
+  float lmin = INFINITY, lmax = -INFINITY, smin = INFINITY, smax = -INFINITY;
+  int cnt = 0;
+  for (int i = t; i < n; i += 1024)
+    if (terms[i * 3] != 0.f) {
+      const float l = terms[i * 3 + 1], s = terms[i * 3 + 2];
+      lmin = fminf(lmin, l); lmax = fmaxf(lmax, l); smin = fminf(smin, s); smax = fmaxf(smax, s); ++cnt;
+    }
+  s0[t] = lmin; s1[t] = lmax; s2[t] = smin; s3[t] = smax; si[t] = cnt;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if (t < o) {
+      s0[t] = fminf(s0[t], s0[t + o]); s1[t] = fmaxf(s1[t], s1[t + o]);
+      s2[t] = fminf(s2[t], s2[t + o]); s3[t] = fmaxf(s3[t], s3[t + o]); si[t] += si[t + o];
+    }
+    __syncthreads();
+  }
+  lmin = s0[0]; lmax = s1[0]; smin = s2[0]; smax = s3[0];
+  const int n_free = si[0];
+  __syncthreads();
+  // cost = w_s * (s - smin)/(smax - smin) + w_l * (l - lmin)/(lmax - lmin); 0/0 = NaN as in the reference.
+  float best = INFINITY; int bi = -1; bool bnan = false;
+  for (int i = t; i < n; i += 1024)
+    if (terms[i * 3] != 0.f) {
+      const float c = w_smooth * ((terms[i * 3 + 2] - smin) / (smax - smin)) + w_len * ((terms[i * 3 + 1] - lmin) / (lmax - lmin));
+      const bool cn = c != c;
+      if (bi < 0 || (cn && !bnan) || (!bnan && c < best)) { best = c; bi = i; bnan = cn; }
+    }
+  s0[t] = best; si[t] = bi; s1[t] = bnan ? 1.f : 0.f;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if (t < o) {
+      const int ia = si[t], ib = si[t + o];
+      const bool na = s1[t] != 0.f, nb = s1[t + o] != 0.f;
+      bool take = false;
+      if (ib >= 0) {
+        if (ia < 0) take = true;
+        else if (na != nb) take = nb;                       // NaN sorts first (torch.argmin propagates NaN)
+        else if (na) take = ib < ia;
+        else take = s0[t + o] < s0[t] || (s0[t + o] == s0[t] && ib < ia);
+      }
+      if (take) { s0[t] = s0[t + o]; si[t] = ib; s1[t] = s1[t + o]; }
+    }
+    __syncthreads();
+  }
+  if (t == 0) {
+    out[0] = (float)si[0]; out[1] = s0[0]; out[2] = (float)n_free; out[3] = lmin; out[4] = lmax; out[5] = smin; out[6] = smax;
+    out[7] = 0.f;
+  }
+}
+
+}  // namespace ramp
+
+using namespace ramp;
+
+template <int DIM, int R>
+static int nn_launch(const float4* c4, int P, int Ppad, const float* q, int Q, int qstride, float thr, float* od, int* oi,
+                     cudaStream_t s) {
+  static bool attr = false;
+  const int smem = 2 * NN_TILE * 16;
+  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(nn_query_kernel<DIM, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
+  const int per = NN_THREADS * R;
+  nn_query_kernel<DIM, R><<<(Q + per - 1) / per, NN_THREADS, smem, s>>>(c4, P, Ppad, q, Q, qstride, thr, od, oi);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" {
+
+size_t ramp_cloud_packed_points(int P) { return (size_t)((P + NN_TILE - 1) / NN_TILE) * NN_TILE; }
+
+int ramp_cloud_pack(const float* cloud, int P, int dim, void* packed, void* stream) {
+  RAMP_CHECK(cloud && packed, "ramp_cloud_pack: null argument");
+  RAMP_CHECK(dim == 2 || dim == 3, "ramp_cloud_pack: dim must be 2 or 3");
+  RAMP_CHECK(P >= 1, "ramp_cloud_pack: empty cloud");
+  const int Ppad = (int)ramp_cloud_packed_points(P);
+  nn_pack_kernel<<<(Ppad + 255) / 256, 256, 0, (cudaStream_t)stream>>>(cloud, P, dim, Ppad, (float4*)packed);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int qstride, float upper_bound,
+                  float* out_dist, int32_t* out_idx, void* stream) {
+  RAMP_CHECK(packed && q && out_dist && out_idx, "ramp_nn_query: null argument");
+  RAMP_CHECK(dim == 2 || dim == 3, "ramp_nn_query: dim must be 2 or 3");
+  if (Q == 0) return 0;
+  const int Ppad = (int)ramp_cloud_packed_points(P);
+  const float4* c4 = (const float4*)packed;
+  cudaStream_t s = (cudaStream_t)stream;
+  // registers-per-thread blocking: as many waypoints per thread as still leaves >= 2 CTAs per SM
+  const long ctas8 = ((long)Q + NN_THREADS * 8 - 1) / (NN_THREADS * 8);
+  int R = ctas8 >= 296 ? 8 : (ctas8 * 2 >= 296 ? 4 : (ctas8 * 4 >= 296 ? 2 : 1));
+  if (dim == 2) {
+    if (R == 8) return nn_launch<2, 8>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+    if (R == 4) return nn_launch<2, 4>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+    if (R == 2) return nn_launch<2, 2>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+    return nn_launch<2, 1>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+  }
+  if (R == 8) return nn_launch<3, 8>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+  if (R == 4) return nn_launch<3, 4>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+  if (R == 2) return nn_launch<3, 2>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+  return nn_launch<3, 1>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+}
+
+int ramp_apf_static(const float* x, int B, int H, int D, int dim, const float* dist, const int32_t* idx,
+                    const void* packed, int P, float thr, float strength, int window, float* out, void* stream) {
+  RAMP_CHECK(x && dist && idx && packed && out, "ramp_apf_static: null argument");
+  RAMP_CHECK(H <= 128, "ramp_apf_static: horizon must be <= 128");
+  if (B == 0) return 0;
+  apf_static_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(x, H, D, dim, dist, idx, (const float4*)packed, P, thr, strength,
+                                                         window, out);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ramp_apf_dynamic(float* x, int B, int H, int D, const float* dist, const int32_t* idx, const void* packed, int P,
+                     int mode, int window, int affected, float strength, float thr_force, const float* goal,
+                     const unsigned char* active, void* stream) {
+  RAMP_CHECK(x && dist && idx && packed, "ramp_apf_dynamic: null argument");
+  RAMP_CHECK(H <= 128, "ramp_apf_dynamic: horizon must be <= 128");
+  RAMP_CHECK(mode == 0 || mode == 1, "ramp_apf_dynamic: mode must be 0 (static) or 1 (pursuer)");
+  if (B == 0) return 0;
+  apf_dynamic_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(x, H, D, dist, idx, (const float4*)packed, P, mode, window,
+                                                          affected, strength, thr_force, goal, active);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ramp_cost_terms(const float* x, int B, int H, int D, int dim, const float* dist, float thr, float* terms,
+                    void* stream) {
+  RAMP_CHECK(x && dist && terms, "ramp_cost_terms: null argument");
+  if (B == 0) return 0;
+  cost_terms_kernel<<<(B + 7) / 8, 256, 0, (cudaStream_t)stream>>>(x, B, H, D, dim, dist, thr, terms);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ramp_select_best(const float* terms, int n, float w_smooth, float w_len, float* out8, void* stream) {
+  RAMP_CHECK(terms && out8, "ramp_select_best: null argument");
+  select_best_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(terms, n, w_smooth, w_len, out8);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,186 @@
+// Fused per-step sampler kernels: score combine (CFG / compositional) -> x0 ->
+// clamp -> posterior mean or DDIM update -> noise -> inpainting, one launch per step.
+// Arithmetic order mirrors the reference's fp32 tensor expressions and uses explicit round-to-nearest
+// mul/add/sub intrinsics (no FMA contraction): at t = T-1 of the 25-step exponential schedule x0 is
+// 4602.7 * (x - eps) before the clamp, so a fused multiply-add would already differ from torch.
+//   combine  : diffusion_model_static.py:161-165,213-216; diffusion_model_dynamic.py:157-160; diffusion_model_3d.py:150,169-172
+//   x0/clamp : diffusion_model_static.py:109-118,167-169
+//   DDPM     : diffusion_model_static.py:120-127 (q_posterior); sample_functions.py:32-48
+//   DDIM     : diffusion_model_static.py:321-332
+//   inpaint  : sample_functions.py:5-10; diffusion_model_dynamic.py:562-566,582-587
+//   q_sample : diffusion_model_dynamic.py:671-680
+#include "../../include/ramp_b200.h"
+#include "common.cuh"
+
+namespace ramp {
+
+struct StepArgs {
+  const float* x;        // [B, H, D]
+  const float* eps;      // network rows; row of (b, g) = b * eps_bstride + g * eps_gstride, g == G is the unconditional row
+  long eps_bstride, eps_gstride;
+  int B, H, D, G;
+  float w[8];            // guidance weights
+  float sqrt_recip, sqrt_recipm1;
+  // DDPM
+  float coef1, coef2, sigma, noise_scale;
+  const float* noise;    // [B, H, D] or null (t == 0)
+  // DDIM
+  float sa_t, sb_t, sa_prev, sdir;
+  // inpainting: waypoint h is overwritten by pin_val[b * pin_bstride + h * D + :] when pin_mask[h] != 0
+  const unsigned char* pin_mask; const float* pin_val; long pin_bstride;
+  float* out;            // x_{t-1} (may alias x)
+  float* x0_out;         // optional clamped x0
+  float* eps_out;        // optional combined eps
+  int mode;              // 0 = DDPM step, 1 = DDIM step, 2 = x0 only
+  int predict_epsilon;
+};
+
+__device__ __forceinline__ float combine_eps(const StepArgs& a, int b, size_t inner) {
+  const float* e = a.eps + (size_t)b * a.eps_bstride * ((size_t)a.H * a.D) + inner;
+  const size_t gs = (size_t)a.eps_gstride * a.H * a.D;
+  const float eu = e[(size_t)a.G * gs];
+  if (a.G == 1) {
+    // (1 + w) * cond - w * uncond
+    return __fsub_rn(__fmul_rn(__fadd_rn(1.f, a.w[0]), e[0]), __fmul_rn(a.w[0], eu));
+  }
+  float acc = eu;   // uncond + sum_g w_g * (cond_g - uncond), left to right
+  for (int g = 0; g < a.G; ++g) acc = __fadd_rn(acc, __fmul_rn(a.w[g], __fsub_rn(e[(size_t)g * gs], eu)));
+  return acc;
+}
+
+__global__ void __launch_bounds__(256) step_kernel(StepArgs a) {
+  const size_t hd = (size_t)a.H * a.D;
+  const size_t total = (size_t)a.B * hd;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / hd);
+    const size_t inner = i - (size_t)b * hd;
+    const int h = (int)(inner / a.D);
+    const float x = a.x[i];
+    const float e = combine_eps(a, b, inner);
+    float x0 = a.predict_epsilon ? __fsub_rn(__fmul_rn(a.sqrt_recip, x), __fmul_rn(a.sqrt_recipm1, e)) : e;
+    x0 = fminf(fmaxf(x0, -1.f), 1.f);
+    if (a.eps_out) a.eps_out[i] = e;
+    if (a.x0_out) a.x0_out[i] = x0;
+    if (a.mode == 2) continue;
+    float r;
+    if (a.mode == 0) {
+      r = __fadd_rn(__fmul_rn(a.coef1, x0), __fmul_rn(a.coef2, x));
+      if (a.noise) r = __fadd_rn(r, __fmul_rn(__fmul_rn(a.sigma, a.noise[i]), a.noise_scale));
+    } else {
+      const float mo = __fdiv_rn(__fsub_rn(x, __fmul_rn(a.sa_t, x0)), a.sb_t);
+      r = __fadd_rn(__fmul_rn(a.sa_prev, x0), __fmul_rn(a.sdir, mo));
+    }
+    if (a.pin_mask && a.pin_mask[h]) r = a.pin_val[(size_t)b * a.pin_bstride + inner];
+    a.out[i] = r;
+  }
+}
+
+// second half of a DDIM step when the APF ran between x0 and the update (x0 is read back from memory)
+struct DdimUpdArgs {
+  const float* x; const float* x0; int B, H, D; float sa_t, sb_t, sa_prev, sdir;
+  const unsigned char* pin_mask; const float* pin_val; long pin_bstride; float* out;
+};
+__global__ void __launch_bounds__(256) ddim_update_kernel(DdimUpdArgs a) {
+  const size_t hd = (size_t)a.H * a.D, total = (size_t)a.B * hd;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / hd);
+    const size_t inner = i - (size_t)b * hd;
+    const int h = (int)(inner / a.D);
+    const float x = a.x[i], x0 = a.x0[i];
+    const float mo = __fdiv_rn(__fsub_rn(x, __fmul_rn(a.sa_t, x0)), a.sb_t);
+    float r = __fadd_rn(__fmul_rn(a.sa_prev, x0), __fmul_rn(a.sdir, mo));
+    if (a.pin_mask && a.pin_mask[h]) r = a.pin_val[(size_t)b * a.pin_bstride + inner];
+    a.out[i] = r;
+  }
+}
+
+__global__ void __launch_bounds__(256) inpaint_kernel(float* x, int B, int H, int D, const unsigned char* pin_mask,
+                                                      const float* pin_val, long pin_bstride) {
+  const size_t hd = (size_t)H * D, total = (size_t)B * hd;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / hd);
+    const size_t inner = i - (size_t)b * hd;
+    if (pin_mask[inner / D]) x[i] = pin_val[(size_t)b * pin_bstride + inner];
+  }
+}
+
+// x_t = sqrt(abar) * x0[b or broadcast] + sqrt(1 - abar) * noise, then inpaint
+__global__ void __launch_bounds__(256) q_sample_kernel(const float* x0, long x0_bstride, const float* noise, int B, int H,
+                                                       int D, float sa, float sb, const unsigned char* pin_mask,
+                                                       const float* pin_val, long pin_bstride, float* out) {
+  const size_t hd = (size_t)H * D, total = (size_t)B * hd;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / hd);
+    const size_t inner = i - (size_t)b * hd;
+    float r = __fadd_rn(__fmul_rn(sa, x0[(size_t)b * x0_bstride + inner]), __fmul_rn(sb, noise[i]));
+    if (pin_mask && pin_mask[inner / D]) r = pin_val[(size_t)b * pin_bstride + inner];
+    out[i] = r;
+  }
+}
+
+static int ew_grid(size_t total) {
+  size_t b = (total + 255) / 256;
+  return (int)(b > 148 * 8 ? 148 * 8 : (b ? b : 1));
+}
+
+}  // namespace ramp
+
+using namespace ramp;
+
+extern "C" {
+
+int ramp_step(const ramp_step_args* u, void* stream) {
+  RAMP_CHECK(u && u->x && u->eps && (u->out || u->mode == 2), "ramp_step: null argument");
+  RAMP_CHECK(u->G >= 1 && u->G <= 8, "ramp_step: 1..8 conditional groups");
+  RAMP_CHECK(u->mode >= 0 && u->mode <= 2, "ramp_step: mode must be 0 (ddpm), 1 (ddim) or 2 (x0 only)");
+  StepArgs a{};
+  a.x = u->x; a.eps = u->eps; a.eps_bstride = u->eps_bstride; a.eps_gstride = u->eps_gstride;
+  a.B = u->B; a.H = u->H; a.D = u->D; a.G = u->G;
+  for (int g = 0; g < 8; ++g) a.w[g] = u->w[g];
+  a.sqrt_recip = u->sqrt_recip; a.sqrt_recipm1 = u->sqrt_recipm1;
+  a.coef1 = u->coef1; a.coef2 = u->coef2; a.sigma = u->sigma; a.noise_scale = u->noise_scale; a.noise = u->noise;
+  a.sa_t = u->sa_t; a.sb_t = u->sb_t; a.sa_prev = u->sa_prev; a.sdir = u->sdir;
+  a.pin_mask = u->pin_mask; a.pin_val = u->pin_val; a.pin_bstride = u->pin_bstride;
+  a.out = u->out; a.x0_out = u->x0_out; a.eps_out = u->eps_out; a.mode = u->mode; a.predict_epsilon = u->predict_epsilon;
+  const size_t total = (size_t)a.B * a.H * a.D;
+  if (!total) return 0;
+  step_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(a);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ramp_ddim_update(const float* x, const float* x0, int B, int H, int D, float sa_t, float sb_t, float sa_prev,
+                     float sdir, const unsigned char* pin_mask, const float* pin_val, long pin_bstride, float* out,
+                     void* stream) {
+  RAMP_CHECK(x && x0 && out, "ramp_ddim_update: null argument");
+  DdimUpdArgs a{x, x0, B, H, D, sa_t, sb_t, sa_prev, sdir, pin_mask, pin_val, pin_bstride, out};
+  const size_t total = (size_t)B * H * D;
+  if (!total) return 0;
+  ddim_update_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(a);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ramp_inpaint(float* x, int B, int H, int D, const unsigned char* pin_mask, const float* pin_val, long pin_bstride,
+                 void* stream) {
+  RAMP_CHECK(x && pin_mask && pin_val, "ramp_inpaint: null argument");
+  const size_t total = (size_t)B * H * D;
+  if (!total) return 0;
+  inpaint_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(x, B, H, D, pin_mask, pin_val, pin_bstride);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int ramp_q_sample(const float* x0, long x0_bstride, const float* noise, int B, int H, int D, float sqrt_ac,
+                  float sqrt_1mac, const unsigned char* pin_mask, const float* pin_val, long pin_bstride, float* out,
+                  void* stream) {
+  RAMP_CHECK(x0 && noise && out, "ramp_q_sample: null argument");
+  const size_t total = (size_t)B * H * D;
+  if (!total) return 0;
+  q_sample_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(x0, x0_bstride, noise, B, H, D, sqrt_ac, sqrt_1mac,
+                                                                     pin_mask, pin_val, pin_bstride, out);
+  RAMP_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -260,7 +260,7 @@ int UnetEngine::finalize(cudaStream_t s) {
 
   // size the workspace with a dry run at max_rows
   dry_ = true; arena_off_ = 0;
-  rc = run(nullptr, cfg_.max_rows, 0.f, nullptr, nullptr, nullptr, s);
+  rc = run(nullptr, cfg_.max_rows, 1, 0.f, nullptr, nullptr, nullptr, s);
   dry_ = false;
   if (rc) return rc;
   arena_bytes_ = arena_off_ + 256;
@@ -277,13 +277,13 @@ int UnetEngine::set_scenes(const float* latents_dev, int n_scenes, cudaStream_t 
   return scene_constants((const SceneBlock*)scene_blocks_dev_, 16, latents_dev, n_scenes, cfg_.ctx_dim, s);
 }
 
-int UnetEngine::energy_grad(const float* x, int n_rows, float t, const int* row2scene, float* eps_out, float* f_out,
-                            cudaStream_t s) {
+int UnetEngine::energy_grad(const float* x, int n_rows, int x_repeat, float t, const int* row2scene, float* eps_out,
+                            float* f_out, cudaStream_t s) {
   RAMP_CHECK(finalized_, "energy_grad before finalize");
   RAMP_CHECK(n_scenes_ > 0, "energy_grad before set_scenes");
   RAMP_CHECK(n_rows >= 1 && n_rows <= cfg_.max_rows, "n_rows exceeds max_rows of this engine");
   arena_off_ = 0;
-  return run(x, n_rows, t, row2scene, eps_out, f_out, s);
+  return run(x, n_rows, x_repeat, t, row2scene, eps_out, f_out, s);
 }
 
 }  // namespace ramp

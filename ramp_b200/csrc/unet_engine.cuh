@@ -50,8 +50,8 @@ class UnetEngine {
   int finalize(cudaStream_t s);
   int set_scenes(const float* latents_dev, int n_scenes, cudaStream_t s);
   // eps_out / f_out: [n_rows, H, D] (either may be null)
-  int energy_grad(const float* x, int n_rows, float t, const int* row2scene, float* eps_out, float* f_out,
-                  cudaStream_t s);
+  int energy_grad(const float* x, int n_rows, int x_repeat, float t, const int* row2scene, float* eps_out,
+                  float* f_out, cudaStream_t s);
   size_t workspace_bytes() const { return arena_bytes_; }
   const UnetConfig& cfg() const { return cfg_; }
 
@@ -98,7 +98,8 @@ class UnetEngine {
     bf16* hi = nullptr; bf16* lo = nullptr; int lds = 0;   // external split destination (e.g. concat buffer), or
     bool want_s = true;                                       // allocate a private one
   };
-  int run(const float* x, int n_rows, float t, const int* row2scene, float* eps_out, float* f_out, cudaStream_t s);
+  int run(const float* x, int n_rows, int x_repeat, float t, const int* row2scene, float* eps_out, float* f_out,
+          cudaStream_t s);
   int gemm(const Act& a, int K, const PackedW& w, const GemmTap* taps, int ntaps, int L_in, int L_out, int pstride,
            const float* bias, const float* bias_tab, const float* res, int ldr, const float* res2, int ldr2,
            float* of, int ldo, bf16* oh, bf16* ol, int lds, int o_L, int o_stride, int o_off);

@@ -13,22 +13,23 @@ static __device__ __forceinline__ void store_split(bf16* hi, bf16* lo, size_t id
 }
 
 // ------------------------------------------------------------------------------------------------
-__global__ void prep_input_kernel(const float* __restrict__ x, int n_samples, int n_pad, int L, int D, bf16* hi,
+__global__ void prep_input_kernel(const float* __restrict__ x, int n_samples, int n_pad, int L, int D, int rep, bf16* hi,
                                   bf16* lo) {
   const size_t total = (size_t)n_pad * L * 16;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int c = (int)(i & 15);
     const size_t row = i >> 4;
     const size_t n = row / L;
-    float v = (c < D && n < (size_t)n_samples) ? x[row * D + c] : 0.f;
+    const size_t l = row - n * L;
+    float v = (c < D && n < (size_t)n_samples) ? x[((n / rep) * L + l) * D + c] : 0.f;
     store_split(hi, lo, i, v);
   }
 }
-int prep_input(const float* x, int n_samples, int n_pad, int L, int D, bf16* hi, bf16* lo, cudaStream_t s) {
+int prep_input(const float* x, int n_samples, int n_pad, int L, int D, int x_repeat, bf16* hi, bf16* lo, cudaStream_t s) {
   const size_t total = (size_t)n_pad * L * 16;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  prep_input_kernel<<<blocks, 256, 0, s>>>(x, n_samples, n_pad, L, D, hi, lo);
+  prep_input_kernel<<<blocks, 256, 0, s>>>(x, n_samples, n_pad, L, D, x_repeat < 1 ? 1 : x_repeat, hi, lo);
   RAMP_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -6,8 +6,8 @@
 
 namespace ramp {
 
-// x [n_samples, L, D] fp32 -> hi/lo planes [n_samples_pad, L, 16] (channels >= D and samples >= n zero)
-int prep_input(const float* x, int n_samples, int n_pad, int L, int D, bf16* hi, bf16* lo, cudaStream_t s);
+// x [ceil(n_samples / x_repeat), L, D] fp32 (row n reads source row n / x_repeat) -> hi/lo planes [n_samples_pad, L, 16] (channels >= D and samples >= n zero)
+int prep_input(const float* x, int n_samples, int n_pad, int L, int D, int x_repeat, bf16* hi, bf16* lo, cudaStream_t s);
 
 // GroupNorm(8 groups) [+ Mish] [+ cond[C]] [+ add]  (layers.py:280-297, layers_attention_mini.py:77-80)
 struct GnArgs {

@@ -237,8 +237,8 @@ int UnetEngine::st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act
 }
 
 // forward_no_energy + EnergyGradFunction (UnetInference.py:19-37,176-224)
-int UnetEngine::run(const float* x, int n_rows, float t, const int* row2scene, float* eps_out, float* f_out,
-                    cudaStream_t s) {
+int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int* row2scene, float* eps_out,
+                    float* f_out, cudaStream_t s) {
   const int H = cfg_.horizon, D = cfg_.state_dim;
   n_ = n_rows; npad_ = (n_rows + 15) / 16 * 16; s_ = s;
   int* r2s = (int*)alloc_bytes((size_t)npad_ * sizeof(int));
@@ -249,7 +249,7 @@ int UnetEngine::run(const float* x, int n_rows, float t, const int* row2scene, f
     TRY(time_cond(time_w_, t, (const CondBlock*)cond_blocks_dev_, 16, s));
   }
   Split xin = allocs((size_t)npad_ * H * 16);
-  if (!dry_) TRY(prep_input(x, n_rows, npad_, H, D, xin.hi, xin.lo, s));
+  if (!dry_) TRY(prep_input(x, n_rows, npad_, H, D, x_repeat, xin.hi, xin.lo, s));
   // concat buffers of the up path: cat[j] = [prev | skip], ld = 2*Cc, at L = H/8 << j
   Split cat[3];
   for (int j = 0; j < 3; ++j) cat[j] = allocs((size_t)npad_ * ((H / 8) << j) * (512 >> j));

@@ -1,0 +1,39 @@
+"""Drop-in for mpd/models/diffusion_models/sample_functions.py (and the names the scripts import from
+sample_functionsdynamic.py).  `ddpm_sample_fn` keeps the reference signature; the per-step arithmetic
+(score combine -> x0 -> clamp -> posterior mean -> noise) is one fused CUDA kernel (ramp_step)."""
+import torch
+
+from . import ops
+
+
+def apply_hard_conditioning(x, conditions):
+    """sample_functions.py:5-10 — in place, on the device (ramp_inpaint)."""
+    if not conditions:
+        return x
+    B, H, D = x.shape
+    return ops.inpaint(x, ops.Pins.from_hard_conds(conditions, B, H, D, x.device))
+
+
+def extract(a, t, x_shape):
+    """sample_functions.py:13-16."""
+    b, *_ = t.shape
+    out = a.gather(-1, t)
+    return out.reshape(b, *((1,) * (len(x_shape) - 1)))
+
+
+@torch.no_grad()
+def ddpm_sample_fn(model, x, hard_conds, context, t, traj_normalized=None, obstacle_pts=None, forward_t=None,
+                   compose=None, noise_std_extra_schedule_fn=None, **kwargs):
+    """sample_functions.py:19-48.  Returns (x_{t-1}, None).  The noise draw is `torch.randn_like(x)`
+    exactly where the reference draws it, so a patched RNG reproduces the same tape."""
+    t_single = int(t[0])
+    ti = max(t_single, 0)
+    noise = torch.randn_like(x)
+    noise_std = 1.0 if noise_std_extra_schedule_fn is None else float(noise_std_extra_schedule_fn(t_single))
+    out = model._ddpm_step(x, ti, obstacle_pts, noise if ti > 0 else None, noise_std, compose=bool(compose))
+    return out, None
+
+
+def guide_gradient_steps(x, hard_conds=None, guide=None, **kwargs):
+    """sample_functionsdynamic.py:280-291 — the scripts pass guide=None; x is returned unchanged."""
+    return x

@@ -208,19 +208,19 @@ class TemporalUnetInference(nn.Module):
                                          ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "ramp_unet_set_scenes")
         self._scene_key = object()
 
-    def energy_grad_rows(self, x, t, row2scene, out=None, want_f=False):
+    def energy_grad_rows(self, x, t, row2scene, out=None, want_f=False, x_repeat=1):
         """eps for rows x [N,H,D] at scalar timestep t, row i conditioned on scene row2scene[i]."""
         if self._engine is None or self._scene_key is None:
             raise RampError("call set_scene_latents() first")
-        N = x.shape[0]
         x = x.detach().to(torch.float32).contiguous()
-        eps = torch.empty_like(x) if out is None else out
-        f = torch.empty_like(x) if want_f else None
-        step = self.max_rows
+        N = x.shape[0] * x_repeat
+        eps = torch.empty((N,) + tuple(x.shape[1:]), device=x.device) if out is None else out
+        f = torch.empty_like(eps) if want_f else None
+        step = self.max_rows - self.max_rows % x_repeat
         st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
         for s in range(0, N, step):
             n = min(step, N - s)
-            check(lib().ramp_unet_energy_grad(self._engine, ptr(x[s:s + n]), n, ctypes.c_float(float(t)),
+            check(lib().ramp_unet_energy_grad(self._engine, ptr(x[s // x_repeat:]), n, x_repeat, ctypes.c_float(float(t)),
                                               ptr(row2scene[s:s + n]), ptr(eps[s:s + n]),
                                               ptr(f[s:s + n]) if want_f else ctypes.c_void_p(0), st),
                   "ramp_unet_energy_grad")
