@@ -104,6 +104,7 @@ class TemporalUnetInference(nn.Module):
         self.conditioning_type = conditioning_type
         self.depth_attn = 2
         self.precision, self.max_rows, self.max_scenes = precision, max_rows, max_scenes
+        self.max_rows_cap = max_rows     # rows per engine call never exceed this; larger batches are chunked
 
         dims = [state_dim] + [unet_input_dim * m for m in dim_mults]
         in_out = list(zip(dims[:-1], dims[1:]))
