@@ -1,0 +1,195 @@
+#!/usr/bin/env python
+"""Benchmark of the RAMP reverse-diffusion planning hot path on B200.
+
+  python bench.py --gpus N --steps K --warmup W        # this repo's CUDA path (one rank per GPU under torchrun)
+  python bench.py --impl reference ...                 # the reference algorithm on the host CPU (oracle port)
+
+A "step" is one complete 25-step reverse-diffusion sampling of one batch of trajectories.
+Workload at N = 1 (BASELINE.json configs[1]): Maze2D compositional energy — scores summed over 6
+obstacle-condition groups + the unconditional branch (7 network rows per trajectory), batch 1024,
+H = 64, D = 4, 25 DDPM steps, random-init weights, synthetic clouds.  Under torchrun every rank runs the
+same per-GPU batch (weak scaling); the only collective is the all-gather of per-trajectory cost terms
+followed by best-of-N selection.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, D, T, G, B_PER_GPU = 64, 4, 25, 6, 1024
+F_ROW = 1.93e9            # algorithmic GEMM-like FLOPs per network row per evaluation, fwd + input-bwd
+WORKLOAD = "maze2d_compose6_b1024_h64_t25_ddpm"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["bf16_tflops_sustained"]), float(p["hbm_gbs"]), "measured"
+    except Exception:
+        return 1400.0, 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def build_model(device, max_rows):
+    from ramp_b200.diffusion import StaticGaussianDiffusionModel
+    from ramp_b200.testing import synthetic_state_dict
+    from ramp_b200.unet import TemporalUnetInference
+    net = TemporalUnetInference(n_support_points=H, state_dim=D, max_rows=max_rows, max_scenes=G + 1)
+    model = StaticGaussianDiffusionModel(model=net, n_diffusion_steps=T, predict_epsilon=True, compose=True)
+    model.load_state_dict(synthetic_state_dict(model, 0))   # random-init weights, non-zero proj_out
+    model.ddim = False                                       # the 25-step DDPM p_sample_loop named by north_star
+    return model.to(device).eval()
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from ramp_b200 import ops
+    from ramp_b200._lib import lib
+    from ramp_b200.sample_functions import ddpm_sample_fn
+    from ramp_b200.testing import synthetic_cloud_2d
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B = args.batch
+    model = build_model(dev, max_rows=args.max_rows)
+    groups_host = synthetic_cloud_2d(seed=5, groups=G).pin_memory()                # [6, 6, 64, 2]
+    hc_host = {0: torch.tensor([-0.8, -0.8, 0.0, 0.0]).pin_memory(), H - 1: torch.tensor([0.8, 0.8, 0.0, 0.0]).pin_memory()}
+    groups = groups_host.to(dev)
+    hc = {k: v.to(dev) for k, v in hc_host.items()}
+    cost_cloud = ops.CloudIndex(groups.reshape(-1, 2))
+    out_host = torch.empty(B, H, D).pin_memory()
+    zeros_traj = torch.zeros(H, D, device=dev)
+    lib().ramp_launch_count.restype = __import__("ctypes").c_ulonglong
+
+    def select(final):
+        terms = ops.cost_terms(final.contiguous(), cost_cloud, 0.05)
+        if world > 1:
+            allt = torch.empty(world * B, 3, device=dev)
+            dist.all_gather_into_tensor(allt, terms)
+            terms = allt
+        return ops.select_best(terms)
+
+    def resident_step():
+        chain = model.run_inference(None, hc, n_samples=B, horizon=H, return_chain=True, traj_normalized=zeros_traj,
+                                    obstacle_pts=groups, sample_fn=ddpm_sample_fn,
+                                    noise_std_extra_schedule_fn=lambda t: 0.5)
+        return select(chain[-1])
+
+    def e2e_step():
+        g = groups_host.to(dev, non_blocking=True)
+        h = {k: v.to(dev, non_blocking=True) for k, v in hc_host.items()}
+        chain = model.run_inference(None, h, n_samples=B, horizon=H, return_chain=True, traj_normalized=zeros_traj,
+                                    obstacle_pts=g, sample_fn=ddpm_sample_fn, noise_std_extra_schedule_fn=lambda t: 0.5)
+        sel = select(chain[-1])
+        out_host.copy_(chain[-1], non_blocking=True)
+        best = sel.cpu()                       # device -> host read of the step's result (synchronises)
+        return best
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    for _ in range(max(args.warmup, 3)):
+        resident_step()
+    sampler = ClockSampler(local)
+    sampler.start()
+    n0 = int(lib().ramp_launch_count())
+    ms = timed(resident_step, args.steps)
+    launches = int(lib().ramp_launch_count()) - n0
+    e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+    sampler.stop_flag = True
+    # per-kernel-class device time of one more identical step (CUDA events around every engine launch)
+    model.model.profile(True)
+    resident_step()
+    prof_ms, prof_n = model.model.profile(False, fetch=True)
+    sampler.join(timeout=2)
+
+    if rank == 0:
+        peak_tf, peak_bw, how = peaks()
+        rows_per_step = B * (G + 1) * T
+        gemm_flops = rows_per_step * F_ROW
+        achieved = gemm_flops / (prof_ms["gemm"] * 1e-3) / 1e12 if prof_ms["gemm"] > 0 else 0.0
+        total_prof = sum(prof_ms.values())
+        line = {
+            "metric": "trajectories/sec (H=64, 25 steps)", "value": world * B * args.steps / (ms * 1e-3),
+            "unit": "trajectories/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 (split-bf16 x3 tensor-core products, fp32 accumulate)", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "trajectories_per_gpu": B, "horizon": H, "state_dim": D,
+                       "diffusion_steps": T, "cond_groups": G, "network_rows_per_step": B * (G + 1),
+                       "cloud": "6 groups x 6 obstacles x 64 points", "weights": "random-init (seeded)",
+                       "l2": "activation working set per network call (>10 GB) exceeds L2; no flush needed",
+                       "sharding": "batch across ranks; all-gather of (free, length, smoothness) + select_best"},
+            "e2e": {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": "trajectories/s",
+                    "h2d_bytes_per_step": int(groups_host.numel() * 4 + 2 * D * 4), "d2h_bytes_per_step": int(B * H * D * 4 + 32)},
+            "gpu_launches": launches,
+            "clocks": sampler.summary(),
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
+                         "frac": achieved / peak_tf, "traffic": None, "peak_source": how + " bf16 sustained",
+                         "kernel": "gemm_tc_kernel", "launches_per_step": prof_n["gemm"],
+                         "avg_launch_us": 1e3 * prof_ms["gemm"] / max(prof_n["gemm"], 1),
+                         "algorithmic_flops_per_launch": gemm_flops / max(prof_n["gemm"], 1),
+                         "share_of_step": prof_ms["gemm"] / total_prof if total_prof else None,
+                         "class_ms": prof_ms,
+                         "note": "parity mode issues 3 bf16 MMAs per product (hi*hi+hi*lo+lo*hi): ceiling = peak/3"},
+        }
+        line["cpu_baseline"] = cpu_baseline(sample_B=args.cpu_sample)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()

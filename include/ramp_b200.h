@@ -20,6 +20,8 @@ extern "C" {
 
 const char* ramp_last_error(void);
 int ramp_version(void);
+/* number of CUDA kernels this library has launched in this process */
+unsigned long long ramp_launch_count(void);
 
 /* ---- low-level dense contraction (building block of the score network; exposed for tests) ----
  * D[(n,l), :] = sum_t A[n, par_t + a_pstride*(l + joff_t), 0:K] . W[wtap_t, :, 0:K]^T (+bias +bias_tab[row2scene[n]] +residual)
@@ -63,6 +65,11 @@ int ramp_unet_set_scenes(void* handle, const float* latents, int n_scenes, void*
  * eps_out / f_out [n_rows, H, D], either may be NULL (f_out = forward_no_energy output). */
 int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, int x_repeat, float t, const int32_t* row2scene,
                           float* eps_out, float* f_out, void* stream);
+
+/* Per-kernel-class device timing (CUDA events on the launch stream around every launch of the engine).
+ * enable != 0 starts recording; a call with ms4_host != NULL synchronises and returns the accumulated
+ * milliseconds and launch counts of {tensor-core GEMM, norms, attention core, elementwise} and resets them. */
+int ramp_unet_profile(void* handle, int enable, float* ms4_host, int* launches4_host);
 
 /* ---- fused sampler step (one launch per reverse-diffusion step) --------------------------------
  * eps rows come from ramp_unet_energy_grad; row of (trajectory b, group g) = b*eps_bstride + g*eps_gstride,

@@ -7,6 +7,8 @@
 namespace ramp {
 static thread_local std::string g_err;
 void set_error(const std::string& msg) { g_err = msg; }
+static unsigned long long g_launches = 0;
+void count_launch() { ++g_launches; }
 
 __global__ void split_kernel(const float* __restrict__ x, size_t n, bf16* hi, bf16* lo) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
@@ -24,13 +26,14 @@ extern "C" {
 
 const char* ramp_last_error(void) { return g_err.c_str(); }
 int ramp_version(void) { return 100; }
+unsigned long long ramp_launch_count(void) { return g_launches; }
 
 int ramp_split_bf16(const float* x, size_t n, void* hi, void* lo, void* stream) {
   size_t b = (n + 255) / 256;
   if (b > 148 * 16) b = 148 * 16;
   if (n == 0) return 0;
   split_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(x, n, (bf16*)hi, (bf16*)lo);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -79,6 +82,11 @@ int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, int x_repeat
                           float* eps_out, float* f_out, void* stream) {
   RAMP_CHECK(handle && x, "ramp_unet_energy_grad: null argument");
   return ((UnetEngine*)handle)->energy_grad(x, n_rows, x_repeat, t, row2scene, eps_out, f_out, (cudaStream_t)stream);
+}
+
+int ramp_unet_profile(void* handle, int enable, float* ms4_host, int* launches4_host) {
+  RAMP_CHECK(handle, "ramp_unet_profile: null handle");
+  return ((UnetEngine*)handle)->profile(enable, ms4_host, launches4_host);
 }
 
 }  // extern "C"

@@ -27,6 +27,14 @@ void set_error(const std::string& msg);
     }                                                                                           \
   } while (0)
 
+// every kernel launch of this library is followed by RAMP_LAUNCH_OK(): counts it and checks the launch
+void count_launch();
+#define RAMP_LAUNCH_OK()                                                                        \
+  do {                                                                                          \
+    ramp::count_launch();                                                                       \
+    RAMP_CUDA_OK(cudaGetLastError());                                                           \
+  } while (0)
+
 typedef __nv_bfloat16 bf16;
 
 // Split-precision activation / weight view: value = hi + lo (two bf16 planes, same layout).

@@ -75,8 +75,8 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
   };
   if (tid == 0) issue(0);
 
-  float mx[R], my[R], mz[R], best[R];
-  int bchunk[R];
+  float mx[R], my[R], mz[R], best[R], second[R];
+  int bchunk[R], schunk[R];
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const int qi = (blockIdx.x * R + r) * NN_THREADS + tid;
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
       my[r] = -2.f * q[(size_t)qi * qstride + 1];
       if (DIM == 3) mz[r] = -2.f * q[(size_t)qi * qstride + 2];
     }
-    best[r] = FLT_MAX; bchunk[r] = 0;
+    best[r] = second[r] = FLT_MAX; bchunk[r] = schunk[r] = 0;
   }
   for (int t = 0; t < ntiles; ++t) {
     if (tid == 0 && t + 1 < ntiles) issue(t + 1);
@@ -103,27 +103,42 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
         for (int r = 0; r < R; ++r)
           cm[r] = min3f(cm[r], nn_key<DIM>(pa, mx[r], my[r], mz[r]), nn_key<DIM>(pb, mx[r], my[r], mz[r]));
       }
+      const int gc = t * (NN_TILE / NN_CHUNK) + c;
 #pragma unroll
-      for (int r = 0; r < R; ++r)
-        if (cm[r] < best[r]) { best[r] = cm[r]; bchunk[r] = t * (NN_TILE / NN_CHUNK) + c; }
+      for (int r = 0; r < R; ++r) {
+        if (cm[r] < best[r]) { second[r] = best[r]; schunk[r] = bchunk[r]; best[r] = cm[r]; bchunk[r] = gc; }
+        else if (cm[r] < second[r]) { second[r] = cm[r]; schunk[r] = gc; }
+      }
     }
     __syncthreads();
   }
-  // recover the argmin inside the winning chunk (same FFMA sequence => bit-identical keys), exact distance
+  // Exact decision: the scan key |p|^2 - 2 q.p carries cancellation error ~2^-22 (|q|^2 + |p|^2); the winning
+  // chunk (and the runner-up chunk when its key is within that bound) is re-scanned with the direct form
+  // (q - p)^2, lowest index winning ties, so the result is the fp32-exact nearest point.
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const int qi = (blockIdx.x * R + r) * NN_THREADS + tid;
     if (qi >= Q) continue;
-    const float4* cp = cloud4 + (size_t)bchunk[r] * NN_CHUNK;
-    int arg = 0;
-    for (int j = NN_CHUNK - 1; j >= 0; --j)
-      if (nn_key<DIM>(cp[j], mx[r], my[r], mz[r]) == best[r]) arg = j;     // lowest index wins ties
-    const float4 p = cp[arg];
-    const float dx = q[(size_t)qi * qstride] - p.x, dy = q[(size_t)qi * qstride + 1] - p.y;
-    float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-    if (DIM == 3) { const float dz = q[(size_t)qi * qstride + 2] - p.z; d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
-    const float d = sqrtf(d2);
-    const int gi = bchunk[r] * NN_CHUNK + arg;
+    const float qx = q[(size_t)qi * qstride], qy = q[(size_t)qi * qstride + 1];
+    const float qz = DIM == 3 ? q[(size_t)qi * qstride + 2] : 0.f;
+    const float q2 = qx * qx + qy * qy + qz * qz;
+    const float tol = 1.2e-6f * (q2 + fabsf(best[r] + q2)) + 1e-30f;
+    float bd2 = FLT_MAX; int gi = P;
+    const int ncand = (second[r] <= best[r] + tol && schunk[r] != bchunk[r]) ? 2 : 1;
+    for (int cnd = 0; cnd < ncand; ++cnd) {
+      const int ch = cnd == 0 ? bchunk[r] : schunk[r];
+      const float4* cp = cloud4 + (size_t)ch * NN_CHUNK;
+      for (int j = 0; j < NN_CHUNK; ++j) {
+        const float4 p = cp[j];
+        if (p.w == FLT_MAX) continue;               // padding
+        const float dx = qx - p.x, dy = qy - p.y;
+        float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+        if (DIM == 3) { const float dz = qz - p.z; d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
+        const int g = ch * NN_CHUNK + j;
+        if (d2 < bd2 || (d2 == bd2 && g < gi)) { bd2 = d2; gi = g; }
+      }
+    }
+    const float d = sqrtf(bd2);
     const bool hit = gi < P && d < thr;
     out_d[qi] = hit ? d : INFINITY;
     out_idx[qi] = hit ? gi : P;
@@ -321,7 +336,7 @@ static int nn_launch(const float4* c4, int P, int Ppad, const float* q, int Q, i
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(nn_query_kernel<DIM, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
   const int per = NN_THREADS * R;
   nn_query_kernel<DIM, R><<<(Q + per - 1) / per, NN_THREADS, smem, s>>>(c4, P, Ppad, q, Q, qstride, thr, od, oi);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -335,7 +350,7 @@ int ramp_cloud_pack(const float* cloud, int P, int dim, void* packed, void* stre
   RAMP_CHECK(P >= 1, "ramp_cloud_pack: empty cloud");
   const int Ppad = (int)ramp_cloud_packed_points(P);
   nn_pack_kernel<<<(Ppad + 255) / 256, 256, 0, (cudaStream_t)stream>>>(cloud, P, dim, Ppad, (float4*)packed);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -369,7 +384,7 @@ int ramp_apf_static(const float* x, int B, int H, int D, int dim, const float* d
   if (B == 0) return 0;
   apf_static_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(x, H, D, dim, dist, idx, (const float4*)packed, P, thr, strength,
                                                          window, out);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -382,7 +397,7 @@ int ramp_apf_dynamic(float* x, int B, int H, int D, const float* dist, const int
   if (B == 0) return 0;
   apf_dynamic_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(x, H, D, dist, idx, (const float4*)packed, P, mode, window,
                                                           affected, strength, thr_force, goal, active);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -391,14 +406,14 @@ int ramp_cost_terms(const float* x, int B, int H, int D, int dim, const float* d
   RAMP_CHECK(x && dist && terms, "ramp_cost_terms: null argument");
   if (B == 0) return 0;
   cost_terms_kernel<<<(B + 7) / 8, 256, 0, (cudaStream_t)stream>>>(x, B, H, D, dim, dist, thr, terms);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
 int ramp_select_best(const float* terms, int n, float w_smooth, float w_len, float* out8, void* stream) {
   RAMP_CHECK(terms && out8, "ramp_select_best: null argument");
   select_best_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(terms, n, w_smooth, w_len, out8);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 

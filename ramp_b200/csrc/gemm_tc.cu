@@ -420,7 +420,7 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
   dim3 grid(m_tiles, d.Nout / p.BN);
   gemm_tc_kernel<<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 

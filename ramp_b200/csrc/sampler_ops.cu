@@ -145,7 +145,7 @@ int ramp_step(const ramp_step_args* u, void* stream) {
   const size_t total = (size_t)a.B * a.H * a.D;
   if (!total) return 0;
   step_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(a);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -157,7 +157,7 @@ int ramp_ddim_update(const float* x, const float* x0, int B, int H, int D, float
   const size_t total = (size_t)B * H * D;
   if (!total) return 0;
   ddim_update_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(a);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -167,7 +167,7 @@ int ramp_inpaint(float* x, int B, int H, int D, const unsigned char* pin_mask, c
   const size_t total = (size_t)B * H * D;
   if (!total) return 0;
   inpaint_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(x, B, H, D, pin_mask, pin_val, pin_bstride);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -179,7 +179,7 @@ int ramp_q_sample(const float* x0, long x0_bstride, const float* noise, int B, i
   if (!total) return 0;
   q_sample_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(x0, x0_bstride, noise, B, H, D, sqrt_ac, sqrt_1mac,
                                                                      pin_mask, pin_val, pin_bstride, out);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 

@@ -69,7 +69,7 @@ int UnetEngine::pack(PackedW& w, const std::string& name, int T, int Nd, int Kd,
   int blocks = (int)((total + 255) / 256);
   if (blocks > 1184) blocks = 1184;
   pack_weight_kernel<<<blocks, 256>>>(src, w.hi, w.lo, T, Nd, Kd, Ns, Ks, st, sn, sk, noff, koff);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -284,6 +284,37 @@ int UnetEngine::energy_grad(const float* x, int n_rows, int x_repeat, float t, c
   RAMP_CHECK(n_rows >= 1 && n_rows <= cfg_.max_rows, "n_rows exceeds max_rows of this engine");
   arena_off_ = 0;
   return run(x, n_rows, x_repeat, t, row2scene, eps_out, f_out, s);
+}
+
+UnetEngine::ProfScope::ProfScope(UnetEngine* eng, int cat) : e(eng), idx(-1) {
+  if (!e->prof_ || e->dry_) return;
+  if (e->prof_used_ == e->prof_events_.size()) {
+    ProfEv ev; ev.cat = cat;
+    if (cudaEventCreate(&ev.a) != cudaSuccess || cudaEventCreate(&ev.b) != cudaSuccess) return;
+    e->prof_events_.push_back(ev);
+  }
+  idx = (int)e->prof_used_++;
+  e->prof_events_[idx].cat = cat;
+  cudaEventRecord(e->prof_events_[idx].a, e->s_);
+}
+UnetEngine::ProfScope::~ProfScope() {
+  if (idx >= 0) cudaEventRecord(e->prof_events_[idx].b, e->s_);
+}
+
+int UnetEngine::profile(int enable, float* ms4, int* launches4) {
+  if (ms4) {
+    RAMP_CUDA_OK(cudaDeviceSynchronize());
+    float acc[4] = {0, 0, 0, 0}; int cnt[4] = {0, 0, 0, 0};
+    for (size_t i = 0; i < prof_used_; ++i) {
+      float ms = 0.f;
+      RAMP_CUDA_OK(cudaEventElapsedTime(&ms, prof_events_[i].a, prof_events_[i].b));
+      acc[prof_events_[i].cat & 3] += ms; cnt[prof_events_[i].cat & 3]++;
+    }
+    for (int k = 0; k < 4; ++k) { ms4[k] = acc[k]; if (launches4) launches4[k] = cnt[k]; }
+    prof_used_ = 0;
+  }
+  prof_ = enable != 0;
+  return 0;
 }
 
 }  // namespace ramp

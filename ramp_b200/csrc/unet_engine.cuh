@@ -53,6 +53,7 @@ class UnetEngine {
   int energy_grad(const float* x, int n_rows, int x_repeat, float t, const int* row2scene, float* eps_out,
                   float* f_out, cudaStream_t s);
   size_t workspace_bytes() const { return arena_bytes_; }
+  int profile(int enable, float* ms4, int* launches4);
   const UnetConfig& cfg() const { return cfg_; }
 
  private:
@@ -110,6 +111,17 @@ class UnetEngine {
   int st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act& dx);
 
   int n_ = 0, npad_ = 0; const int* r2s_ = nullptr; cudaStream_t s_ = nullptr;
+
+  // optional per-class timing
+  bool prof_ = false;
+  struct ProfEv { cudaEvent_t a, b; int cat; };
+  std::vector<ProfEv> prof_events_; size_t prof_used_ = 0;
+ public:
+  struct ProfScope {
+    UnetEngine* e; int idx;
+    ProfScope(UnetEngine* eng, int cat);
+    ~ProfScope();
+  };
 };
 
 }  // namespace ramp

@@ -30,7 +30,7 @@ int prep_input(const float* x, int n_samples, int n_pad, int L, int D, int x_rep
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
   prep_input_kernel<<<blocks, 256, 0, s>>>(x, n_samples, n_pad, L, D, x_repeat < 1 ? 1 : x_repeat, hi, lo);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(256) gn_forward_kernel(GnArgs a) {
 int gn_forward(const GnArgs& a, cudaStream_t s) {
   RAMP_CHECK(a.C % 8 == 0, "gn: C must be a multiple of 8");
   gn_forward_kernel<<<a.n_samples, 256, 0, s>>>(a);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
 int gn_backward(const GnBwdArgs& a, cudaStream_t s) {
   RAMP_CHECK(a.C % 8 == 0, "gn: C must be a multiple of 8");
   gn_backward_kernel<<<a.n_samples, 256, 0, s>>>(a);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -145,7 +145,7 @@ int ln_forward(const float* x, int rows, int C, const float* gamma, const float*
                cudaStream_t s) {
   RAMP_CHECK(C == 256, "ln: C must be 256");
   ln_forward_kernel<<<(rows + 7) / 8, 256, 0, s>>>(x, rows, gamma, beta, out_hi, out_lo);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -197,7 +197,7 @@ int ln_backward(const float* x, int rows, int C, const float* gamma, const float
                 bf16* out_hi, bf16* out_lo, cudaStream_t s) {
   RAMP_CHECK(C == 256, "ln: C must be 256");
   ln_backward_kernel<<<(rows + 7) / 8, 256, 0, s>>>(x, rows, gamma, dy, add, out_f32, out_hi, out_lo);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -258,7 +258,7 @@ int attn_forward(const float* qkv, int n_samples, int L, bf16* out_hi, bf16* out
   static bool attr = false;
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem(64, false))); attr = true; }
   attn_forward_kernel<<<n_samples * 4, 128, attn_smem(L, false), s>>>(qkv, L, out_hi, out_lo);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -313,7 +313,7 @@ int attn_backward(const float* qkv, const float* d_out, int n_samples, int L, bf
   static bool attr = false;
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem(64, true))); attr = true; }
   attn_backward_kernel<<<n_samples * 4, 128, attn_smem(L, true), s>>>(qkv, d_out, L, dq_hi, dq_lo);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -344,12 +344,12 @@ static int ew_blocks(size_t total) {
 }
 int geglu_forward(const float* u, int rows, int inner, bf16* out_hi, bf16* out_lo, cudaStream_t s) {
   geglu_forward_kernel<<<ew_blocks((size_t)rows * inner), 256, 0, s>>>(u, rows, inner, out_hi, out_lo);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 int geglu_backward(const float* u, const float* dg, int rows, int inner, bf16* du_hi, bf16* du_lo, cudaStream_t s) {
   geglu_backward_kernel<<<ew_blocks((size_t)rows * inner), 256, 0, s>>>(u, dg, rows, inner, du_hi, du_lo);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(128) time_cond_kernel(const float* __restrict_
 }
 int time_cond(const float* tw, float t, const CondBlock* blocks_dev, int n_blocks, cudaStream_t s) {
   time_cond_kernel<<<n_blocks, 128, 0, s>>>(tw, t, blocks_dev);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 
@@ -412,7 +412,7 @@ __global__ void __launch_bounds__(256) scene_const_kernel(const SceneBlock* bloc
 int scene_constants(const SceneBlock* blocks_dev, int n_blocks, const float* latents, int n_scenes, int ctx_dim,
                     cudaStream_t s) {
   scene_const_kernel<<<dim3(n_blocks, n_scenes), 256, 0, s>>>(blocks_dev, latents, n_scenes, ctx_dim);
-  RAMP_CUDA_OK(cudaGetLastError());
+  RAMP_LAUNCH_OK();
   return 0;
 }
 

@@ -31,6 +31,7 @@ int UnetEngine::gemm(const Act& a, int K, const PackedW& w, const GemmTap* taps,
                      const float* res2, int ldr2, float* of, int ldo, bf16* oh, bf16* ol, int lds, int o_L,
                      int o_stride, int o_off) {
   if (dry_) return 0;
+  ProfScope ps(this, 0);
   GemmDesc d{};
   d.a_hi = a.hi; d.a_lo = a.lo; d.n_samples = npad_; d.L_in = L_in; d.ldA = a.lds; d.K = K; d.a_pstride = pstride;
   d.L_out = L_out; d.ntaps = ntaps;
@@ -53,7 +54,7 @@ int UnetEngine::res_fwd(const ResW& w, const Act& x, int L, const OutSpec& o, Ac
   if (!dry_) {
     GnArgs g{}; g.x = sv.c1; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g1; g.beta = w.b1;
     g.eps = 1e-5f; g.mish = 1; g.cond = w.cond; g.out_hi = h1.hi; g.out_lo = h1.lo; g.ldS = co;
-    TRY(gn_forward(g, s_));
+    ProfScope ps(this, 1); TRY(gn_forward(g, s_));
   }
   sv.c2 = allocf(M * co);
   Act h1a; h1a.hi = h1.hi; h1a.lo = h1.lo; h1a.lds = co; h1a.C = co;
@@ -77,7 +78,7 @@ int UnetEngine::res_fwd(const ResW& w, const Act& x, int L, const OutSpec& o, Ac
     GnArgs g{}; g.x = sv.c2; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g2; g.beta = w.b2;
     g.eps = 1e-5f; g.mish = 1; g.add = addp; g.ldAdd = ldadd; g.out_f32 = const_cast<float*>(y.f); g.ldO = co;
     g.out_hi = oh; g.out_lo = ol; g.ldS = lds;
-    TRY(gn_forward(g, s_));
+    ProfScope ps(this, 1); TRY(gn_forward(g, s_));
   }
   return 0;
 }
@@ -90,7 +91,7 @@ int UnetEngine::res_bwd(const ResW& w, const ResSave& sv, const Act& dy, int L, 
   if (!dry_) {
     GnBwdArgs g{}; g.x = sv.c2; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g2; g.beta = w.b2;
     g.eps = 1e-5f; g.mish = 1; g.dy = dy.f; g.ldDy = dy.ldf; g.out_hi = t1.hi; g.out_lo = t1.lo; g.ldS = co;
-    TRY(gn_backward(g, s_));
+    ProfScope ps(this, 1); TRY(gn_backward(g, s_));
   }
   float* dh1 = allocf(M * co);
   Act t1a; t1a.hi = t1.hi; t1a.lo = t1.lo; t1a.lds = co;
@@ -100,7 +101,7 @@ int UnetEngine::res_bwd(const ResW& w, const ResSave& sv, const Act& dy, int L, 
   if (!dry_) {
     GnBwdArgs g{}; g.x = sv.c1; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g1; g.beta = w.b1;
     g.eps = 1e-5f; g.mish = 1; g.dy = dh1; g.ldDy = co; g.out_hi = t2.hi; g.out_lo = t2.lo; g.ldS = co;
-    TRY(gn_backward(g, s_));
+    ProfScope ps(this, 1); TRY(gn_backward(g, s_));
   }
   const float* res = dy.f; int ldr = dy.ldf;
   if (w.has_res) {
@@ -131,7 +132,7 @@ int UnetEngine::st_fwd(const STW& w, const Act& x, int L, const OutSpec& o, Act&
   if (!dry_) {
     GnArgs g{}; g.x = x.f; g.ldX = x.ldf; g.n_samples = npad_; g.L = L; g.C = C; g.gamma = w.gn_g; g.beta = w.gn_b;
     g.eps = 1e-6f; g.mish = 0; g.out_hi = xn.hi; g.out_lo = xn.lo; g.ldS = C;
-    TRY(gn_forward(g, s_));
+    ProfScope ps(this, 1); TRY(gn_forward(g, s_));
   }
   float* z = allocf(M * 256);
   Act xna; xna.hi = xn.hi; xna.lo = xn.lo; xna.lds = C;
@@ -143,25 +144,25 @@ int UnetEngine::st_fwd(const STW& w, const Act& x, int L, const OutSpec& o, Act&
     TBlockSave& ts = sv.blk[b];
     ts.zin = z;
     Split a = allocs(M * 256);
-    if (!dry_) TRY(ln_forward(z, (int)M, 256, t.ln1g, t.ln1b, a.hi, a.lo, s_));
+    if (!dry_) { ProfScope ps(this, 1); TRY(ln_forward(z, (int)M, 256, t.ln1g, t.ln1b, a.hi, a.lo, s_)); }
     ts.qkv = allocf(M * 768);
     Act aa; aa.hi = a.hi; aa.lo = a.lo; aa.lds = 256;
     TRY(gemm(aa, 256, t.qkv_f, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, ts.qkv, 768, nullptr,
              nullptr, 0, L, 1, 0));
     Split ao = allocs(M * 256);
-    if (!dry_) TRY(attn_forward(ts.qkv, npad_, L, ao.hi, ao.lo, s_));
+    if (!dry_) { ProfScope ps(this, 2); TRY(attn_forward(ts.qkv, npad_, L, ao.hi, ao.lo, s_)); }
     ts.z1 = allocf(M * 256);
     Act aoa; aoa.hi = ao.hi; aoa.lo = ao.lo; aoa.lds = 256;
     TRY(gemm(aoa, 256, t.o_f, TAP_1X1, 1, L, L, 1, nullptr, t.bias_tab, z, 256, nullptr, 0, ts.z1, 256, nullptr, nullptr,
              0, L, 1, 0));
     Split f = allocs(M * 256);
-    if (!dry_) TRY(ln_forward(ts.z1, (int)M, 256, t.ln3g, t.ln3b, f.hi, f.lo, s_));
+    if (!dry_) { ProfScope ps(this, 1); TRY(ln_forward(ts.z1, (int)M, 256, t.ln3g, t.ln3b, f.hi, f.lo, s_)); }
     ts.u = allocf(M * 2048);
     Act fa; fa.hi = f.hi; fa.lo = f.lo; fa.lds = 256;
     TRY(gemm(fa, 256, t.ff1_f, TAP_1X1, 1, L, L, 1, t.ff1_bias, nullptr, nullptr, 0, nullptr, 0, ts.u, 2048, nullptr,
              nullptr, 0, L, 1, 0));
     Split g = allocs(M * 1024);
-    if (!dry_) TRY(geglu_forward(ts.u, (int)M, 1024, g.hi, g.lo, s_));
+    if (!dry_) { ProfScope ps(this, 3); TRY(geglu_forward(ts.u, (int)M, 1024, g.hi, g.lo, s_)); }
     float* z2 = allocf(M * 256);
     if (b == 1) zs = allocs(M * 256);
     Act ga; ga.hi = g.hi; ga.lo = g.lo; ga.lds = 1024;
@@ -197,27 +198,27 @@ int UnetEngine::st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act
     TRY(gemm(dza, 256, t.ff2_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dg, 1024, nullptr, nullptr,
              0, L, 1, 0));
     Split du = allocs(M * 2048);
-    if (!dry_) TRY(geglu_backward(ts.u, dg, (int)M, 1024, du.hi, du.lo, s_));
+    if (!dry_) { ProfScope ps(this, 3); TRY(geglu_backward(ts.u, dg, (int)M, 1024, du.hi, du.lo, s_)); }
     float* df = allocf(M * 256);
     Act dua; dua.hi = du.hi; dua.lo = du.lo; dua.lds = 2048;
     TRY(gemm(dua, 2048, t.ff1_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, df, 256, nullptr, nullptr,
              0, L, 1, 0));
     float* dz1 = allocf(M * 256);
     Split dz1s = allocs(M * 256);
-    if (!dry_) TRY(ln_backward(ts.z1, (int)M, 256, t.ln3g, df, dz, dz1, dz1s.hi, dz1s.lo, s_));
+    if (!dry_) { ProfScope ps(this, 1); TRY(ln_backward(ts.z1, (int)M, 256, t.ln3g, df, dz, dz1, dz1s.hi, dz1s.lo, s_)); }
     float* dout = allocf(M * 256);
     Act d1a; d1a.hi = dz1s.hi; d1a.lo = dz1s.lo; d1a.lds = 256;
     TRY(gemm(d1a, 256, t.o_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dout, 256, nullptr, nullptr,
              0, L, 1, 0));
     Split dqkv = allocs(M * 768);
-    if (!dry_) TRY(attn_backward(ts.qkv, dout, npad_, L, dqkv.hi, dqkv.lo, s_));
+    if (!dry_) { ProfScope ps(this, 2); TRY(attn_backward(ts.qkv, dout, npad_, L, dqkv.hi, dqkv.lo, s_)); }
     float* da = allocf(M * 256);
     Act dqa; dqa.hi = dqkv.hi; dqa.lo = dqkv.lo; dqa.lds = 768;
     TRY(gemm(dqa, 768, t.qkv_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, da, 256, nullptr, nullptr,
              0, L, 1, 0));
     dz = allocf(M * 256);
     dzs = allocs(M * 256);
-    if (!dry_) TRY(ln_backward(ts.zin, (int)M, 256, t.ln1g, da, dz1, dz, dzs.hi, dzs.lo, s_));
+    if (!dry_) { ProfScope ps(this, 1); TRY(ln_backward(ts.zin, (int)M, 256, t.ln1g, da, dz1, dz, dzs.hi, dzs.lo, s_)); }
   }
   float* dxn = allocf(M * C);
   Act dza; dza.hi = dzs.hi; dza.lo = dzs.lo; dza.lds = 256;
@@ -231,7 +232,7 @@ int UnetEngine::st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act
     GnBwdArgs g{}; g.x = sv.x; g.ldX = sv.ldx; g.n_samples = npad_; g.L = L; g.C = C; g.gamma = w.gn_g; g.beta = w.gn_b;
     g.eps = 1e-6f; g.mish = 0; g.dy = dxn; g.ldDy = C; g.add = dy.f; g.ldAdd = dy.ldf; g.out_f32 = dxf; g.ldO = C;
     g.out_hi = ds.hi; g.out_lo = ds.lo; g.ldS = C;
-    TRY(gn_backward(g, s_));
+    ProfScope ps(this, 1); TRY(gn_backward(g, s_));
   }
   return 0;
 }
@@ -319,7 +320,7 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
   if (!dry_) {
     GnArgs g{}; g.x = cfin; g.ldX = 32; g.n_samples = npad_; g.L = H; g.C = 32; g.gamma = final_g_; g.beta = final_b_;
     g.eps = 1e-5f; g.mish = 1; g.out_hi = hs.hi; g.out_lo = hs.lo; g.ldS = 32;
-    TRY(gn_forward(g, s));
+    ProfScope ps(this, 1); TRY(gn_forward(g, s));
   }
   float* fo = allocf(M * 16);
   Split fos = allocs(M * 16);
@@ -331,7 +332,7 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
   const int eb = (int)((((size_t)n_rows * H * D + 255) / 256) > 1184 ? 1184 : (((size_t)n_rows * H * D + 255) / 256));
   if (!dry_ && f_out) {
     extract_kernel<<<eb, 256, 0, s>>>(fo, n_rows, H, D, f_out);
-    RAMP_CUDA_OK(cudaGetLastError());
+    RAMP_LAUNCH_OK();
   }
   if (!dry_ && !eps_out) return 0;
 
@@ -346,7 +347,7 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
   if (!dry_) {
     GnBwdArgs g{}; g.x = cfin; g.ldX = 32; g.n_samples = npad_; g.L = H; g.C = 32; g.gamma = final_g_; g.beta = final_b_;
     g.eps = 1e-5f; g.mish = 1; g.dy = dh; g.ldDy = 32; g.out_hi = dcs.hi; g.out_lo = dcs.lo; g.ldS = 32;
-    TRY(gn_backward(g, s));
+    ProfScope ps(this, 1); TRY(gn_backward(g, s));
   }
   Act dy; dy.C = 32;
   {
@@ -403,7 +404,7 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
       L *= 2;
     } else if (!dry_) {
       extract_kernel<<<eb, 256, 0, s>>>(d0.f, n_rows, H, D, eps_out);
-      RAMP_CUDA_OK(cudaGetLastError());
+      RAMP_LAUNCH_OK();
     }
   }
   return 0;

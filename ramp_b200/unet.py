@@ -285,3 +285,17 @@ class TemporalUnetInference(nn.Module):
 
     def forward_no_energy(self, x, time, x_start=None, obstacle_pts=None, forward_t=None, compose=False):
         return self._rows(x, time, obstacle_pts, compose, want_f=True)[1]
+
+    def profile(self, enable, fetch=False):
+        """Per-kernel-class CUDA-event timing of the engine (ramp_unet_profile).  With fetch=True returns
+        ({class: ms}, {class: launches}) accumulated since the last fetch."""
+        if self._engine is None:
+            raise RampError("engine not built yet")
+        names = ("gemm", "norm", "attention", "elementwise")
+        if fetch:
+            ms = (ctypes.c_float * 4)()
+            cnt = (ctypes.c_int * 4)()
+            check(lib().ramp_unet_profile(self._engine, int(bool(enable)), ms, cnt), "ramp_unet_profile")
+            return dict(zip(names, list(ms))), dict(zip(names, list(cnt)))
+        check(lib().ramp_unet_profile(self._engine, int(bool(enable)), None, None), "ramp_unet_profile")
+        return None

@@ -168,7 +168,25 @@ def test_3d_ddpm25_vs_reference(cuda):
                                 sample_fn=ddpm_sample_fn, noise_std_extra_schedule_fn=lambda t: 0.5)
     d = (chain.cpu() - g["chain"]).abs()
     print("3d per-step max:", ["%.1e" % v for v in d.amax(dim=(1, 2, 3)).tolist()])
-    assert (d[-1] > 1e-3).float().mean() < 0.02 and d[-1].median() < 1e-4
+    # one trajectory (384 numbers), CFG weights 6.75 / -5.75 amplify the network's ~5e-5 split-bf16 error 12x:
+    # free-running is a statistical bound, the per-step bound is teacher-forced below.
+    assert (d[-1] > 1e-3).float().mean() < 0.05 and d[-1].median() < 1e-3
+    noise = [torch.randn((1, 64, 6), generator=torch.Generator("cpu").manual_seed(g["noise_seed"] + 1 + k)) for k in range(25)]
+    from ramp_b200 import ops
+    pins = ops.Pins.from_hard_conds(hc(6, cuda), 1, 64, 6, cuda)
+    cloud = g["cloud"].to(cuda).unsqueeze(0)
+
+    def step(k, x):
+        t = 24 - k
+        return m._ddpm_step(x, t, cloud, noise[k].to(cuda) if t > 0 else None, 0.5, pins=pins)
+
+    per = _teacher_forced(m, g["chain"], step)
+    print("3d teacher-forced max:", ["%.1e" % e.max() for e in per])
+    for k, e in enumerate(per):
+        if k == 0:
+            assert (e > 1e-3).float().mean() < 0.02
+        else:
+            assert e.max() < 2e-3 and (e > 1e-3).float().mean() < 0.01, (k, e.max())
 
 
 def test_3d_batch_equals_looped_singles(cuda):
