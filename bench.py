@@ -193,3 +193,81 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU baseline: the reference algorithm restated on the host (oracle port; /root/reference does not exist
+# on the GPU box).  Same model, same 7 rows per trajectory, same 25 steps — on a BOUNDED batch.
+# ---------------------------------------------------------------------------------------------------
+def _cpu_once(sample_B):
+    from oracle import ramp_oracle as O
+    from ramp_b200.testing import synthetic_cloud_2d, synthetic_state_dict, tape
+    from ramp_b200.diffusion import StaticGaussianDiffusionModel
+    from ramp_b200.unet import TemporalUnetInference
+    net = TemporalUnetInference(n_support_points=H, state_dim=D)
+    sd = synthetic_state_dict(StaticGaussianDiffusionModel(model=net, n_diffusion_steps=T, predict_epsilon=True), 0)
+    sch = O.make_schedule(T)
+    lat = O.scene_encoder_2d(sd, synthetic_cloud_2d(seed=5, groups=G))
+    hc = {0: torch.tensor([-0.8, -0.8, 0.0, 0.0]), H - 1: torch.tensor([0.8, 0.8, 0.0, 0.0])}
+    noise = tape(100, [(sample_B, H, D)] * (T + 1))
+    t0 = time.perf_counter()
+    O.sample_ddpm(sd, sch, T, lat, [2.0] * G, hc, noise, noise_scale=0.5)
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(sample_B=2):
+    threads = torch.get_num_threads()
+    dt = _cpu_once(sample_B)
+    return {"value": sample_B / dt, "unit": "trajectories/s", "cores": threads, "kind": "port",
+            "sample": "%d trajectories x %d network rows x %d DDPM steps (same model/config), %.1f s on %d threads"
+                      % (sample_B, G + 1, T, dt, threads)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm (oracle port) on this box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = torch.get_num_threads()
+    sample_B = args.cpu_sample
+    for _ in range(min(args.warmup, 1)):
+        _cpu_once(sample_B)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        _cpu_once(sample_B)
+    dt = time.perf_counter() - t0
+    val = sample_B * args.steps / dt
+    line = {"impl": "reference", "metric": "trajectories/sec (H=64, 25 steps)", "value": val, "unit": "trajectories/s",
+            "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": min(args.warmup, 1),
+            "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "trajectories_per_step": sample_B, "horizon": H, "state_dim": D,
+                       "diffusion_steps": T, "cond_groups": G,
+                       "note": "bounded sample of the same workload; reference = pure PyTorch, run as the CPU oracle port"},
+            "cpu_baseline": {"value": val, "unit": "trajectories/s", "cores": threads, "kind": "port",
+                             "sample": "%d trajectories per step, %d steps" % (sample_B, args.steps)},
+            "e2e": {"value": val, "unit": "trajectories/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=B_PER_GPU, help="trajectories per GPU")
+    ap.add_argument("--max-rows", type=int, default=1792, help="network rows per engine call (workspace size)")
+    ap.add_argument("--cpu-sample", type=int, default=2, help="trajectories in the bounded CPU sample")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
