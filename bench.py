@@ -188,7 +188,8 @@ def run_ours(args):
                          "class_ms": prof_ms,
                          "note": "parity mode issues 3 bf16 MMAs per product (hi*hi+hi*lo+lo*hi): ceiling = peak/3"},
         }
-        line["cpu_baseline"] = cpu_baseline(sample_B=args.cpu_sample)
+        if args.cpu_sample > 0:
+            line["cpu_baseline"] = cpu_baseline(sample_B=args.cpu_sample)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -1,0 +1,70 @@
+"""The C-ABI shared library loads without a GPU and exports every symbol include/ramp_b200.h declares.
+No compute call is made here (there is no CPU path to call)."""
+import ctypes
+import os
+import re
+import subprocess
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "ramp_b200.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(ramp_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_builds_loads_and_exports_header_symbols():
+    from ramp_b200 import build
+    path = build.build()
+    lib = ctypes.CDLL(path)
+    names = declared_symbols()
+    assert len(names) >= 24
+    for n in names:
+        assert hasattr(lib, n), "missing export: " + n
+    lib.ramp_version.restype = ctypes.c_int
+    assert lib.ramp_version() >= 100
+    lib.ramp_last_error.restype = ctypes.c_char_p
+    assert isinstance(lib.ramp_last_error(), bytes)
+
+
+def test_no_undeclared_exports():
+    from ramp_b200 import build
+    path = build.build()
+    out = subprocess.run(["nm", "-D", "--defined-only", path], capture_output=True, text=True).stdout
+    exported = sorted(l.split()[-1] for l in out.splitlines() if " T ramp_" in l)
+    assert exported == declared_symbols()
+
+
+def test_header_compiles_as_plain_c(tmp_path):
+    c = tmp_path / "t.c"
+    c.write_text('#include "ramp_b200.h"\nint main(void){ramp_step_args a; ramp_unet_config c; (void)a; (void)c; return 0;}\n')
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-c", str(c), "-o",
+                        str(tmp_path / "t.o")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "ramp_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt, f
+                assert "/root/reference" not in txt, f
+
+
+def test_ops_fail_loudly_without_cuda():
+    import pytest
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    from ramp_b200 import ops
+    from ramp_b200._lib import RampError
+    with pytest.raises(RampError):
+        ops.CloudIndex(torch.zeros(8, 2))
+    from ramp_b200.unet import TemporalUnetInference
+    net = TemporalUnetInference(n_support_points=64, state_dim=4)
+    with pytest.raises(RampError):
+        net.prepare()
