@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(128) attn_forward_kernel(const float* __restri
   }
 }
 static size_t attn_smem(int L, bool bwd) { return sizeof(float) * ((bwd ? 4 : 3) * L * AP + (bwd ? 2 : 1) * L * (L + 1)); }
-int attn_forward(const float* qkv, int n_samples, int L, bf16* out_hi, bf16* out_lo, cudaStream_t s) {
+int attn_forward_generic(const float* qkv, int n_samples, int L, bf16* out_hi, bf16* out_lo, cudaStream_t s) {
   RAMP_CHECK(L <= 64, "attention: L must be <= 64");
   static bool attr = false;
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem(64, false))); attr = true; }
@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(128) attn_backward_kernel(const float* __restr
     store_split(hi, lo, o + 512, dv);
   }
 }
-int attn_backward(const float* qkv, const float* d_out, int n_samples, int L, bf16* dq_hi, bf16* dq_lo, cudaStream_t s) {
+int attn_backward_generic(const float* qkv, const float* d_out, int n_samples, int L, bf16* dq_hi, bf16* dq_lo, cudaStream_t s) {
   RAMP_CHECK(L <= 64, "attention: L must be <= 64");
   static bool attr = false;
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem(64, true))); attr = true; }

@@ -44,6 +44,10 @@ int attn_forward(const float* qkv, int n_samples, int L, bf16* out_hi, bf16* out
 // dqkv hi/lo [rows, 768] from d_out fp32 [rows, 256]
 int attn_backward(const float* qkv, const float* d_out, int n_samples, int L, bf16* dq_hi, bf16* dq_lo, cudaStream_t s);
 
+// any L <= 64 (one CTA per (sample, head), scalar smem loops) — used when L is not 8/16/32/64
+int attn_forward_generic(const float* qkv, int n_samples, int L, bf16* out_hi, bf16* out_lo, cudaStream_t s);
+int attn_backward_generic(const float* qkv, const float* d_out, int n_samples, int L, bf16* dq_hi, bf16* dq_lo, cudaStream_t s);
+
 // GEGLU: u [rows, 2*inner] (a | gate) -> a * gelu(gate)
 int geglu_forward(const float* u, int rows, int inner, bf16* out_hi, bf16* out_lo, cudaStream_t s);
 int geglu_backward(const float* u, const float* dg, int rows, int inner, bf16* du_hi, bf16* du_lo, cudaStream_t s);
