@@ -156,6 +156,8 @@ def run_ours(args):
     # per-kernel-class device time of one more identical step (CUDA events around every engine launch)
     model.model.profile(True)
     resident_step()
+    if args.dump_launches and rank == 0:
+        model.model.profile_dump(args.dump_launches)
     prof_ms, prof_n = model.model.profile(False, fetch=True)
     sampler.join(timeout=2)
 
@@ -260,6 +262,7 @@ def main():
     ap.add_argument("--batch", type=int, default=B_PER_GPU, help="trajectories per GPU")
     ap.add_argument("--max-rows", type=int, default=1792, help="network rows per engine call (workspace size)")
     ap.add_argument("--cpu-sample", type=int, default=2, help="trajectories in the bounded CPU sample")
+    ap.add_argument("--dump-launches", default="", help="write the per-launch CUDA-event CSV of one profiled step here")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -70,6 +70,8 @@ int ramp_unet_energy_grad(void* handle, const float* x, int n_rows, int x_repeat
  * enable != 0 starts recording; a call with ms4_host != NULL synchronises and returns the accumulated
  * milliseconds and launch counts of {tensor-core GEMM, norms, attention core, elementwise} and resets them. */
 int ramp_unet_profile(void* handle, int enable, float* ms4_host, int* launches4_host);
+/* writes one CSV line (class, shape tag, ms) per launch recorded since the last fetch; call BEFORE the fetch */
+int ramp_unet_profile_dump(void* handle, const char* path);
 
 /* ---- fused sampler step (one launch per reverse-diffusion step) --------------------------------
  * eps rows come from ramp_unet_energy_grad; row of (trajectory b, group g) = b*eps_bstride + g*eps_gstride,

@@ -89,4 +89,9 @@ int ramp_unet_profile(void* handle, int enable, float* ms4_host, int* launches4_
   return ((UnetEngine*)handle)->profile(enable, ms4_host, launches4_host);
 }
 
+int ramp_unet_profile_dump(void* handle, const char* path) {
+  RAMP_CHECK(handle && path, "ramp_unet_profile_dump: null argument");
+  return ((UnetEngine*)handle)->profile_dump(path);
+}
+
 }  // extern "C"

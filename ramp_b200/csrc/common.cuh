@@ -108,7 +108,28 @@ struct GemmDesc {
   bf16* out_hi; bf16* out_lo; int ldS;
   int o_L, o_stride, o_off;
   int precision;                // 1: hi*hi only; 3: hi*hi + hi*lo + lo*hi
+  // fused epilogues (EPI_*): the thread that owns an accumulator row also owns the whole output row when
+  // Nout == BN == 256, so LayerNorm and its backward are thread-local; GEGLU pairs (a, gate) live in one tile
+  // because FF1's output channels are packed tile-interleaved (geglu_perm()).
+  int epi;                      // GemmEpi
+  const float* ln_gamma; const float* ln_beta;   // [256]
+  float* ln_stats;              // [rows, 2] (mean, rstd): written by EPI_LN_FWD, read by EPI_LN_BWD
+  const float* ln_x;            // EPI_LN_BWD: the LayerNorm input, fp32 [rows, 256]
+  const float* u;               // EPI_GEGLU_BWD: saved FF1 output, fp32 [rows, 2048] (tile-interleaved)
+  bf16* out2_hi; bf16* out2_lo; int ldS2;   // EPI_LN_FWD: LN(out) planes; EPI_GEGLU_FWD: a * gelu(gate) planes
 };
+enum GemmEpi {
+  EPI_PLAIN = 0,
+  EPI_GEGLU_FWD = 1,   // acc (+bias) = (a | gate) per 256-col tile -> out_f32 = u, out2 = a * gelu(gate) [rows, Nout/2]
+  EPI_GEGLU_BWD = 2,   // acc = d(a*gelu(gate)) [rows, 1024] -> out_hi/lo = du [rows, 2048] (tile-interleaved)
+  EPI_LN_FWD = 3,      // v = acc + bias + bias_tab + residual -> out_f32 = v, out2 = LN(v), ln_stats
+  EPI_LN_BWD = 4       // acc = dLN-output -> out = residual + LN_backward(ln_x, acc)
+};
+// tile-interleaved position of FF1 output channel o (0..2047; a = 0..1023, gate = 1024..2047)
+__host__ __device__ inline int geglu_perm(int o) {
+  const int part = o >> 10, c = o & 1023;
+  return (c >> 7) * 256 + part * 128 + (c & 127);
+}
 int gemm_launch(const GemmDesc& d, cudaStream_t stream);
 int gemm_init();   // resolves cuTensorMapEncodeTiled, sets smem attributes
 

@@ -1,4 +1,4 @@
-// tcgen05 / TMEM / TMA multi-tap split-precision GEMM for sm_100a.
+// tcgen05 / TMEM / TMA multi-tap split-precision GEMM for sm_100a — persistent, epilogue-overlapped.
 //
 // One kernel serves every dense contraction of the score network:
 // linears, 1x1 / k5 / stride-2 / transposed 1-D convolutions and all of their input gradients.
@@ -9,8 +9,15 @@
 // * Operands are bf16 hi/lo planes (value = hi + lo).  precision==3 issues hi*hi + hi*lo + lo*hi
 //   into the same fp32 TMEM accumulator (fp32-equivalent products, error ~2^-17); precision==1 issues
 //   hi*hi only.
+// * Persistent: one CTA per SM walks tiles (n fastest, so co-running CTAs share A tiles in L2).  The
+//   accumulator is double buffered in TMEM (2 x BN columns), so the epilogue of tile i overlaps the
+//   MMAs of tile i+1; the TMA producer runs ahead across tile boundaries through the smem ring.
 // * Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + single-thread tcgen05.mma issuer,
-//   warps 2..5 = epilogue (tcgen05.ld -> bias / per-scene bias / residual -> fp32 and/or hi/lo stores).
+//   warps 2..5 = epilogue.  An epilogue thread owns one accumulator row; global loads / stores are
+//   transposed through a per-warp smem staging tile so that every warp-wide access is row-contiguous.
+// * Fused epilogues (GemmEpi): GEGLU forward / backward, LayerNorm forward / backward (a thread owns the
+//   full 256-channel row when Nout == BN == 256; intermediate values are parked back in TMEM with
+//   tcgen05.st between the statistics pass and the normalisation pass).
 #include "common.cuh"
 #include <cstring>
 #include <mutex>
@@ -23,10 +30,13 @@ static constexpr int BM = 128;
 static constexpr int BK = 64;                 // bf16 elements = 128 B = one SWIZZLE_128B row
 static constexpr int A_TILE_BYTES = BM * BK * 2;
 static constexpr int GEMM_THREADS = 192;
+static constexpr int STG_LD = 36;             // staging row stride (floats): 16 B aligned, conflict-free float4 phases
+static constexpr int STG_BYTES = 4 * 32 * STG_LD * 4;
 
 struct GemmParams {
   int n_samples, L_out, nb;                   // nb = samples per 128-row tile
   int ntaps, kblocks, BN, nplanes, stages;
+  int m_tiles, n_tiles;
   int tap_par[5], tap_joff[5], tap_wrow[5];   // tap_wrow = wtap * Nout
   const float* bias; const float* bias_tab; const int* row2scene; int Nout;
   const float* residual; int ldR;
@@ -34,6 +44,9 @@ struct GemmParams {
   float* out_f32; int ldO;
   bf16* out_hi; bf16* out_lo; int ldS;
   int o_L, o_stride, o_off;
+  int epi;
+  const float* ln_gamma; const float* ln_beta; float* ln_stats; const float* ln_x; const float* u;
+  bf16* out2_hi; bf16* out2_lo; int ldS2;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -111,87 +124,303 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
       : "r"(taddr));
 }
 
-// ---------------------------------------------------------------------------------------------
-// kernel
-// ---------------------------------------------------------------------------------------------
-template <int W>  // W = accumulator columns handled per tcgen05.ld (32, or 16 for BN == 16)
-__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32_t* v, int col0, bool row_ok,
-                                               size_t out_row, int sample) {
-  if (!row_ok) return;
-  float r[W];
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+        "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]),
+        "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]),
+        "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void ld_acc(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  tmem_ld32(taddr, r);
+  tmem_ld_wait();
 #pragma unroll
-  for (int i = 0; i < W; ++i) r[i] = __uint_as_float(v[i]);
-  if (p.bias) {
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void st_acc(uint32_t taddr, const float (&v)[32]) {
+  uint32_t r[32];
 #pragma unroll
-    for (int i = 0; i < W; i += 4) {
-      float4 b = *reinterpret_cast<const float4*>(p.bias + col0 + i);
-      r[i] += b.x; r[i + 1] += b.y; r[i + 2] += b.z; r[i + 3] += b.w;
-    }
+  for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(v[i]);
+  tmem_st32(taddr, r);
+}
+
+// ---------------------------------------------------------------------------------------------
+// epilogue plumbing: a thread owns accumulator row (q*32 + lane) of the tile; for global traffic the
+// warp re-maps to (row = (lane >> 3) + 4 i, 16-byte column group = lane & 7) through its staging tile.
+// ---------------------------------------------------------------------------------------------
+struct EpiCtx {
+  float* stg;              // this warp's staging tile [32][STG_LD]
+  int lane;
+  bool my_ok; size_t my_row; int my_sample;
+  unsigned ok8; size_t row8[8];
+};
+
+// v[32] (this thread's row, columns col0..col0+31) -> base[row * ld + col0 ..] for every live row of the warp
+__device__ __forceinline__ void chunk_store_f32(const EpiCtx& e, const float (&v)[32], float* base, int ld, int col0) {
+  float* srow = e.stg + e.lane * STG_LD;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) *reinterpret_cast<float4*>(srow + 4 * k) = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+  __syncwarp();
+  const int rsub = e.lane >> 3, c4 = e.lane & 7;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 t = *reinterpret_cast<const float4*>(e.stg + (rsub + 4 * i) * STG_LD + 4 * c4);
+    if ((e.ok8 >> i) & 1u) *reinterpret_cast<float4*>(base + e.row8[i] * ld + col0 + 4 * c4) = t;
   }
+  __syncwarp();
+}
+// same, as bf16 hi / lo planes (ld, col0 in bf16 elements)
+__device__ __forceinline__ void chunk_store_split(const EpiCtx& e, const float (&v)[32], bf16* hi, bf16* lo, int ld, int col0) {
+  uint32_t* srow = reinterpret_cast<uint32_t*>(e.stg) + e.lane * STG_LD;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      bf16 h0, l0, h1, l1;
+      split_bf16(v[8 * k + 2 * j], h0, l0);
+      split_bf16(v[8 * k + 2 * j + 1], h1, l1);
+      h[j] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+      l[j] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+    }
+    *reinterpret_cast<uint4*>(srow + 4 * k) = make_uint4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<uint4*>(srow + 16 + 4 * k) = make_uint4(l[0], l[1], l[2], l[3]);
+  }
+  __syncwarp();
+  const int rsub = e.lane >> 3, c4 = e.lane & 7;
+  bf16* plane = (c4 < 4) ? hi : lo;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const uint4 t = *reinterpret_cast<const uint4*>(reinterpret_cast<uint32_t*>(e.stg) + (rsub + 4 * i) * STG_LD + 4 * c4);
+    if ((e.ok8 >> i) & 1u) *reinterpret_cast<uint4*>(plane + e.row8[i] * ld + col0 + 8 * (c4 & 3)) = t;
+  }
+  __syncwarp();
+}
+// base[row * ld + col0 ..] -> v[32] for this thread's row (zeros for dead rows)
+__device__ __forceinline__ void chunk_load_f32(const EpiCtx& e, const float* __restrict__ base, int ld, int col0, float (&v)[32]) {
+  const int rsub = e.lane >> 3, c4 = e.lane & 7;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    if ((e.ok8 >> i) & 1u) t = *reinterpret_cast<const float4*>(base + e.row8[i] * ld + col0 + 4 * c4);
+    *reinterpret_cast<float4*>(e.stg + (rsub + 4 * i) * STG_LD + 4 * c4) = t;
+  }
+  __syncwarp();
+  const float* srow = e.stg + e.lane * STG_LD;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const float4 t = *reinterpret_cast<const float4*>(srow + 4 * k);
+    v[4 * k] = t.x; v[4 * k + 1] = t.y; v[4 * k + 2] = t.z; v[4 * k + 3] = t.w;
+  }
+  __syncwarp();
+}
+__device__ __forceinline__ void add_vec32(float (&v)[32], const float* __restrict__ b) {
+#pragma unroll
+  for (int i = 0; i < 32; i += 4) {
+    const float4 t = *reinterpret_cast<const float4*>(b + i);
+    v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
+  }
+}
+// acc + bias + per-scene bias + residual(s) for columns col .. col+31
+__device__ __forceinline__ void epi_affine(const GemmParams& p, const EpiCtx& e, float (&v)[32], int col) {
+  if (p.bias) add_vec32(v, p.bias + col);
+  if (p.bias_tab && e.my_ok) add_vec32(v, p.bias_tab + (size_t)p.row2scene[e.my_sample] * p.Nout + col);
+  if (p.residual) { float r[32]; chunk_load_f32(e, p.residual, p.ldR, col, r);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += r[i]; }
+  if (p.residual2) { float r[32]; chunk_load_f32(e, p.residual2, p.ldR2, col, r);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += r[i]; }
+}
+
+// ---- one tile's epilogue, by mode.  acc = TMEM address of this warp's lane quarter, column 0 of the tile ----
+__device__ __forceinline__ void epi_plain(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
+  for (int c = 0; c < p.BN; c += 32) {
+    float v[32];
+    ld_acc(acc + c, v);
+    epi_affine(p, e, v, colbase + c);
+    if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, colbase + c);
+    if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, colbase + c);
+  }
+}
+// BN == 16 tiles (Nout == 16): tiny outputs, direct per-row stores
+__device__ __forceinline__ void epi_plain16(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
+  uint32_t r[16];
+  tmem_ld16(acc, r);
+  tmem_ld_wait();
+  if (!e.my_ok) return;
+  float v[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+  if (p.bias)
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] += p.bias[colbase + i];
   if (p.bias_tab) {
-    const float* bt = p.bias_tab + (size_t)p.row2scene[sample] * p.Nout + col0;
+    const float* bt = p.bias_tab + (size_t)p.row2scene[e.my_sample] * p.Nout + colbase;
 #pragma unroll
-    for (int i = 0; i < W; i += 4) {
-      float4 b = *reinterpret_cast<const float4*>(bt + i);
-      r[i] += b.x; r[i + 1] += b.y; r[i + 2] += b.z; r[i + 3] += b.w;
-    }
+    for (int i = 0; i < 16; ++i) v[i] += bt[i];
   }
-  if (p.residual) {
-    const float* rs = p.residual + out_row * p.ldR + col0;
+  if (p.residual)
 #pragma unroll
-    for (int i = 0; i < W; i += 4) {
-      float4 b = *reinterpret_cast<const float4*>(rs + i);
-      r[i] += b.x; r[i + 1] += b.y; r[i + 2] += b.z; r[i + 3] += b.w;
-    }
-  }
-  if (p.residual2) {
-    const float* rs = p.residual2 + out_row * p.ldR2 + col0;
+    for (int i = 0; i < 16; ++i) v[i] += p.residual[e.my_row * p.ldR + colbase + i];
+  if (p.residual2)
 #pragma unroll
-    for (int i = 0; i < W; i += 4) {
-      float4 b = *reinterpret_cast<const float4*>(rs + i);
-      r[i] += b.x; r[i + 1] += b.y; r[i + 2] += b.z; r[i + 3] += b.w;
-    }
-  }
+    for (int i = 0; i < 16; ++i) v[i] += p.residual2[e.my_row * p.ldR2 + colbase + i];
   if (p.out_f32) {
-    float* o = p.out_f32 + out_row * p.ldO + col0;
+    float* o = p.out_f32 + e.my_row * p.ldO + colbase;
 #pragma unroll
-    for (int i = 0; i < W; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+    for (int i = 0; i < 16; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
   }
   if (p.out_hi) {
-    bf16* oh = p.out_hi + out_row * p.ldS + col0;
-    bf16* ol = p.out_lo + out_row * p.ldS + col0;
+    __align__(16) bf16 h[16];
+    __align__(16) bf16 l[16];
 #pragma unroll
-    for (int i = 0; i < W; i += 8) {
-      __align__(16) bf16 h[8];
-      __align__(16) bf16 l[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) split_bf16(r[i + j], h[j], l[j]);
-      *reinterpret_cast<uint4*>(oh + i) = *reinterpret_cast<const uint4*>(h);
-      *reinterpret_cast<uint4*>(ol + i) = *reinterpret_cast<const uint4*>(l);
+    for (int i = 0; i < 16; ++i) split_bf16(v[i], h[i], l[i]);
+    bf16* oh = p.out_hi + e.my_row * p.ldS + colbase;
+    bf16* ol = p.out_lo + e.my_row * p.ldS + colbase;
+    *reinterpret_cast<uint4*>(oh) = *reinterpret_cast<const uint4*>(h);
+    *reinterpret_cast<uint4*>(oh + 8) = *reinterpret_cast<const uint4*>(h + 8);
+    *reinterpret_cast<uint4*>(ol) = *reinterpret_cast<const uint4*>(l);
+    *reinterpret_cast<uint4*>(ol + 8) = *reinterpret_cast<const uint4*>(l + 8);
+  }
+}
+// GEGLU forward (layers_attention_mini.py:38-45): tile columns [0,128) = a, [128,256) = gate
+__device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int tile_n) {
+  const int colbase = tile_n * 256;
+  for (int c = 0; c < 128; c += 32) {
+    float a[32], g[32];
+    ld_acc(acc + c, a);
+    ld_acc(acc + 128 + c, g);
+    if (p.bias) { add_vec32(a, p.bias + colbase + c); add_vec32(g, p.bias + colbase + 128 + c); }
+    if (p.out_f32) {
+      chunk_store_f32(e, a, p.out_f32, p.ldO, colbase + c);
+      chunk_store_f32(e, g, p.out_f32, p.ldO, colbase + 128 + c);
     }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) a[i] *= gelu_f(g[i]);
+    chunk_store_split(e, a, p.out2_hi, p.out2_lo, p.ldS2, tile_n * 128 + c);
+  }
+}
+// GEGLU backward: acc = d(a * gelu(gate)) for natural columns colbase + c; u and du are tile-interleaved
+__device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
+  for (int c = 0; c < p.BN; c += 32) {
+    float d[32], a[32], g[32];
+    ld_acc(acc + c, d);
+    const int j = colbase + c;
+    const int pa = (j >> 7) * 256 + (j & 127), pg = pa + 128;
+    chunk_load_f32(e, p.u, 2048, pa, a);
+    chunk_load_f32(e, p.u, 2048, pg, g);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float da = d[i] * gelu_f(g[i]);
+      g[i] = d[i] * a[i] * gelu_grad_f(g[i]);
+      a[i] = da;
+    }
+    chunk_store_split(e, a, p.out_hi, p.out_lo, p.ldS, pa);
+    chunk_store_split(e, g, p.out_hi, p.out_lo, p.ldS, pg);
+  }
+}
+// LayerNorm forward over the 256 channels of the row this thread owns (eps 1e-5, layers_attention_mini.py:138-140)
+__device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc) {
+  float shift = 0.f, s = 0.f, ss = 0.f;
+  for (int c = 0; c < 256; c += 32) {
+    float v[32];
+    ld_acc(acc + c, v);
+    epi_affine(p, e, v, c);
+    if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, c);
+    if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, c);
+    st_acc(acc + c, v);
+    if (c == 0) shift = v[0];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) { const float d = v[i] - shift; s += d; ss = fmaf(d, d, ss); }
+  }
+  tmem_st_wait();
+  const float m0 = s * (1.f / 256.f);
+  const float mean = shift + m0;
+  const float rstd = rsqrtf(fmaxf(ss * (1.f / 256.f) - m0 * m0, 0.f) + 1e-5f);
+  if (p.ln_stats && e.my_ok) *reinterpret_cast<float2*>(p.ln_stats + e.my_row * 2) = make_float2(mean, rstd);
+  for (int c = 0; c < 256; c += 32) {
+    float v[32];
+    ld_acc(acc + c, v);
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 g = *reinterpret_cast<const float4*>(p.ln_gamma + c + i);
+      const float4 b = *reinterpret_cast<const float4*>(p.ln_beta + c + i);
+      v[i] = (v[i] - mean) * rstd * g.x + b.x; v[i + 1] = (v[i + 1] - mean) * rstd * g.y + b.y;
+      v[i + 2] = (v[i + 2] - mean) * rstd * g.z + b.z; v[i + 3] = (v[i + 3] - mean) * rstd * g.w + b.w;
+    }
+    chunk_store_split(e, v, p.out2_hi, p.out2_lo, p.ldS2, c);
+  }
+}
+// out = residual + LayerNorm_backward(ln_x, acc): dx = rstd * (dyh - mean(dyh) - xh * mean(dyh * xh)), dyh = acc * gamma
+__device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc) {
+  float mean = 0.f, rstd = 0.f;
+  if (e.my_ok) { const float2 st = *reinterpret_cast<const float2*>(p.ln_stats + e.my_row * 2); mean = st.x; rstd = st.y; }
+  float s1 = 0.f, s2 = 0.f;
+  for (int c = 0; c < 256; c += 32) {
+    float d[32], x[32];
+    ld_acc(acc + c, d);
+    chunk_load_f32(e, p.ln_x, 256, c, x);
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 g = *reinterpret_cast<const float4*>(p.ln_gamma + c + i);
+      d[i] *= g.x; d[i + 1] *= g.y; d[i + 2] *= g.z; d[i + 3] *= g.w;
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) { s1 += d[i]; s2 = fmaf(d[i], (x[i] - mean) * rstd, s2); }
+    st_acc(acc + c, d);
+  }
+  tmem_st_wait();
+  s1 *= (1.f / 256.f); s2 *= (1.f / 256.f);
+  for (int c = 0; c < 256; c += 32) {
+    float d[32], x[32];
+    ld_acc(acc + c, d);
+    chunk_load_f32(e, p.ln_x, 256, c, x);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) d[i] = rstd * (d[i] - s1 - (x[i] - mean) * rstd * s2);
+    if (p.residual) { chunk_load_f32(e, p.residual, p.ldR, c, x);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) d[i] += x[i]; }
+    if (p.out_f32) chunk_store_f32(e, d, p.out_f32, p.ldO, c);
+    if (p.out_hi) chunk_store_split(e, d, p.out_hi, p.out_lo, p.ldS, c);
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// kernel
+// ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant__ CUtensorMap mapAlo,
                const __grid_constant__ CUtensorMap mapBhi, const __grid_constant__ CUtensorMap mapBlo,
                const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b_tile_bytes = p.BN * BK * 2;
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + b_tile_bytes);
-  const uint32_t bar_base = smem_base + p.stages * stage_bytes;   // full[s], empty[s], tmem_full, tmem_ptr
-  const uint32_t full0 = bar_base, empty0 = bar_base + 8 * p.stages, tmem_full = bar_base + 16 * p.stages;
-  const uint32_t tmem_slot = tmem_full + 8;
+  const uint32_t stg_base = smem_base + p.stages * stage_bytes;            // 4 x [32][STG_LD] floats
+  const uint32_t bar_base = stg_base + STG_BYTES;
+  const uint32_t full0 = bar_base, empty0 = bar_base + 8 * p.stages;
+  const uint32_t tfull0 = bar_base + 16 * p.stages, tempty0 = tfull0 + 16;  // 2 + 2 accumulator barriers
+  const uint32_t tmem_slot = tempty0 + 16;
   const int iters = p.ntaps * p.kblocks;
-  const int tile_m = blockIdx.x, tile_n = blockIdx.y;
+  const int total_tiles = p.m_tiles * p.n_tiles;
   uint32_t tmem_cols = 32;
-  while ((int)tmem_cols < p.BN) tmem_cols <<= 1;
+  while ((int)tmem_cols < 2 * p.BN) tmem_cols <<= 1;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-    mbar_init(tmem_full, 1);
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull0 + 8 * b, 1); mbar_init(tempty0 + 8 * b, 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAhi) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBhi) : "memory");
@@ -211,21 +440,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
     // ---------------- TMA producer ----------------
     if (lane == 0) {
       int it = 0;
-      for (int t = 0; t < p.ntaps; ++t) {
-        for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (it / p.stages) & 1;
-          mbar_wait(empty0 + 8 * s, ph ^ 1);
-          const uint32_t st = smem_base + s * stage_bytes;
-          const uint32_t fb = full0 + 8 * s;
-          mbar_expect_tx(fb, (uint32_t)(p.nplanes * (p.nb * p.L_out * BK * 2 + b_tile_bytes)));
-          const int c3 = tile_m * p.nb;
-          tma_load_4d(st, &mapAhi, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3);
-          uint32_t off = A_TILE_BYTES;
-          if (p.nplanes == 2) { tma_load_4d(st + off, &mapAlo, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3); off += A_TILE_BYTES; }
-          tma_load_2d(st + off, &mapBhi, fb, kb * BK, p.tap_wrow[t] + tile_n * p.BN);
-          off += b_tile_bytes;
-          if (p.nplanes == 2) tma_load_2d(st + off, &mapBlo, fb, kb * BK, p.tap_wrow[t] + tile_n * p.BN);
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
+        const int c3 = tile_m * p.nb;
+        for (int t = 0; t < p.ntaps; ++t) {
+          for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
+            const int s = it % p.stages;
+            const uint32_t ph = (it / p.stages) & 1;
+            mbar_wait(empty0 + 8 * s, ph ^ 1);
+            const uint32_t st = smem_base + s * stage_bytes;
+            const uint32_t fb = full0 + 8 * s;
+            mbar_expect_tx(fb, (uint32_t)(p.nplanes * (p.nb * p.L_out * BK * 2 + b_tile_bytes)));
+            tma_load_4d(st, &mapAhi, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3);
+            uint32_t off = A_TILE_BYTES;
+            if (p.nplanes == 2) { tma_load_4d(st + off, &mapAlo, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3); off += A_TILE_BYTES; }
+            tma_load_2d(st + off, &mapBhi, fb, kb * BK, p.tap_wrow[t] + tile_n * p.BN);
+            off += b_tile_bytes;
+            if (p.nplanes == 2) tma_load_2d(st + off, &mapBlo, fb, kb * BK, p.tap_wrow[t] + tile_n * p.BN);
+          }
         }
       }
     }
@@ -234,61 +466,83 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
     if (lane == 0) {
       // instruction descriptor: D=f32, A=B=bf16, both K-major, N = BN, M = 128
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-      for (int it = 0; it < iters; ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (it / p.stages) & 1;
-        mbar_wait(full0 + 8 * s, ph);
+      int it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        const int buf = lt & 1;
+        mbar_wait(tempty0 + 8 * buf, ((lt >> 1) & 1) ^ 1);      // epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t st = smem_base + s * stage_bytes;
-        const uint32_t a_hi = st;
-        const uint32_t a_lo = st + A_TILE_BYTES;
-        const uint32_t b_hi = st + p.nplanes * A_TILE_BYTES;
-        const uint32_t b_lo = b_hi + b_tile_bytes;
+        const uint32_t dacc = tmem_acc + (uint32_t)(buf * p.BN);
+        for (int i = 0; i < iters; ++i, ++it) {
+          const int s = it % p.stages;
+          const uint32_t ph = (it / p.stages) & 1;
+          mbar_wait(full0 + 8 * s, ph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t st = smem_base + s * stage_bytes;
+          const uint32_t a_hi = st;
+          const uint32_t a_lo = st + A_TILE_BYTES;
+          const uint32_t b_hi = st + p.nplanes * A_TILE_BYTES;
+          const uint32_t b_lo = b_hi + b_tile_bytes;
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint32_t ko = k * 32;   // 16 bf16 = 32 B inside the 128 B swizzle row
-          const uint32_t first = (it == 0 && k == 0) ? 0u : 1u;
-          if (p.nplanes == 2) {
-            umma_bf16(tmem_acc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc, first);
-            umma_bf16(tmem_acc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc, 1u);
-            umma_bf16(tmem_acc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, 1u);
-          } else {
-            umma_bf16(tmem_acc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, first);
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint32_t ko = k * 32;   // 16 bf16 = 32 B inside the 128 B swizzle row
+            const uint32_t first = (i == 0 && k == 0) ? 0u : 1u;
+            if (p.nplanes == 2) {
+              umma_bf16(dacc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc, first);
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc, 1u);
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, 1u);
+            } else {
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, first);
+            }
           }
+          umma_commit(empty0 + 8 * s);           // frees the smem stage when these MMAs retire
         }
-        umma_commit(empty0 + 8 * s);           // frees the smem stage when these MMAs retire
+        umma_commit(tfull0 + 8 * buf);            // accumulator complete
       }
-      umma_commit(tmem_full);                   // accumulator complete
     }
   } else {
     // ---------------- epilogue (warps 2..5 -> TMEM lane quarters 2,3,0,1) ----------------
     const int q = warp & 3;
-    mbar_wait(tmem_full, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int r = q * 32 + lane;
-    const int n_local = r / p.L_out, l = r - n_local * p.L_out;
-    const int sample = tile_m * p.nb + n_local;
-    const bool row_ok = n_local < p.nb && sample < p.n_samples;
-    const size_t out_row = (size_t)sample * p.o_L + (size_t)l * p.o_stride + p.o_off;
-    const uint32_t taddr = tmem_acc + ((uint32_t)(q * 32) << 16);
-    const int colbase = tile_n * p.BN;
-    if (p.BN >= 32) {
-      for (int c = 0; c < p.BN; c += 32) {
-        uint32_t v[32];
-        tmem_ld32(taddr + c, v);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        epilogue_chunk<32>(p, v, colbase + c, row_ok, out_row, sample);
+    EpiCtx e;
+    e.lane = lane;
+    e.stg = reinterpret_cast<float*>(smem_gen + p.stages * stage_bytes) + q * 32 * STG_LD;
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
+      const int buf = lt & 1;
+      {
+        const int r = q * 32 + lane;
+        const int n_local = r / p.L_out, l = r - n_local * p.L_out;
+        e.my_sample = tile_m * p.nb + n_local;
+        e.my_ok = n_local < p.nb && e.my_sample < p.n_samples;
+        e.my_row = (size_t)e.my_sample * p.o_L + (size_t)l * p.o_stride + p.o_off;
+        e.ok8 = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = q * 32 + (lane >> 3) + 4 * i;
+          const int nl = rr / p.L_out, ll = rr - nl * p.L_out;
+          const int smp = tile_m * p.nb + nl;
+          if (nl < p.nb && smp < p.n_samples) e.ok8 |= 1u << i;
+          e.row8[i] = (size_t)smp * p.o_L + (size_t)ll * p.o_stride + p.o_off;
+        }
       }
-    } else {
-      uint32_t v[16];
-      tmem_ld16(taddr, v);
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      epilogue_chunk<16>(p, v, colbase, row_ok, out_row, sample);
+      mbar_wait(tfull0 + 8 * buf, (lt >> 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t acc = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);
+      if (p.BN == 16) epi_plain16(p, e, acc, tile_n * 16);
+      else if (p.epi == EPI_PLAIN) epi_plain(p, e, acc, tile_n * p.BN);
+      else if (p.epi == EPI_GEGLU_FWD) epi_geglu_fwd(p, e, acc, tile_n);
+      else if (p.epi == EPI_GEGLU_BWD) epi_geglu_bwd(p, e, acc, tile_n * p.BN);
+      else if (p.epi == EPI_LN_FWD) epi_ln_fwd(p, e, acc);
+      else epi_ln_bwd(p, e, acc);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(tmem_cols) : "memory");
   }
 }
@@ -301,6 +555,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn g_encode = nullptr;
 static int g_max_smem = 0;
+static int g_num_sms = 148;
 
 int gemm_init() {
   if (g_encode) return 0;
@@ -311,6 +566,7 @@ int gemm_init() {
   int dev = 0;
   RAMP_CUDA_OK(cudaGetDevice(&dev));
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, g_max_smem));
   g_encode = (EncodeTiledFn)fn;
   return 0;
@@ -360,15 +616,16 @@ static int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t*
   return 0;
 }
 
+
 static int pick_bn(int Nout, int m_tiles) {
-  // Largest tile that divides Nout; prefer >= 2 waves of 148 CTAs when the problem allows it.
+  // Largest tile that divides Nout; drop to smaller tiles only while the grid would leave SMs idle.
   const int cands[5] = {256, 128, 64, 32, 16};
   int best = 0;
   for (int i = 0; i < 5; ++i) {
     int bn = cands[i];
     if (Nout % bn) continue;
     if (!best) best = bn;
-    if ((long)m_tiles * (Nout / bn) >= 2 * 148 || bn <= 64) return bn;
+    if ((long)m_tiles * (Nout / bn) >= g_num_sms || bn <= 64) return bn;
   }
   return best;
 }
@@ -381,17 +638,35 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   RAMP_CHECK(d.ntaps >= 1 && d.ntaps <= 5, "gemm: 1..5 taps");
   RAMP_CHECK(d.precision == 1 || d.precision == 3, "gemm: precision must be 1 or 3");
   RAMP_CHECK(d.L_in % d.a_pstride == 0, "gemm: L_in must be a multiple of a_pstride");
+  RAMP_CHECK(d.epi >= EPI_PLAIN && d.epi <= EPI_LN_BWD, "gemm: unknown epilogue");
   GemmParams p;
   std::memset(&p, 0, sizeof(p));
   p.n_samples = d.n_samples; p.L_out = d.L_out; p.nb = BM / d.L_out;
   p.ntaps = d.ntaps; p.kblocks = (d.K + BK - 1) / BK;
-  const int m_tiles = (d.n_samples + p.nb - 1) / p.nb;
-  p.BN = pick_bn(d.Nout, m_tiles);
+  p.m_tiles = (d.n_samples + p.nb - 1) / p.nb;
+  p.BN = pick_bn(d.Nout, p.m_tiles);
+  p.epi = d.epi;
+  if (d.epi == EPI_GEGLU_FWD) {
+    RAMP_CHECK(d.Nout % 256 == 0 && d.out2_hi && d.out2_lo, "gemm: GEGLU forward needs Nout % 256 == 0 and out2 planes");
+    p.BN = 256;
+  } else if (d.epi == EPI_GEGLU_BWD) {
+    RAMP_CHECK(d.Nout % 128 == 0 && d.u && d.out_hi && d.out_lo, "gemm: GEGLU backward needs Nout % 128 == 0, u and out planes");
+    if (p.BN < 32) p.BN = 128;
+  } else if (d.epi == EPI_LN_FWD) {
+    RAMP_CHECK(d.Nout == 256 && d.ln_gamma && d.ln_beta && d.out2_hi && d.out2_lo, "gemm: LN forward needs Nout == 256, gamma/beta, out2 planes");
+    p.BN = 256;
+  } else if (d.epi == EPI_LN_BWD) {
+    RAMP_CHECK(d.Nout == 256 && d.ln_gamma && d.ln_stats && d.ln_x, "gemm: LN backward needs Nout == 256, gamma, stats, ln_x");
+    p.BN = 256;
+  }
+  p.n_tiles = d.Nout / p.BN;
   p.nplanes = d.precision == 3 ? 2 : 1;
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + p.BN * BK * 2);
-  int stages = (g_max_smem - 2048) / stage_bytes;
-  if (stages > 4) stages = 4;
-  if (stages > p.ntaps * p.kblocks) stages = p.ntaps * p.kblocks;
+  const int fixed = 1024 + STG_BYTES + 256;
+  int stages = (g_max_smem - fixed) / stage_bytes;
+  if (stages > 6) stages = 6;
+  const long total_iters = (long)p.ntaps * p.kblocks * ((long)p.m_tiles * p.n_tiles + g_num_sms - 1) / g_num_sms;
+  if (stages > total_iters) stages = (int)total_iters;
   RAMP_CHECK(stages >= 1, "gemm: tile does not fit shared memory");
   p.stages = stages;
   for (int t = 0; t < d.ntaps; ++t) {
@@ -401,6 +676,10 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   p.residual = d.residual; p.ldR = d.ldR; p.residual2 = d.residual2; p.ldR2 = d.ldR2; p.out_f32 = d.out_f32; p.ldO = d.ldO;
   p.out_hi = d.out_hi; p.out_lo = d.out_lo; p.ldS = d.ldS;
   p.o_L = d.o_L; p.o_stride = d.o_stride; p.o_off = d.o_off;
+  p.ln_gamma = d.ln_gamma; p.ln_beta = d.ln_beta; p.ln_stats = d.ln_stats; p.ln_x = d.ln_x; p.u = d.u;
+  p.out2_hi = d.out2_hi; p.out2_lo = d.out2_lo; p.ldS2 = d.ldS2;
+  RAMP_CHECK(p.BN == 16 || ((d.ldO % 4 == 0) && (d.ldS % 8 == 0) && (d.ldR % 4 == 0) && (d.ldR2 % 4 == 0) && (d.ldS2 % 8 == 0)),
+             "gemm: output / residual leading dimensions must keep 16-byte alignment");
 
   CUtensorMap mAhi, mAlo, mBhi, mBlo;
   {
@@ -417,8 +696,9 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
     if (make_map(&mBhi, d.w_hi, 2, dims, str, box)) return -3;
     if (p.nplanes == 2) { if (make_map(&mBlo, d.w_lo, 2, dims, str, box)) return -3; } else mBlo = mBhi;
   }
-  const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
-  dim3 grid(m_tiles, d.Nout / p.BN);
+  const size_t smem = (size_t)stages * stage_bytes + fixed;
+  const long tiles = (long)p.m_tiles * p.n_tiles;
+  dim3 grid((unsigned)(tiles < g_num_sms ? tiles : g_num_sms));
   gemm_tc_kernel<<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p);
   RAMP_LAUNCH_OK();
   return 0;

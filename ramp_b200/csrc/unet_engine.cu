@@ -1,6 +1,7 @@
 // See unet_engine.cuh.  Part 1: parameters, weight packing, workspace.
 #include "unet_engine.cuh"
 #include "unet_ops.cuh"
+#include <cstdarg>
 
 namespace ramp {
 
@@ -55,7 +56,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ src, bf16* hi, bf16
 }
 
 int UnetEngine::pack(PackedW& w, const std::string& name, int T, int Nd, int Kd, int Ns, int Ks, long st, long sn,
-                     long sk, int noff, int koff, bool alloc) {
+                     long sk, int noff, int koff, bool alloc, long src_off, size_t full_numel) {
   if (alloc) {
     const size_t n = (size_t)T * Nd * Kd;
     w.hi = (bf16*)dev_alloc(n * 2);
@@ -63,8 +64,9 @@ int UnetEngine::pack(PackedW& w, const std::string& name, int T, int Nd, int Kd,
     RAMP_CHECK(w.hi && w.lo, "cudaMalloc failed while packing " + name);
     w.ntaps = T; w.Nout = Nd; w.Kw = Kd; w.K = Kd;
   }
-  const float* src = P(name, (size_t)0 + (size_t)T * Ns * Ks);
+  const float* src = P(name, full_numel ? full_numel : (size_t)T * Ns * Ks);
   if (!src) return 0;   // reported by finalize()
+  src += src_off;
   const long total = (long)T * Ns * Ks;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 1184) blocks = 1184;
@@ -137,13 +139,33 @@ int UnetEngine::load_st(STW& st, const std::string& p, int C) {
     }
     rc = pack(t.o_f, q + "attn1.to_out.0.weight", 1, 256, 256, 256, 256, 0, 256, 1); if (rc) return rc;
     rc = pack(t.o_b, q + "attn1.to_out.0.weight", 1, 256, 256, 256, 256, 0, 1, 256); if (rc) return rc;
-    rc = pack(t.ff1_f, q + "ff.net.0.proj.weight", 1, 2048, 256, 2048, 256, 0, 256, 1); if (rc) return rc;
-    rc = pack(t.ff1_b, q + "ff.net.0.proj.weight", 1, 256, 2048, 256, 2048, 0, 1, 256); if (rc) return rc;
+    // FF1 (GEGLU projection, 256 -> a[1024] | gate[1024]) is packed tile-interleaved (geglu_perm): every 256-column
+    // output tile holds 128 a-channels and their 128 gates, so the GEGLU is applied in the GEMM epilogue.
+    for (int part = 0; part < 2; ++part)
+      for (int tl = 0; tl < 8; ++tl) {
+        const int n0 = part * 1024 + tl * 128, d0 = tl * 256 + part * 128;
+        const bool first = part == 0 && tl == 0;
+        rc = pack(t.ff1_f, q + "ff.net.0.proj.weight", 1, 2048, 256, 128, 256, 0, 256, 1, d0, 0, first, (long)n0 * 256, (size_t)2048 * 256);
+        if (rc) return rc;
+        rc = pack(t.ff1_b, q + "ff.net.0.proj.weight", 1, 256, 2048, 256, 128, 0, 1, 256, 0, d0, first, (long)n0 * 256, (size_t)2048 * 256);
+        if (rc) return rc;
+      }
     rc = pack(t.ff2_f, q + "ff.net.2.weight", 1, 256, 1024, 256, 1024, 0, 1024, 1); if (rc) return rc;
     rc = pack(t.ff2_b, q + "ff.net.2.weight", 1, 1024, 256, 1024, 256, 0, 1, 1024); if (rc) return rc;
     t.ln1g = P(q + "norm1.weight", 256); t.ln1b = P(q + "norm1.bias", 256);
     t.ln3g = P(q + "norm3.weight", 256); t.ln3b = P(q + "norm3.bias", 256);
-    t.ff1_bias = P(q + "ff.net.0.proj.bias", 2048); t.ff2_bias = P(q + "ff.net.2.bias", 256);
+    t.ff2_bias = P(q + "ff.net.2.bias", 256);
+    {
+      const float* b = P(q + "ff.net.0.proj.bias", 2048);
+      float* bp = (float*)dev_alloc(2048 * sizeof(float));
+      RAMP_CHECK(bp, "cudaMalloc failed");
+      if (b)
+        for (int part = 0; part < 2; ++part)
+          for (int tl = 0; tl < 8; ++tl)
+            RAMP_CUDA_OK(cudaMemcpy(bp + tl * 256 + part * 128, b + part * 1024 + tl * 128, 128 * sizeof(float),
+                                    cudaMemcpyDeviceToDevice));
+      t.ff1_bias = bp;
+    }
     // touched so that a checkpoint lacking them is reported: unused by the math (single-key softmax == 1)
     P(q + "attn2.to_q.weight", 256 * 256); P(q + "attn2.to_k.weight", (size_t)256 * cfg_.ctx_dim);
     P(q + "norm2.weight", 256); P(q + "norm2.bias", 256);
@@ -295,10 +317,34 @@ UnetEngine::ProfScope::ProfScope(UnetEngine* eng, int cat) : e(eng), idx(-1) {
   }
   idx = (int)e->prof_used_++;
   e->prof_events_[idx].cat = cat;
+  e->prof_events_[idx].tag[0] = 0;
   cudaEventRecord(e->prof_events_[idx].a, e->s_);
 }
 UnetEngine::ProfScope::~ProfScope() {
   if (idx >= 0) cudaEventRecord(e->prof_events_[idx].b, e->s_);
+}
+
+void UnetEngine::ProfScope::tag(const char* fmt, ...) {
+  if (idx < 0) return;
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(e->prof_events_[idx].tag, sizeof(e->prof_events_[idx].tag), fmt, ap);
+  va_end(ap);
+}
+
+int UnetEngine::profile_dump(const char* path) {
+  RAMP_CUDA_OK(cudaDeviceSynchronize());
+  FILE* f = fopen(path, "w");
+  RAMP_CHECK(f != nullptr, "profile_dump: cannot open file");
+  static const char* names[4] = {"gemm", "norm", "attention", "elementwise"};
+  fprintf(f, "class,tag,ms\n");
+  for (size_t i = 0; i < prof_used_; ++i) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, prof_events_[i].a, prof_events_[i].b);
+    fprintf(f, "%s,%s,%.6f\n", names[prof_events_[i].cat & 3], prof_events_[i].tag, ms);
+  }
+  fclose(f);
+  return 0;
 }
 
 int UnetEngine::profile(int enable, float* ms4, int* launches4) {

@@ -30,7 +30,7 @@ struct ResW {
 };
 struct TBlockW {
   PackedW qkv_f, qkv_b, o_f, o_b, ff1_f, ff1_b, ff2_f, ff2_b;
-  const float *ln1g, *ln1b, *ln3g, *ln3b, *ff1_bias, *ff2_bias;
+  const float *ln1g, *ln1b, *ln3g, *ln3b, *ff1_bias, *ff2_bias;   // ff1_bias: tile-interleaved copy (geglu_perm)
   float* bias_tab = nullptr;   // [max_scenes, 256]: attn1.to_out bias + collapsed attn2 output per scene
 };
 struct STW {
@@ -39,7 +39,12 @@ struct STW {
 
 // forward activations kept for the backward sweep
 struct ResSave { float* c1; float* c2; };
-struct TBlockSave { float* zin; float* qkv; float* z1; float* u; };
+struct TBlockSave { float* zin; float* qkv; float* z1; float* u; float* stats1; float* stats3; };   // stats: (mean, rstd) per token
+struct GemmFuse {      // fused-epilogue request for UnetEngine::gemm (see GemmEpi in common.cuh)
+  int epi = EPI_PLAIN;
+  const float* ln_gamma = nullptr; const float* ln_beta = nullptr; float* ln_stats = nullptr; const float* ln_x = nullptr;
+  const float* u = nullptr; bf16* out2_hi = nullptr; bf16* out2_lo = nullptr; int ldS2 = 0;
+};
 struct STSave { const float* x; int ldx; TBlockSave blk[2]; };
 
 class UnetEngine {
@@ -54,6 +59,7 @@ class UnetEngine {
                   float* f_out, cudaStream_t s);
   size_t workspace_bytes() const { return arena_bytes_; }
   int profile(int enable, float* ms4, int* launches4);
+  int profile_dump(const char* path);   // per-launch CSV (class, tag, ms) of the events recorded since the last fetch
   const UnetConfig& cfg() const { return cfg_; }
 
  private:
@@ -83,7 +89,7 @@ class UnetEngine {
   // helpers
   const float* P(const std::string& name, size_t numel);
   int pack(PackedW& w, const std::string& name, int T, int Nd, int Kd, int Ns, int Ks, long st, long sn, long sk,
-           int noff = 0, int koff = 0, bool alloc = true);
+           int noff = 0, int koff = 0, bool alloc = true, long src_off = 0, size_t full_numel = 0);
   int load_conv(ConvW& c, const std::string& prefix, int cin, int cout, int kw, bool transposed = false);
   int load_res(ResW& r, const std::string& prefix, int cin, int cout, int cin_true);
   int load_st(STW& st, const std::string& prefix, int C);
@@ -103,7 +109,8 @@ class UnetEngine {
           cudaStream_t s);
   int gemm(const Act& a, int K, const PackedW& w, const GemmTap* taps, int ntaps, int L_in, int L_out, int pstride,
            const float* bias, const float* bias_tab, const float* res, int ldr, const float* res2, int ldr2,
-           float* of, int ldo, bf16* oh, bf16* ol, int lds, int o_L, int o_stride, int o_off);
+           float* of, int ldo, bf16* oh, bf16* ol, int lds, int o_L, int o_stride, int o_off,
+           const GemmFuse* fuse = nullptr);
   int res_fwd(const ResW& w, const Act& x, int L, const OutSpec& o, Act& y, ResSave& sv);
   int res_bwd(const ResW& w, const ResSave& sv, const Act& dy, int L, const float* extra, int ldextra, Act& dx,
               bool want_split);
@@ -114,12 +121,13 @@ class UnetEngine {
 
   // optional per-class timing
   bool prof_ = false;
-  struct ProfEv { cudaEvent_t a, b; int cat; };
+  struct ProfEv { cudaEvent_t a, b; int cat; char tag[56]; };
   std::vector<ProfEv> prof_events_; size_t prof_used_ = 0;
  public:
   struct ProfScope {
     UnetEngine* e; int idx;
     ProfScope(UnetEngine* eng, int cat);
+    void tag(const char* fmt, ...);
     ~ProfScope();
   };
 };

@@ -29,9 +29,10 @@ __global__ void extract_kernel(const float* __restrict__ src, int n_rows, int H,
 int UnetEngine::gemm(const Act& a, int K, const PackedW& w, const GemmTap* taps, int ntaps, int L_in, int L_out,
                      int pstride, const float* bias, const float* bias_tab, const float* res, int ldr,
                      const float* res2, int ldr2, float* of, int ldo, bf16* oh, bf16* ol, int lds, int o_L,
-                     int o_stride, int o_off) {
+                     int o_stride, int o_off, const GemmFuse* fuse) {
   if (dry_) return 0;
   ProfScope ps(this, 0);
+  ps.tag("M%ld_N%d_K%dx%d_L%d_e%d", (long)npad_ * L_out, w.Nout, K, ntaps, L_out, fuse ? fuse->epi : 0);
   GemmDesc d{};
   d.a_hi = a.hi; d.a_lo = a.lo; d.n_samples = npad_; d.L_in = L_in; d.ldA = a.lds; d.K = K; d.a_pstride = pstride;
   d.L_out = L_out; d.ntaps = ntaps;
@@ -40,6 +41,10 @@ int UnetEngine::gemm(const Act& a, int K, const PackedW& w, const GemmTap* taps,
   d.bias = bias; d.bias_tab = bias_tab; d.row2scene = r2s_; d.residual = res; d.ldR = ldr; d.residual2 = res2;
   d.ldR2 = ldr2; d.out_f32 = of; d.ldO = ldo; d.out_hi = oh; d.out_lo = ol; d.ldS = lds;
   d.o_L = o_L; d.o_stride = o_stride; d.o_off = o_off; d.precision = cfg_.precision;
+  if (fuse) {
+    d.epi = fuse->epi; d.ln_gamma = fuse->ln_gamma; d.ln_beta = fuse->ln_beta; d.ln_stats = fuse->ln_stats;
+    d.ln_x = fuse->ln_x; d.u = fuse->u; d.out2_hi = fuse->out2_hi; d.out2_lo = fuse->out2_lo; d.ldS2 = fuse->ldS2;
+  }
   return gemm_launch(d, s_);
 }
 
@@ -134,41 +139,64 @@ int UnetEngine::st_fwd(const STW& w, const Act& x, int L, const OutSpec& o, Act&
     g.eps = 1e-6f; g.mish = 0; g.out_hi = xn.hi; g.out_lo = xn.lo; g.ldS = C;
     ProfScope ps(this, 1); TRY(gn_forward(g, s_));
   }
+  // proj_in -> z (fp32, residual stream) with LayerNorm1 of block 0 fused into the epilogue
   float* z = allocf(M * 256);
+  Split a = allocs(M * 256);                    // LN1(z) of the current block
   Act xna; xna.hi = xn.hi; xna.lo = xn.lo; xna.lds = C;
-  TRY(gemm(xna, C, w.pin.f, TAP_1X1, 1, L, L, 1, w.pin.bias, nullptr, nullptr, 0, nullptr, 0, z, 256, nullptr, nullptr, 0,
-           L, 1, 0));
+  sv.blk[0].stats1 = allocf(M * 2);
+  {
+    GemmFuse f; f.epi = EPI_LN_FWD; f.ln_gamma = w.blk[0].ln1g; f.ln_beta = w.blk[0].ln1b; f.ln_stats = sv.blk[0].stats1;
+    f.out2_hi = a.hi; f.out2_lo = a.lo; f.ldS2 = 256;
+    TRY(gemm(xna, C, w.pin.f, TAP_1X1, 1, L, L, 1, w.pin.bias, nullptr, nullptr, 0, nullptr, 0, z, 256, nullptr, nullptr, 0,
+             L, 1, 0, &f));
+  }
   Split zs{nullptr, nullptr};
   for (int b = 0; b < 2; ++b) {
     const TBlockW& t = w.blk[b];
     TBlockSave& ts = sv.blk[b];
     ts.zin = z;
-    Split a = allocs(M * 256);
-    if (!dry_) { ProfScope ps(this, 1); TRY(ln_forward(z, (int)M, 256, t.ln1g, t.ln1b, a.hi, a.lo, s_)); }
     ts.qkv = allocf(M * 768);
     Act aa; aa.hi = a.hi; aa.lo = a.lo; aa.lds = 256;
     TRY(gemm(aa, 256, t.qkv_f, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, ts.qkv, 768, nullptr,
              nullptr, 0, L, 1, 0));
     Split ao = allocs(M * 256);
     if (!dry_) { ProfScope ps(this, 2); TRY(attn_forward(ts.qkv, npad_, L, ao.hi, ao.lo, s_)); }
+    // attn1.to_out (+ collapsed attn2 constant per scene) + residual -> z1, LayerNorm3 fused
     ts.z1 = allocf(M * 256);
+    ts.stats3 = allocf(M * 2);
+    Split f3 = allocs(M * 256);
     Act aoa; aoa.hi = ao.hi; aoa.lo = ao.lo; aoa.lds = 256;
-    TRY(gemm(aoa, 256, t.o_f, TAP_1X1, 1, L, L, 1, nullptr, t.bias_tab, z, 256, nullptr, 0, ts.z1, 256, nullptr, nullptr,
-             0, L, 1, 0));
-    Split f = allocs(M * 256);
-    if (!dry_) { ProfScope ps(this, 1); TRY(ln_forward(ts.z1, (int)M, 256, t.ln3g, t.ln3b, f.hi, f.lo, s_)); }
+    {
+      GemmFuse f; f.epi = EPI_LN_FWD; f.ln_gamma = t.ln3g; f.ln_beta = t.ln3b; f.ln_stats = ts.stats3;
+      f.out2_hi = f3.hi; f.out2_lo = f3.lo; f.ldS2 = 256;
+      TRY(gemm(aoa, 256, t.o_f, TAP_1X1, 1, L, L, 1, nullptr, t.bias_tab, z, 256, nullptr, 0, ts.z1, 256, nullptr, nullptr,
+               0, L, 1, 0, &f));
+    }
+    // FF1 with the GEGLU in the epilogue: u (saved for the backward sweep, tile-interleaved) and a * gelu(gate)
     ts.u = allocf(M * 2048);
-    Act fa; fa.hi = f.hi; fa.lo = f.lo; fa.lds = 256;
-    TRY(gemm(fa, 256, t.ff1_f, TAP_1X1, 1, L, L, 1, t.ff1_bias, nullptr, nullptr, 0, nullptr, 0, ts.u, 2048, nullptr,
-             nullptr, 0, L, 1, 0));
     Split g = allocs(M * 1024);
-    if (!dry_) { ProfScope ps(this, 3); TRY(geglu_forward(ts.u, (int)M, 1024, g.hi, g.lo, s_)); }
-    float* z2 = allocf(M * 256);
-    if (b == 1) zs = allocs(M * 256);
+    Act fa; fa.hi = f3.hi; fa.lo = f3.lo; fa.lds = 256;
+    {
+      GemmFuse f; f.epi = EPI_GEGLU_FWD; f.out2_hi = g.hi; f.out2_lo = g.lo; f.ldS2 = 1024;
+      TRY(gemm(fa, 256, t.ff1_f, TAP_1X1, 1, L, L, 1, t.ff1_bias, nullptr, nullptr, 0, nullptr, 0, ts.u, 2048, nullptr,
+               nullptr, 0, L, 1, 0, &f));
+    }
     Act ga; ga.hi = g.hi; ga.lo = g.lo; ga.lds = 1024;
-    TRY(gemm(ga, 1024, t.ff2_f, TAP_1X1, 1, L, L, 1, t.ff2_bias, nullptr, ts.z1, 256, nullptr, 0, z2, 256,
-             b == 1 ? zs.hi : nullptr, b == 1 ? zs.lo : nullptr, 256, L, 1, 0));
-    z = z2;
+    if (b == 0) {
+      // FF2 + residual -> z2 (fp32) with LayerNorm1 of block 1 fused
+      float* z2 = allocf(M * 256);
+      Split a2 = allocs(M * 256);
+      sv.blk[1].stats1 = allocf(M * 2);
+      GemmFuse f; f.epi = EPI_LN_FWD; f.ln_gamma = w.blk[1].ln1g; f.ln_beta = w.blk[1].ln1b; f.ln_stats = sv.blk[1].stats1;
+      f.out2_hi = a2.hi; f.out2_lo = a2.lo; f.ldS2 = 256;
+      TRY(gemm(ga, 1024, t.ff2_f, TAP_1X1, 1, L, L, 1, t.ff2_bias, nullptr, ts.z1, 256, nullptr, 0, z2, 256, nullptr,
+               nullptr, 0, L, 1, 0, &f));
+      z = z2; a = a2;
+    } else {
+      zs = allocs(M * 256);
+      TRY(gemm(ga, 1024, t.ff2_f, TAP_1X1, 1, L, L, 1, t.ff2_bias, nullptr, ts.z1, 256, nullptr, 0, nullptr, 0, zs.hi,
+               zs.lo, 256, L, 1, 0));
+    }
   }
   y = Act(); y.C = C;
   float* yf = nullptr;
@@ -193,32 +221,38 @@ int UnetEngine::st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act
   for (int b = 1; b >= 0; --b) {
     const TBlockW& t = w.blk[b];
     const TBlockSave& ts = sv.blk[b];
-    float* dg = allocf(M * 1024);
-    Act dza; dza.hi = dzs.hi; dza.lo = dzs.lo; dza.lds = 256;
-    TRY(gemm(dza, 256, t.ff2_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dg, 1024, nullptr, nullptr,
-             0, L, 1, 0));
+    // FF2^T with the GEGLU backward in the epilogue -> du (tile-interleaved planes)
     Split du = allocs(M * 2048);
-    if (!dry_) { ProfScope ps(this, 3); TRY(geglu_backward(ts.u, dg, (int)M, 1024, du.hi, du.lo, s_)); }
-    float* df = allocf(M * 256);
-    Act dua; dua.hi = du.hi; dua.lo = du.lo; dua.lds = 2048;
-    TRY(gemm(dua, 2048, t.ff1_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, df, 256, nullptr, nullptr,
-             0, L, 1, 0));
+    Act dza; dza.hi = dzs.hi; dza.lo = dzs.lo; dza.lds = 256;
+    {
+      GemmFuse f; f.epi = EPI_GEGLU_BWD; f.u = ts.u;
+      TRY(gemm(dza, 256, t.ff2_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, nullptr, 0, du.hi, du.lo,
+               2048, L, 1, 0, &f));
+    }
+    // FF1^T with the LayerNorm3 backward in the epilogue: dz1 = dz + LN3'(z1, .)
     float* dz1 = allocf(M * 256);
     Split dz1s = allocs(M * 256);
-    if (!dry_) { ProfScope ps(this, 1); TRY(ln_backward(ts.z1, (int)M, 256, t.ln3g, df, dz, dz1, dz1s.hi, dz1s.lo, s_)); }
+    Act dua; dua.hi = du.hi; dua.lo = du.lo; dua.lds = 2048;
+    {
+      GemmFuse f; f.epi = EPI_LN_BWD; f.ln_gamma = t.ln3g; f.ln_stats = ts.stats3; f.ln_x = ts.z1;
+      TRY(gemm(dua, 2048, t.ff1_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, dz, 256, nullptr, 0, dz1, 256, dz1s.hi, dz1s.lo,
+               256, L, 1, 0, &f));
+    }
     float* dout = allocf(M * 256);
     Act d1a; d1a.hi = dz1s.hi; d1a.lo = dz1s.lo; d1a.lds = 256;
     TRY(gemm(d1a, 256, t.o_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dout, 256, nullptr, nullptr,
              0, L, 1, 0));
     Split dqkv = allocs(M * 768);
     if (!dry_) { ProfScope ps(this, 2); TRY(attn_backward(ts.qkv, dout, npad_, L, dqkv.hi, dqkv.lo, s_)); }
-    float* da = allocf(M * 256);
-    Act dqa; dqa.hi = dqkv.hi; dqa.lo = dqkv.lo; dqa.lds = 768;
-    TRY(gemm(dqa, 768, t.qkv_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, da, 256, nullptr, nullptr,
-             0, L, 1, 0));
+    // QKV^T with the LayerNorm1 backward in the epilogue: dz = dz1 + LN1'(zin, .)
     dz = allocf(M * 256);
     dzs = allocs(M * 256);
-    if (!dry_) { ProfScope ps(this, 1); TRY(ln_backward(ts.zin, (int)M, 256, t.ln1g, da, dz1, dz, dzs.hi, dzs.lo, s_)); }
+    Act dqa; dqa.hi = dqkv.hi; dqa.lo = dqkv.lo; dqa.lds = 768;
+    {
+      GemmFuse f; f.epi = EPI_LN_BWD; f.ln_gamma = t.ln1g; f.ln_stats = ts.stats1; f.ln_x = ts.zin;
+      TRY(gemm(dqa, 768, t.qkv_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, dz1, 256, nullptr, 0, dz, 256, dzs.hi, dzs.lo,
+               256, L, 1, 0, &f));
+    }
   }
   float* dxn = allocf(M * C);
   Act dza; dza.hi = dzs.hi; dza.lo = dzs.lo; dza.lds = 256;

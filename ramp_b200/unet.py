@@ -286,6 +286,9 @@ class TemporalUnetInference(nn.Module):
     def forward_no_energy(self, x, time, x_start=None, obstacle_pts=None, forward_t=None, compose=False):
         return self._rows(x, time, obstacle_pts, compose, want_f=True)[1]
 
+    def profile_dump(self, path):
+        check(lib().ramp_unet_profile_dump(self._engine, str(path).encode()), "ramp_unet_profile_dump")
+
     def profile(self, enable, fetch=False):
         """Per-kernel-class CUDA-event timing of the engine (ramp_unet_profile).  With fetch=True returns
         ({class: ms}, {class: launches}) accumulated since the last fetch."""
