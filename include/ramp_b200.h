@@ -103,6 +103,10 @@ int ramp_q_sample(const float* x0, long x0_bstride, const float* noise, int B, i
                   float sqrt_1mac, const unsigned char* pin_mask, const float* pin_val, long pin_bstride, float* out,
                   void* stream);
 
+/* sm (diffusion_model_dynamic.py:192-214), in place: waypoints start+1 .. start+n become a constant-velocity segment
+ * from waypoint `start` toward waypoint start+n (speed capped at max_vel, time step dt); D must be 4 */
+int ramp_smooth_segment(float* x, int B, int H, int D, int start, int n, float dt, float max_vel, void* stream);
+
 /* ---- point cloud: nearest point, APF, cost, selection ------------------------------------------
  * ramp_cloud_pack: cloud [P, dim] fp32 -> packed buffer of ramp_cloud_packed_points(P) float4
  * ramp_nn_query  : cKDTree.query(k=1, distance_upper_bound) (APFhelper.py:17-35): for q[i*qstride + 0..dim-1],
@@ -114,15 +118,22 @@ int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int
 /* avoidance (APFhelper.py:37-104): windowed Gaussian push away from the nearest point; out may alias x */
 int ramp_apf_static(const float* x, int B, int H, int D, int dim, const float* dist, const int32_t* idx,
                     const void* packed, int P, float thr, float strength, int window, float* out, void* stream);
-/* avoidance (APFhelper_dynamic.py:107-142), in place; mode 0 = static boxes, 1 = pursuer disc (goal mixing) */
+/* avoidance (APFhelper_dynamic.py:107-142), in place; mode 0 = static boxes, 1 = pursuer disc (goal mixing).
+ * Optional gate (diffusion_model_dynamic.py:408-425): trajectory b is pushed only if
+ * |gate_x[b, gate_row, 0:2] - gate_pos[0:2]| < gate_thr (gate_x NULL = no gate); `active` is a second, explicit mask. */
 int ramp_apf_dynamic(float* x, int B, int H, int D, const float* dist, const int32_t* idx, const void* packed, int P,
                      int mode, int window, int affected, float strength, float thr_force, const float* goal,
-                     const unsigned char* active, void* stream);
+                     const unsigned char* active, const float* gate_x, int gate_row, const float* gate_pos,
+                     float gate_thr, void* stream);
 /* cost.py:3-54: terms[b] = (collision_free, path_length, smoothness); dist from ramp_nn_query(upper_bound = thr) */
 int ramp_cost_terms(const float* x, int B, int H, int D, int dim, const float* dist, float thr, float* terms,
                     void* stream);
-/* cost.py:56-88 over n (all-gathered) trajectories: out8 = (best index or -1, best cost, n_free, len min/max, smooth min/max, 0) */
-int ramp_select_best(const float* terms, int n, float w_smooth, float w_len, float* out8, void* stream);
+/* cost.py:56-88 over n (all-gathered) trajectories: out8 = (best index or -1, best cost, n_free, len min/max,
+ * smooth min/max, rank of the best among the collision-free ones = cost.py's best_index).  normalize != 0 applies the
+ * min-max normalisation (0/0 = NaN as in the reference).  costs_out (nullable) [n]: total cost per trajectory,
+ * +inf where it collides. */
+int ramp_select_best(const float* terms, int n, float w_smooth, float w_len, int normalize, float* out8,
+                     float* costs_out, void* stream);
 
 #ifdef __cplusplus
 }

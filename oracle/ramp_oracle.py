@@ -520,3 +520,71 @@ def sample_ddim(sd, sch, T, n_steps, scene_latents, weights, hard_conds, noise, 
         x = inpaint(x, hard_conds)
         chain.append(x.clone())
     return torch.stack(chain, 0)
+
+
+# --------------------------------------------------------------------------------------
+# dynamic model: stacked-CFG row quirk, stage I, one replan tick (diffusion_model_dynamic.py)
+# --------------------------------------------------------------------------------------
+
+
+def eps_dynamic(sd, x, t_int, scene_latent, w=2.5, prefix="model."):
+    """p_mean_variance of the dynamic model (diffusion_model_dynamic.py:152-160): the batch is stacked twice and the
+    network zeroes the latent of every odd row of the stack (UnetInference.py:192-195)."""
+    B = x.shape[0]
+    x2 = x.repeat(2, 1, 1)
+    lat = scene_latent.reshape(1, -1).repeat(2 * B, 1).clone()
+    lat[1::2] = 0
+    t = torch.full((2 * B,), int(t_int), dtype=torch.long)
+    out = energy_grad(sd, x2, t, lat, prefix)
+    return (1 + w) * out[:B] - w * out[B:]
+
+
+def dynamic_stage1(sd, sch, T, scene_latent, hard_conds, x_T, n_high=10):
+    """Stage I (diffusion_model_dynamic.py:537-546): n_high DDIM steps without APF."""
+    x = inpaint(x_T.clone(), hard_conds)
+    for t in ddim_timesteps(T, n_high):
+        eps = eps_dynamic(sd, x, int(t), scene_latent)
+        x0 = x0_from_eps(sch, x, int(t), eps)
+        x = inpaint(ddim_step(sch, x, int(t), int(t) - T // n_high, x0), hard_conds)
+    return x
+
+
+def _pin_history(x, history, goal_row, zero_start_velocity):
+    for i, h in enumerate(history):
+        x[:, i] = h.reshape(1, -1)
+    x[:, -1] = goal_row
+    if zero_start_velocity:
+        x[:, 0, 2:] = 0.0
+    return x
+
+
+def dynamic_tick_batch(sd, sch, T, scene_latent, x_clean, history, stepp, k, noise, static_pts, disc_pts, center,
+                       n_high=10, n_low=5, thr_static=0.2, thr_pred=0.5, strength=0.15, w_static=8, w_pred=5):
+    """One stage-II replan up to the selection (diffusion_model_dynamic.py:553-591).  history: list of [1, D]
+    executed states; static_pts / disc_pts: numpy clouds of the ObstacleField; center: pursuer centre (2,)."""
+    H = x_clean.shape[0]
+    ts = ddim_timesteps(T, n_high)
+    low = ts[-n_low:]
+    goal_row = x_clean[-1].clone()
+    x = q_sample(sch, x_clean[None].repeat(noise.shape[0], 1, 1), int(low[0]), noise)
+    x[:, 0, 2:] = 0
+    x = _pin_history(x, history, goal_row, zero_start_velocity=False)
+    for t in low:
+        t = int(t)
+        if t == 0:
+            x[:, stepp + 1:stepp + 4] = smooth_segment(x[:, stepp], x[:, stepp + 3], 3)
+        eps = eps_dynamic(sd, x, t, scene_latent)
+        x0 = x0_from_eps(sch, x, t, eps)
+        if t == 0:
+            start = x[:, k].clone()
+            dist = (start[:, :2] - torch.as_tensor(center, dtype=x.dtype)[None]).norm(dim=1)
+            for b in range(x.shape[0]):
+                x0[b] = apf_dynamic(x0[b], static_pts, thr_static, thr_static, strength, window=w_static)
+                if dist[b] < thr_pred:
+                    x0[b] = apf_dynamic(x0[b], disc_pts, thr_pred, thr_static, strength, window=w_pred, is_dynamic=True,
+                                        affected=H, goal=x[0, -1])
+            x0[:, -1] = x[:, -1]
+        x = ddim_step(sch, x, t, t - T // n_high, x0)
+        x = _pin_history(x, history, goal_row, zero_start_velocity=True)
+    x[:, stepp + 1:stepp + 3] = smooth_segment(x[:, stepp], x[:, stepp + 2], 2)
+    return x

@@ -5,4 +5,7 @@ libramp_b200.so (hand-written CUDA behind a C ABI, include/ramp_b200.h).  There 
 from .unet import TemporalUnetInference, UNET_DIM_MULTS  # noqa: F401
 from .diffusion import (StaticGaussianDiffusionModel, GaussianDiffusionModel3d, make_timesteps,  # noqa: F401
                         cosine_beta_schedule, exponential_beta_schedule)
+from .dynamic import DynamicGaussianDiffusionModel  # noqa: F401
+from .cost import compute_trajectory_costs, compute_collision_with_pointcloud, compute_path_length, compute_smoothness  # noqa: F401
+from .apf import ObstacleField, avoidance  # noqa: F401
 from .sample_functions import apply_hard_conditioning, ddpm_sample_fn, extract, guide_gradient_steps  # noqa: F401

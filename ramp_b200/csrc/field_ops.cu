@@ -197,11 +197,18 @@ __global__ void __launch_bounds__(128) apf_dynamic_kernel(float* __restrict__ x,
                                                           const float4* __restrict__ cloud4, int P, int mode, int window,
                                                           int affected, float strength, float thr_force,
                                                           const float* __restrict__ goal,
-                                                          const unsigned char* __restrict__ active) {
+                                                          const unsigned char* __restrict__ active,
+                                                          const float* __restrict__ gate_x, int gate_row,
+                                                          const float* __restrict__ gate_pos, float gate_thr) {
   __shared__ float sd[128];
   __shared__ int si[128];
   const int b = blockIdx.x, t = threadIdx.x;
   if (active && !active[b]) return;
+  if (gate_x) {   // pursuer gate: |x[b, gate_row, :2] - pursuer| < threshold (diffusion_model_dynamic.py:408-425)
+    const float gx = gate_x[((size_t)b * H + gate_row) * D] - gate_pos[0];
+    const float gy = gate_x[((size_t)b * H + gate_row) * D + 1] - gate_pos[1];
+    if (!(sqrtf(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy))) < gate_thr)) return;
+  }
   float* xb = x + (size_t)b * H * D;
   const int n = mode == 1 ? min(affected, H) : H;
   sd[t] = (t < n) ? dist[(size_t)b * H + t] : INFINITY;
@@ -270,7 +277,8 @@ __global__ void __launch_bounds__(256) cost_terms_kernel(const float* __restrict
 
 // selection (cost.py:56-88) over n gathered trajectories: min-max normalise over survivors, weighted sum, argmin
 __global__ void __launch_bounds__(1024) select_best_kernel(const float* __restrict__ terms, int n, float w_smooth,
-                                                           float w_len, float* __restrict__ out /* [8] */) {
+                                                           float w_len, int normalize, float* __restrict__ out /* [8] */,
+                                                           float* __restrict__ costs_out) {
   __shared__ float s0[1024], s1[1024], s2[1024], s3[1024];
   __shared__ int si[1024];
   const int t = threadIdx.x;
@@ -295,12 +303,18 @@ __global__ void __launch_bounds__(1024) select_best_kernel(const float* __restri
   __syncthreads();
   // cost = w_s * (s - smin)/(smax - smin) + w_l * (l - lmin)/(lmax - lmin); 0/0 = NaN as in the reference.
   float best = INFINITY; int bi = -1; bool bnan = false;
-  for (int i = t; i < n; i += 1024)
+  for (int i = t; i < n; i += 1024) {
     if (terms[i * 3] != 0.f) {
-      const float c = w_smooth * ((terms[i * 3 + 2] - smin) / (smax - smin)) + w_len * ((terms[i * 3 + 1] - lmin) / (lmax - lmin));
+      const float sv = terms[i * 3 + 2], lv = terms[i * 3 + 1];
+      const float c = normalize ? w_smooth * ((sv - smin) / (smax - smin)) + w_len * ((lv - lmin) / (lmax - lmin))
+                                : w_smooth * sv + w_len * lv;
       const bool cn = c != c;
       if (bi < 0 || (cn && !bnan) || (!bnan && c < best)) { best = c; bi = i; bnan = cn; }
+      if (costs_out) costs_out[i] = c;
+    } else if (costs_out) {
+      costs_out[i] = INFINITY;
     }
+  }
   s0[t] = best; si[t] = bi; s1[t] = bnan ? 1.f : 0.f;
   __syncthreads();
   for (int o = 512; o > 0; o >>= 1) {
@@ -318,9 +332,21 @@ __global__ void __launch_bounds__(1024) select_best_kernel(const float* __restri
     }
     __syncthreads();
   }
+  const int best_i = si[0];
+  const float best_c = s0[0];
+  __syncthreads();
+  // rank of the winner among the collision-free trajectories (= cost.py's best_index into the filtered batch)
+  int below = 0;
+  for (int i = t; i < best_i; i += 1024) below += terms[i * 3] != 0.f ? 1 : 0;
+  si[t] = below;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if (t < o) si[t] += si[t + o];
+    __syncthreads();
+  }
   if (t == 0) {
-    out[0] = (float)si[0]; out[1] = s0[0]; out[2] = (float)n_free; out[3] = lmin; out[4] = lmax; out[5] = smin; out[6] = smax;
-    out[7] = 0.f;
+    out[0] = (float)best_i; out[1] = best_c; out[2] = (float)n_free; out[3] = lmin; out[4] = lmax; out[5] = smin; out[6] = smax;
+    out[7] = best_i >= 0 ? (float)si[0] : -1.f;
   }
 }
 
@@ -390,13 +416,16 @@ int ramp_apf_static(const float* x, int B, int H, int D, int dim, const float* d
 
 int ramp_apf_dynamic(float* x, int B, int H, int D, const float* dist, const int32_t* idx, const void* packed, int P,
                      int mode, int window, int affected, float strength, float thr_force, const float* goal,
-                     const unsigned char* active, void* stream) {
+                     const unsigned char* active, const float* gate_x, int gate_row, const float* gate_pos,
+                     float gate_thr, void* stream) {
   RAMP_CHECK(x && dist && idx && packed, "ramp_apf_dynamic: null argument");
   RAMP_CHECK(H <= 128, "ramp_apf_dynamic: horizon must be <= 128");
   RAMP_CHECK(mode == 0 || mode == 1, "ramp_apf_dynamic: mode must be 0 (static) or 1 (pursuer)");
+  RAMP_CHECK(!gate_x || (gate_pos && gate_row >= 0 && gate_row < H), "ramp_apf_dynamic: bad gate");
   if (B == 0) return 0;
   apf_dynamic_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(x, H, D, dist, idx, (const float4*)packed, P, mode, window,
-                                                          affected, strength, thr_force, goal, active);
+                                                          affected, strength, thr_force, goal, active, gate_x, gate_row,
+                                                          gate_pos, gate_thr);
   RAMP_LAUNCH_OK();
   return 0;
 }
@@ -410,9 +439,10 @@ int ramp_cost_terms(const float* x, int B, int H, int D, int dim, const float* d
   return 0;
 }
 
-int ramp_select_best(const float* terms, int n, float w_smooth, float w_len, float* out8, void* stream) {
+int ramp_select_best(const float* terms, int n, float w_smooth, float w_len, int normalize, float* out8,
+                     float* costs_out, void* stream) {
   RAMP_CHECK(terms && out8, "ramp_select_best: null argument");
-  select_best_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(terms, n, w_smooth, w_len, out8);
+  select_best_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(terms, n, w_smooth, w_len, normalize, out8, costs_out);
   RAMP_LAUNCH_OK();
   return 0;
 }

@@ -13,8 +13,10 @@
 //   accumulator is double buffered in TMEM (2 x BN columns), so the epilogue of tile i overlaps the
 //   MMAs of tile i+1; the TMA producer runs ahead across tile boundaries through the smem ring.
 // * Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + single-thread tcgen05.mma issuer,
-//   warps 2..5 = epilogue.  An epilogue thread owns one accumulator row; global loads / stores are
-//   transposed through a per-warp smem staging tile so that every warp-wide access is row-contiguous.
+//   warps 2..9 = two epilogue groups (group g owns accumulator buffer g, i.e. every other tile, so a tile's
+//   epilogue may take twice the MMA time before it stalls the tensor pipe).  An epilogue thread owns one
+//   accumulator row; global loads / stores are transposed through a per-warp XOR-swizzled smem staging tile
+//   so that every warp-wide access is row-contiguous.
 // * Fused epilogues (GemmEpi): GEGLU forward / backward, LayerNorm forward / backward (a thread owns the
 //   full 256-channel row when Nout == BN == 256; intermediate values are parked back in TMEM with
 //   tcgen05.st between the statistics pass and the normalisation pass).
@@ -29,9 +31,9 @@ namespace ramp {
 static constexpr int BM = 128;
 static constexpr int BK = 64;                 // bf16 elements = 128 B = one SWIZZLE_128B row
 static constexpr int A_TILE_BYTES = BM * BK * 2;
-static constexpr int GEMM_THREADS = 192;
-static constexpr int STG_LD = 36;             // staging row stride (floats): 16 B aligned, conflict-free float4 phases
-static constexpr int STG_BYTES = 4 * 32 * STG_LD * 4;
+static constexpr int EPI_WARPS = 8;            // two groups of four: group g drains accumulator buffer g
+static constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;
+static constexpr int STG_BYTES = EPI_WARPS * 32 * 32 * 4;   // per warp a 32 x 32 fp32 tile, XOR-swizzled 16-byte groups
 
 struct GemmParams {
   int n_samples, L_out, nb;                   // nb = samples per 128-row tile
@@ -157,8 +159,10 @@ __device__ __forceinline__ void st_acc(uint32_t taddr, const float (&v)[32]) {
 // epilogue plumbing: a thread owns accumulator row (q*32 + lane) of the tile; for global traffic the
 // warp re-maps to (row = (lane >> 3) + 4 i, 16-byte column group = lane & 7) through its staging tile.
 // ---------------------------------------------------------------------------------------------
+// staging tile: float4 group k of row r lives at float4 index r * 8 + (k ^ (r & 7))  (conflict-free both ways)
+__device__ __forceinline__ int stg_idx(int r, int k) { return r * 8 + (k ^ (r & 7)); }
 struct EpiCtx {
-  float* stg;              // this warp's staging tile [32][STG_LD]
+  float* stg;              // this warp's staging tile (32 x 32 fp32)
   int lane;
   bool my_ok; size_t my_row; int my_sample;
   unsigned ok8; size_t row8[8];
@@ -166,21 +170,21 @@ struct EpiCtx {
 
 // v[32] (this thread's row, columns col0..col0+31) -> base[row * ld + col0 ..] for every live row of the warp
 __device__ __forceinline__ void chunk_store_f32(const EpiCtx& e, const float (&v)[32], float* base, int ld, int col0) {
-  float* srow = e.stg + e.lane * STG_LD;
+  float4* s4 = reinterpret_cast<float4*>(e.stg);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) *reinterpret_cast<float4*>(srow + 4 * k) = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+  for (int k = 0; k < 8; ++k) s4[stg_idx(e.lane, k)] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
   __syncwarp();
   const int rsub = e.lane >> 3, c4 = e.lane & 7;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const float4 t = *reinterpret_cast<const float4*>(e.stg + (rsub + 4 * i) * STG_LD + 4 * c4);
+    const float4 t = s4[stg_idx(rsub + 4 * i, c4)];
     if ((e.ok8 >> i) & 1u) *reinterpret_cast<float4*>(base + e.row8[i] * ld + col0 + 4 * c4) = t;
   }
   __syncwarp();
 }
 // same, as bf16 hi / lo planes (ld, col0 in bf16 elements)
 __device__ __forceinline__ void chunk_store_split(const EpiCtx& e, const float (&v)[32], bf16* hi, bf16* lo, int ld, int col0) {
-  uint32_t* srow = reinterpret_cast<uint32_t*>(e.stg) + e.lane * STG_LD;
+  uint4* s4 = reinterpret_cast<uint4*>(e.stg);
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     uint32_t h[4], l[4];
@@ -192,15 +196,15 @@ __device__ __forceinline__ void chunk_store_split(const EpiCtx& e, const float (
       h[j] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
       l[j] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
     }
-    *reinterpret_cast<uint4*>(srow + 4 * k) = make_uint4(h[0], h[1], h[2], h[3]);
-    *reinterpret_cast<uint4*>(srow + 16 + 4 * k) = make_uint4(l[0], l[1], l[2], l[3]);
+    s4[stg_idx(e.lane, k)] = make_uint4(h[0], h[1], h[2], h[3]);
+    s4[stg_idx(e.lane, 4 + k)] = make_uint4(l[0], l[1], l[2], l[3]);
   }
   __syncwarp();
   const int rsub = e.lane >> 3, c4 = e.lane & 7;
   bf16* plane = (c4 < 4) ? hi : lo;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const uint4 t = *reinterpret_cast<const uint4*>(reinterpret_cast<uint32_t*>(e.stg) + (rsub + 4 * i) * STG_LD + 4 * c4);
+    const uint4 t = s4[stg_idx(rsub + 4 * i, c4)];
     if ((e.ok8 >> i) & 1u) *reinterpret_cast<uint4*>(plane + e.row8[i] * ld + col0 + 8 * (c4 & 3)) = t;
   }
   __syncwarp();
@@ -208,17 +212,17 @@ __device__ __forceinline__ void chunk_store_split(const EpiCtx& e, const float (
 // base[row * ld + col0 ..] -> v[32] for this thread's row (zeros for dead rows)
 __device__ __forceinline__ void chunk_load_f32(const EpiCtx& e, const float* __restrict__ base, int ld, int col0, float (&v)[32]) {
   const int rsub = e.lane >> 3, c4 = e.lane & 7;
+  float4* s4 = reinterpret_cast<float4*>(e.stg);
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
     if ((e.ok8 >> i) & 1u) t = *reinterpret_cast<const float4*>(base + e.row8[i] * ld + col0 + 4 * c4);
-    *reinterpret_cast<float4*>(e.stg + (rsub + 4 * i) * STG_LD + 4 * c4) = t;
+    s4[stg_idx(rsub + 4 * i, c4)] = t;
   }
   __syncwarp();
-  const float* srow = e.stg + e.lane * STG_LD;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    const float4 t = *reinterpret_cast<const float4*>(srow + 4 * k);
+    const float4 t = s4[stg_idx(e.lane, k)];
     v[4 * k] = t.x; v[4 * k + 1] = t.y; v[4 * k + 2] = t.z; v[4 * k + 3] = t.w;
   }
   __syncwarp();
@@ -240,6 +244,28 @@ __device__ __forceinline__ void epi_affine(const GemmParams& p, const EpiCtx& e,
   if (p.residual2) { float r[32]; chunk_load_f32(e, p.residual2, p.ldR2, col, r);
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] += r[i]; }
+}
+
+// L2 prefetch of everything this thread's row will read in the tile's epilogue; issued BEFORE waiting for the
+// accumulator, so the HBM latency of the epilogue inputs hides behind the tile's MMAs.
+__device__ __forceinline__ void prefetch_row(const float* base, size_t row, int ld, int col0, int ncols) {
+  const float* p0 = base + row * ld + col0;
+  for (int c = 0; c < ncols; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(p0 + c));
+}
+__device__ __forceinline__ void epi_prefetch(const GemmParams& p, const EpiCtx& e, int tile_n) {
+  if (!e.my_ok || p.BN == 16) return;
+  const int colbase = tile_n * p.BN;
+  if (p.epi == EPI_GEGLU_BWD) {
+    for (int c = 0; c < p.BN; c += 128) {
+      const int j = colbase + c;
+      prefetch_row(p.u, e.my_row, 2048, (j >> 7) * 256, 256);
+    }
+    return;
+  }
+  if (p.epi == EPI_LN_BWD) prefetch_row(p.ln_x, e.my_row, 256, 0, 256);
+  if (p.epi == EPI_GEGLU_FWD) return;
+  if (p.residual) prefetch_row(p.residual, e.my_row, p.ldR, colbase, p.BN);
+  if (p.residual2) prefetch_row(p.residual2, e.my_row, p.ldR2, colbase, p.BN);
 }
 
 // ---- one tile's epilogue, by mode.  acc = TMEM address of this warp's lane quarter, column 0 of the tile ----
@@ -321,8 +347,10 @@ __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx&
     chunk_load_f32(e, p.u, 2048, pg, g);
 #pragma unroll
     for (int i = 0; i < 32; ++i) {
-      const float da = d[i] * gelu_f(g[i]);
-      g[i] = d[i] * a[i] * gelu_grad_f(g[i]);
+      const float cdf = 0.5f * (1.f + erff(g[i] * 0.70710678118654752f));
+      const float pdf = 0.39894228040143268f * expf(-0.5f * g[i] * g[i]);
+      const float da = d[i] * (g[i] * cdf);                 // d * gelu(gate)
+      g[i] = d[i] * a[i] * (cdf + g[i] * pdf);              // d * a * gelu'(gate)
       a[i] = da;
     }
     chunk_store_split(e, a, p.out_hi, p.out_lo, p.ldS, pa);
@@ -408,7 +436,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b_tile_bytes = p.BN * BK * 2;
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + b_tile_bytes);
-  const uint32_t stg_base = smem_base + p.stages * stage_bytes;            // 4 x [32][STG_LD] floats
+  const uint32_t stg_base = smem_base + p.stages * stage_bytes;            // EPI_WARPS staging tiles
   const uint32_t bar_base = stg_base + STG_BYTES;
   const uint32_t full0 = bar_base, empty0 = bar_base + 8 * p.stages;
   const uint32_t tfull0 = bar_base + 16 * p.stages, tempty0 = tfull0 + 16;  // 2 + 2 accumulator barriers
@@ -500,15 +528,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
       }
     }
   } else {
-    // ---------------- epilogue (warps 2..5 -> TMEM lane quarters 2,3,0,1) ----------------
-    const int q = warp & 3;
+    // ---------------- epilogue: group (warp-2)/4 drains accumulator buffer `group`; TMEM lane quarter = warp % 4 ----
+    const int q = warp & 3, group = (warp - 2) >> 2;
     EpiCtx e;
     e.lane = lane;
-    e.stg = reinterpret_cast<float*>(smem_gen + p.stages * stage_bytes) + q * 32 * STG_LD;
+    e.stg = reinterpret_cast<float*>(smem_gen + p.stages * stage_bytes) + (warp - 2) * 32 * 32;
     int lt = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      if ((lt & 1) != group) continue;
       const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
-      const int buf = lt & 1;
+      const int buf = group;
       {
         const int r = q * 32 + lane;
         const int n_local = r / p.L_out, l = r - n_local * p.L_out;
@@ -525,6 +554,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
           e.row8[i] = (size_t)smp * p.o_L + (size_t)ll * p.o_stride + p.o_off;
         }
       }
+      epi_prefetch(p, e, tile_n);
       mbar_wait(tfull0 + 8 * buf, (lt >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t acc = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);

@@ -118,6 +118,31 @@ __global__ void __launch_bounds__(256) q_sample_kernel(const float* x0, long x0_
   }
 }
 
+// sm (diffusion_model_dynamic.py:192-214): constant-velocity segment of `n` states after waypoint `start`, heading for
+// waypoint start + n, speed capped at max_vel; positions s1 + k*dt*v, velocities v (state = x, y, vx, vy).
+__global__ void __launch_bounds__(128) smooth_segment_kernel(float* x, int B, int H, int D, int start, int n, float dt,
+                                                             float max_vel) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float* xb = x + (size_t)b * H * D;
+  const float s1x = xb[start * D], s1y = xb[start * D + 1];
+  const float dx = __fsub_rn(xb[(start + n) * D], s1x), dy = __fsub_rn(xb[(start + n) * D + 1], s1y);
+  const float dist = sqrtf(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+  const float ux = dist > 1e-6f ? __fdiv_rn(dx, dist) : 0.f, uy = dist > 1e-6f ? __fdiv_rn(dy, dist) : 0.f;
+  const float total_time = (float)n * dt;
+  float vx = __fdiv_rn(dx, total_time), vy = __fdiv_rn(dy, total_time);
+  const float vmag = sqrtf(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)));
+  if (vmag > max_vel) { vx = __fmul_rn(ux, max_vel); vy = __fmul_rn(uy, max_vel); }
+  for (int k = 1; k <= n; ++k) {
+    const float t = __fmul_rn((float)k, dt);
+    float* o = xb + (size_t)(start + k) * D;
+    o[0] = __fadd_rn(s1x, __fmul_rn(t, vx));
+    o[1] = __fadd_rn(s1y, __fmul_rn(t, vy));
+    o[2] = vx;
+    o[3] = vy;
+  }
+}
+
 static int ew_grid(size_t total) {
   size_t b = (total + 255) / 256;
   return (int)(b > 148 * 8 ? 148 * 8 : (b ? b : 1));
@@ -167,6 +192,16 @@ int ramp_inpaint(float* x, int B, int H, int D, const unsigned char* pin_mask, c
   const size_t total = (size_t)B * H * D;
   if (!total) return 0;
   inpaint_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>(x, B, H, D, pin_mask, pin_val, pin_bstride);
+  RAMP_LAUNCH_OK();
+  return 0;
+}
+
+int ramp_smooth_segment(float* x, int B, int H, int D, int start, int n, float dt, float max_vel, void* stream) {
+  RAMP_CHECK(x, "ramp_smooth_segment: null argument");
+  RAMP_CHECK(D == 4, "ramp_smooth_segment: state must be (x, y, vx, vy)");
+  RAMP_CHECK(start >= 0 && n >= 1 && start + n < H, "ramp_smooth_segment: segment outside the horizon");
+  if (B == 0) return 0;
+  smooth_segment_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(x, B, H, D, start, n, dt, max_vel);
   RAMP_LAUNCH_OK();
   return 0;
 }

@@ -164,8 +164,12 @@ class _DiffusionBase(nn.Module):
         B = x.shape[0]
         key = (B, G, x.device)
         if key not in self._r2s:
-            self._r2s = {key: (torch.arange(B * (G + 1), device=x.device, dtype=torch.int32) % (G + 1)).contiguous()}
+            self._r2s = {key: self._row_scenes(B, G, x.device)}
         return self.model.energy_grad_rows(x, t, self._r2s[key], x_repeat=G + 1)
+
+    def _row_scenes(self, B, G, device):
+        """Scene (latent row) of network row b*(G+1)+g: group g for g < G, the zero latent (index G) for g == G."""
+        return (torch.arange(B * (G + 1), device=device, dtype=torch.int32) % (G + 1)).contiguous()
 
     def _groups_and_weights(self, obstacle_pts, compose):
         raise NotImplementedError

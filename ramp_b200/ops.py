@@ -130,6 +130,17 @@ class CloudIndex:
         return dist, idx
 
 
+_far = {}
+
+
+def far_cloud(device):
+    """A one-point cloud far outside the workspace (path length / smoothness without a collision test)."""
+    key = str(device)
+    if key not in _far:
+        _far[key] = CloudIndex(torch.full((1, 2), 1.0e6, device=device))
+    return _far[key]
+
+
 def apf_static(x, cloud, dist, idx, thr, strength, window, out=None):
     _need_cuda(x, dist, idx)
     B, H, D = x.shape
@@ -139,12 +150,23 @@ def apf_static(x, cloud, dist, idx, thr, strength, window, out=None):
     return out
 
 
-def apf_dynamic(x, cloud, dist, idx, mode, window, affected, strength, thr_force, goal=None, active=None):
-    _need_cuda(x, dist, idx, goal, active)
+def apf_dynamic(x, cloud, dist, idx, mode, window, affected, strength, thr_force, goal=None, active=None, gate_x=None,
+                gate_row=0, gate_pos=None, gate_thr=0.0):
+    _need_cuda(x, dist, idx, goal, active, gate_x, gate_pos)
     B, H, D = x.shape
     check(lib().ramp_apf_dynamic(ptr(x), B, H, D, ptr(dist), ptr(idx), ptr(cloud.packed), cloud.P, int(mode), int(window),
                                  int(affected), _c_float(strength), _c_float(thr_force), ptr(goal), ptr(active),
-                                 _stream()), "ramp_apf_dynamic")
+                                 ptr(gate_x), int(gate_row), ptr(gate_pos), _c_float(gate_thr), _stream()),
+          "ramp_apf_dynamic")
+    return x
+
+
+def smooth_segment(x, start, n, dt=0.1, max_vel=0.8):
+    """sm (diffusion_model_dynamic.py:192-214) in place on waypoints start+1 .. start+n."""
+    _need_cuda(x)
+    B, H, D = x.shape
+    check(lib().ramp_smooth_segment(ptr(x), B, H, D, int(start), int(n), _c_float(dt), _c_float(max_vel), _stream()),
+          "ramp_smooth_segment")
     return x
 
 
@@ -159,10 +181,11 @@ def cost_terms(x, cloud, thr, terms=None):
     return terms
 
 
-def select_best(terms, w_smooth=0.1, w_len=0.9):
-    """-> device tensor [8]: (best index or -1, best cost, n_free, len min, len max, smooth min, smooth max, 0)."""
-    _need_cuda(terms)
-    out = torch.empty(8, device=terms.device)
-    check(lib().ramp_select_best(ptr(terms), terms.shape[0], _c_float(w_smooth), _c_float(w_len), ptr(out), _stream()),
-          "ramp_select_best")
+def select_best(terms, w_smooth=0.1, w_len=0.9, normalize=True, costs_out=None, out=None):
+    """-> device tensor [8]: (best index or -1, best cost, n_free, len min, len max, smooth min, smooth max,
+    rank of the best among the collision-free trajectories)."""
+    _need_cuda(terms, costs_out)
+    out = torch.empty(8, device=terms.device) if out is None else out
+    check(lib().ramp_select_best(ptr(terms), terms.shape[0], _c_float(w_smooth), _c_float(w_len), int(bool(normalize)),
+                                 ptr(out), ptr(costs_out), _stream()), "ramp_select_best")
     return out
