@@ -161,6 +161,11 @@ def run_ours(args):
     prof_ms, prof_n = model.model.profile(False, fetch=True)
     sampler.join(timeout=2)
 
+    replan = None
+    if rank == 0 and args.replan_ticks > 0:
+        model.model.release_engine()
+        torch.cuda.empty_cache()
+        replan = replan_latency(dev, args.replan_ticks, max(3, args.replan_ticks // 10))
     if rank == 0:
         peak_tf, peak_bw, how = peaks()
         rows_per_step = B * (G + 1) * T
@@ -192,10 +197,82 @@ def run_ours(args):
         }
         if args.cpu_sample > 0:
             line["cpu_baseline"] = cpu_baseline(sample_B=args.cpu_sample)
+        if replan is not None:
+            line["replan"] = replan
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------------
+# Replan latency (BASELINE.json configs[2]): one stage-II tick of the dynamic planner as a CUDA graph —
+# batch 1024, 5 DDIM steps of the 100-step schedule (diffusion_model_dynamic.py:553-598), APF on the last step
+# against a 3840-point static cloud + 256-point pursuer disc, cost/selection against the same 4096 points.
+# Per tick the host uploads the new pursuer cloud (pinned -> device), replays the graph and reads the
+# selection back; latency = host wall clock between synchronised points (what TimerCUDA measures).
+# ---------------------------------------------------------------------------------------------------
+def replan_latency(dev, ticks, warm, batch=1024):
+    import numpy as np
+    from ramp_b200.apf_dynamic import generate_box_points, generate_sphere_points
+    from ramp_b200.dynamic import DynamicGaussianDiffusionModel
+    from ramp_b200.graphs import ReplanGraph
+    from ramp_b200.testing import SyntheticPursuitDataset, pursuit_cloud_2d, synthetic_state_dict
+    from ramp_b200.unet import TemporalUnetInference
+    net = TemporalUnetInference(n_support_points=H, state_dim=D, max_rows=2 * batch, max_scenes=2)
+    m = DynamicGaussianDiffusionModel(model=net, n_diffusion_steps=100, predict_epsilon=True)
+    m.load_state_dict(synthetic_state_dict(m, 0))
+    m = m.to(dev).eval()
+    ds = SyntheticPursuitDataset()
+    cloud = pursuit_cloud_2d(ds).to(dev)
+    np.random.seed(0)
+    boxes = ds.env.obj_fixed_list[0].fields[0]
+    static_pts = torch.from_numpy(np.vstack([generate_box_points(c, s, 960) for c, s in
+                                             zip(boxes.centers.numpy(), boxes.sizes.numpy())])).float()
+    pursuer = ds.env.obj_extra_list[0].fields[0]
+    disc_host = torch.empty(256, 2).pin_memory()
+    center_host = torch.empty(2).pin_memory()
+    sel_host = torch.empty(8).pin_memory()
+    k = 3                                               # a tick with three executed states pinned
+    s = torch.linspace(0, 1, H)[:, None]
+    plan = torch.cat([-0.8 + 1.6 * s, -0.8 + 1.6 * s, torch.full((H, 2), 0.2)], dim=1)
+    g = ReplanGraph(m, batch, H, k, cloud, static_pts, torch.zeros(256, 2), static_pts)
+    g.x_clean.copy_(plan.to(dev))
+    g.history.copy_(plan[:k + 1].to(dev))
+    lat_ms, dev_ms = [], []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for it in range(warm + ticks):
+        pursuer.update_centers(it, plan[k:k + 1, :2])            # host-side pursuer dynamics (environment protocol)
+        c = pursuer.centers[0].numpy()
+        disc_host.copy_(torch.from_numpy(generate_sphere_points(c, 0.1, 256)).float())
+        center_host.copy_(torch.from_numpy(c))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e0.record()
+        g.disc_points.copy_(disc_host, non_blocking=True)
+        g.disc_center.copy_(center_host, non_blocking=True)
+        g.replay()
+        sel_host.copy_(g.sel, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        if it >= warm:
+            lat_ms.append(1e3 * (t1 - t0))
+            dev_ms.append(e0.elapsed_time(e1))
+        if int(sel_host[0]) >= 0:
+            g.x_clean.copy_(g.best)                              # next tick refines the selected plan
+            g.x_clean[:k + 1] = g.history
+    lat_ms.sort()
+    dev_ms.sort()
+    q = lambda v, f: v[min(len(v) - 1, int(f * len(v)))]  # noqa: E731
+    flops = 2 * batch * 5 * F_ROW
+    return {"p50_ms": q(lat_ms, 0.5), "p95_ms": q(lat_ms, 0.95), "device_p50_ms": q(dev_ms, 0.5), "ticks": ticks,
+            "warmup_ticks": warm, "batch": batch, "ddim_steps": 5, "network_rows_per_step": 2 * batch,
+            "apf_cloud_points": 3840 + 256, "cost_cloud_points": 4096, "cuda_graph": True,
+            "h2d_bytes_per_tick": 256 * 2 * 4 + 8, "d2h_bytes_per_tick": 32,
+            "tensor_floor_ms": 1e3 * 3 * flops / (peaks()[0] * 1e12),
+            "note": "reference tick shape (5 DDIM steps of 100, CFG rows x2); floor = 3 split-bf16 MMAs per product at the "
+                    "measured sustained bf16 peak"}
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -262,6 +339,7 @@ def main():
     ap.add_argument("--batch", type=int, default=B_PER_GPU, help="trajectories per GPU")
     ap.add_argument("--max-rows", type=int, default=1792, help="network rows per engine call (workspace size)")
     ap.add_argument("--cpu-sample", type=int, default=2, help="trajectories in the bounded CPU sample")
+    ap.add_argument("--replan-ticks", type=int, default=60, help="timed replan ticks of the dynamic planner (0 = skip)")
     ap.add_argument("--dump-launches", default="", help="write the per-launch CUDA-event CSV of one profiled step here")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -49,6 +49,13 @@ __device__ __forceinline__ void split_bf16(float v, bf16& hi, bf16& lo) {
   lo = __float2bfloat16_rn(v - __bfloat162float(hi));
 }
 
+// two values at once: packed bf16x2 planes (element 0 in the low half), 6 instructions per pair
+__device__ __forceinline__ void split2_bf16(float v0, float v1, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(v1), "f"(v0));
+  const float r0 = v0 - __uint_as_float(hi << 16), r1 = v1 - __uint_as_float(hi & 0xffff0000u);
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(r1), "f"(r0));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -120,8 +127,9 @@ struct GemmDesc {
 };
 enum GemmEpi {
   EPI_PLAIN = 0,
-  EPI_GEGLU_FWD = 1,   // acc (+bias) = (a | gate) per 256-col tile -> out_f32 = u, out2 = a * gelu(gate) [rows, Nout/2]
-  EPI_GEGLU_BWD = 2,   // acc = d(a*gelu(gate)) [rows, 1024] -> out_hi/lo = du [rows, 2048] (tile-interleaved)
+  EPI_GEGLU_FWD = 1,   // acc (+bias) = (a | gate) per 256-col tile -> out2 = a * gelu(gate) [rows, Nout/2] and, for the
+                       // backward sweep, out_f32 = u = (gelu(gate) | a * gelu'(gate)) in the same tile-interleaved columns
+  EPI_GEGLU_BWD = 2,   // acc = d = d(a*gelu(gate)) [rows, 1024] -> out_hi/lo = (d * u_s | d * u_q) [rows, 2048]
   EPI_LN_FWD = 3,      // v = acc + bias + bias_tab + residual -> out_f32 = v, out2 = LN(v), ln_stats
   EPI_LN_BWD = 4       // acc = dLN-output -> out = residual + LN_backward(ln_x, acc)
 };

@@ -189,13 +189,7 @@ __device__ __forceinline__ void chunk_store_split(const EpiCtx& e, const float (
   for (int k = 0; k < 4; ++k) {
     uint32_t h[4], l[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      bf16 h0, l0, h1, l1;
-      split_bf16(v[8 * k + 2 * j], h0, l0);
-      split_bf16(v[8 * k + 2 * j + 1], h1, l1);
-      h[j] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-      l[j] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
-    }
+    for (int j = 0; j < 4; ++j) split2_bf16(v[8 * k + 2 * j], v[8 * k + 2 * j + 1], h[j], l[j]);
     s4[stg_idx(e.lane, k)] = make_uint4(h[0], h[1], h[2], h[3]);
     s4[stg_idx(e.lane, 4 + k)] = make_uint4(l[0], l[1], l[2], l[3]);
   }
@@ -323,20 +317,29 @@ __device__ __forceinline__ void epi_plain16(const GemmParams& p, const EpiCtx& e
 __device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int tile_n) {
   const int colbase = tile_n * 256;
   for (int c = 0; c < 128; c += 32) {
-    float a[32], g[32];
+    float a[32], g[32], s_[32];
     ld_acc(acc + c, a);
     ld_acc(acc + 128 + c, g);
     if (p.bias) { add_vec32(a, p.bias + colbase + c); add_vec32(g, p.bias + colbase + 128 + c); }
+    // s = gelu(gate), q = a * gelu'(gate): everything the backward needs, so it is two multiplies per element there
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float cdf = 0.5f * (1.f + erff(g[i] * 0.70710678118654752f));
+      const float pdf = 0.39894228040143268f * expf(-0.5f * g[i] * g[i]);
+      const float sgl = g[i] * cdf;
+      g[i] = a[i] * (cdf + g[i] * pdf);
+      a[i] *= sgl;
+      if (p.out_f32) s_[i] = sgl;
+    }
     if (p.out_f32) {
-      chunk_store_f32(e, a, p.out_f32, p.ldO, colbase + c);
+      chunk_store_f32(e, s_, p.out_f32, p.ldO, colbase + c);
       chunk_store_f32(e, g, p.out_f32, p.ldO, colbase + 128 + c);
     }
-#pragma unroll
-    for (int i = 0; i < 32; ++i) a[i] *= gelu_f(g[i]);
     chunk_store_split(e, a, p.out2_hi, p.out2_lo, p.ldS2, tile_n * 128 + c);
   }
 }
-// GEGLU backward: acc = d(a * gelu(gate)) for natural columns colbase + c; u and du are tile-interleaved
+// GEGLU backward: acc = d(a * gelu(gate)) for natural columns colbase + c; u = (gelu(gate) | a gelu'(gate)) and du are
+// tile-interleaved
 __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
   for (int c = 0; c < p.BN; c += 32) {
     float d[32], a[32], g[32];
@@ -346,13 +349,7 @@ __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx&
     chunk_load_f32(e, p.u, 2048, pa, a);
     chunk_load_f32(e, p.u, 2048, pg, g);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const float cdf = 0.5f * (1.f + erff(g[i] * 0.70710678118654752f));
-      const float pdf = 0.39894228040143268f * expf(-0.5f * g[i] * g[i]);
-      const float da = d[i] * (g[i] * cdf);                 // d * gelu(gate)
-      g[i] = d[i] * a[i] * (cdf + g[i] * pdf);              // d * a * gelu'(gate)
-      a[i] = da;
-    }
+    for (int i = 0; i < 32; ++i) { a[i] *= d[i]; g[i] *= d[i]; }    // u = (gelu(gate) | a * gelu'(gate))
     chunk_store_split(e, a, p.out_hi, p.out_lo, p.ldS, pa);
     chunk_store_split(e, g, p.out_hi, p.out_lo, p.ldS, pg);
   }

@@ -35,78 +35,181 @@ int prep_input(const float* x, int n_samples, int n_pad, int L, int D, int x_rep
 }
 
 // ------------------------------------------------------------------------------------------------
-// GroupNorm: one warp per (sample, group); 8 groups -> 8 warps per CTA, one CTA per sample.
+// GroupNorm(8 groups) over one sample's [L, C] tile (L*C <= 2048 floats): one 256-thread CTA per sample.
+// The tile is read ONCE with coalesced float4 loads and stays in registers (<= 2 float4 per thread); group
+// statistics are reduced by segmented warp shuffles (the lanes of one group are adjacent) + shared atomics.
+// Mish(x) = x * tanh(softplus(x)) is evaluated as x * n / (n + 2), n = e^x (e^x + 2)  (exact identity).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) gn_forward_kernel(GnArgs a) {
-  const int n = blockIdx.x, g = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int cg = a.C / 8, m = a.L * cg;
-  const float* xs = a.x + (size_t)n * a.L * a.ldX + g * cg;
-  float s = 0.f;
-  for (int i = lane; i < m; i += 32) s += xs[(size_t)(i / cg) * a.ldX + (i % cg)];
-  const float mean = warp_sum(s) / m;
-  float v = 0.f;
-  for (int i = lane; i < m; i += 32) {
-    float d = xs[(size_t)(i / cg) * a.ldX + (i % cg)] - mean;
-    v += d * d;
+__device__ __forceinline__ float mish_fast(float x) {
+  if (x > 20.f) return x;
+  const float w = expf(x), n = w * (w + 2.f);
+  return x * (n / (n + 2.f));
+}
+__device__ __forceinline__ float mish_grad_fast(float x) {
+  if (x > 20.f) return 1.f;
+  const float w = expf(x), n = w * (w + 2.f), d = 1.f / (n + 2.f);
+  return n * d + x * (4.f * w * (w + 1.f)) * d * d;
+}
+// sum of v over the lanes that share a group: groups are `seg` adjacent lanes (seg = 1, 2, 4 or 8)
+__device__ __forceinline__ float seg_sum(float v, int seg) {
+  for (int o = 1; o < seg; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+struct GnTile {           // the (<= 2) float4 of the sample tile owned by a thread
+  float4 v[2]; int row[2], col[2]; bool ok[2];
+};
+__device__ __forceinline__ void gn_load(GnTile& t, const float* __restrict__ x, int ldX, size_t row0, int L, int C) {
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int idx = (threadIdx.x + i * 256) * 4;
+    t.ok[i] = idx < L * C;
+    t.row[i] = t.ok[i] ? idx / C : 0;
+    t.col[i] = t.ok[i] ? idx - t.row[i] * C : 0;
+    t.v[i] = t.ok[i] ? *reinterpret_cast<const float4*>(x + (row0 + t.row[i]) * ldX + t.col[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  const float rstd = rsqrtf(warp_sum(v) / m + a.eps);
-  for (int i = lane; i < m; i += 32) {
-    const int l = i / cg, c = g * cg + (i % cg);
-    const size_t row = (size_t)n * a.L + l;
-    float y = (a.x[row * a.ldX + c] - mean) * rstd * a.gamma[c] + a.beta[c];
-    if (a.mish) y = mish_f(y);
-    if (a.cond) y += a.cond[c];
-    if (a.add) y += a.add[row * a.ldAdd + c];
-    if (a.out_f32) a.out_f32[row * a.ldO + c] = y;
-    if (a.out_hi) store_split(a.out_hi, a.out_lo, row * a.ldS + c, y);
+}
+// red[0..7] += per-group sums of (a[0], a[1]) (one value per owned float4); returns after a CTA barrier
+__device__ __forceinline__ void gn_group_reduce(const GnTile& t, const float (&a)[2], int cg, float* red) {
+  const int seg = cg >= 32 ? 8 : cg / 4;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const float s = seg_sum(a[i], seg);
+    if (t.ok[i] && (threadIdx.x & (seg - 1)) == 0) atomicAdd(&red[t.col[i] / cg], s);
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void gn_store(float4 y, size_t row, int c, float* out_f32, int ldO, bf16* hi, bf16* lo, int ldS) {
+  if (out_f32) *reinterpret_cast<float4*>(out_f32 + row * ldO + c) = y;
+  if (hi) {
+    uint32_t h0, l0, h1, l1;
+    split2_bf16(y.x, y.y, h0, l0);
+    split2_bf16(y.z, y.w, h1, l1);
+    *reinterpret_cast<uint2*>(hi + row * ldS + c) = make_uint2(h0, h1);
+    *reinterpret_cast<uint2*>(lo + row * ldS + c) = make_uint2(l0, l1);
+  }
+}
+// mean / rstd of every group into stat[0..7] / stat[8..15]
+__device__ __forceinline__ void gn_stats(const GnTile& t, int L, int C, float eps, float* red, float* stat) {
+  const int cg = C / 8;
+  const float inv_m = 1.f / (float)(L * cg);
+  if (threadIdx.x < 16) red[threadIdx.x] = 0.f;
+  __syncthreads();
+  float a[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) a[i] = (t.v[i].x + t.v[i].y) + (t.v[i].z + t.v[i].w);
+  gn_group_reduce(t, a, cg, red);
+  if (threadIdx.x < 8) stat[threadIdx.x] = red[threadIdx.x] * inv_m;
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const float m = stat[t.col[i] / cg];
+    const float dx = t.v[i].x - m, dy = t.v[i].y - m, dz = t.v[i].z - m, dw = t.v[i].w - m;
+    a[i] = t.ok[i] ? (dx * dx + dy * dy) + (dz * dz + dw * dw) : 0.f;
+  }
+  gn_group_reduce(t, a, cg, red + 8);
+  if (threadIdx.x < 8) stat[8 + threadIdx.x] = rsqrtf(red[8 + threadIdx.x] * inv_m + eps);
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) gn_forward_kernel(GnArgs a) {
+  __shared__ float red[16], stat[16];
+  const size_t row0 = (size_t)blockIdx.x * a.L;
+  const int cg = a.C / 8;
+  GnTile t;
+  gn_load(t, a.x, a.ldX, row0, a.L, a.C);
+  gn_stats(t, a.L, a.C, a.eps, red, stat);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    if (!t.ok[i]) continue;
+    const int c = t.col[i], g = c / cg;
+    const size_t row = row0 + t.row[i];
+    const float mean = stat[g], rstd = stat[8 + g];
+    const float4 gm = *reinterpret_cast<const float4*>(a.gamma + c), bt = *reinterpret_cast<const float4*>(a.beta + c);
+    float y[4] = {(t.v[i].x - mean) * rstd * gm.x + bt.x, (t.v[i].y - mean) * rstd * gm.y + bt.y,
+                  (t.v[i].z - mean) * rstd * gm.z + bt.z, (t.v[i].w - mean) * rstd * gm.w + bt.w};
+    if (a.mish)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) y[j] = mish_fast(y[j]);
+    if (a.cond) {
+      const float4 cd = *reinterpret_cast<const float4*>(a.cond + c);
+      y[0] += cd.x; y[1] += cd.y; y[2] += cd.z; y[3] += cd.w;
+    }
+    if (a.add) {
+      const float4 ad = *reinterpret_cast<const float4*>(a.add + row * a.ldAdd + c);
+      y[0] += ad.x; y[1] += ad.y; y[2] += ad.z; y[3] += ad.w;
+    }
+    gn_store(make_float4(y[0], y[1], y[2], y[3]), row, c, a.out_f32, a.ldO, a.out_hi, a.out_lo, a.ldS);
   }
 }
 int gn_forward(const GnArgs& a, cudaStream_t s) {
-  RAMP_CHECK(a.C % 8 == 0, "gn: C must be a multiple of 8");
+  RAMP_CHECK(a.C % 32 == 0 && a.L * a.C <= 2048, "gn: C must be a multiple of 32 and L*C <= 2048");
+  RAMP_CHECK(a.ldX % 4 == 0 && (!a.add || a.ldAdd % 4 == 0) && (!a.out_f32 || a.ldO % 4 == 0) && (!a.out_hi || a.ldS % 4 == 0),
+             "gn: leading dimensions must be multiples of 4");
   gn_forward_kernel<<<a.n_samples, 256, 0, s>>>(a);
   RAMP_LAUNCH_OK();
   return 0;
 }
 
 __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
-  const int n = blockIdx.x, g = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int cg = a.C / 8, m = a.L * cg;
-  const float* xs = a.x + (size_t)n * a.L * a.ldX + g * cg;
-  float s = 0.f;
-  for (int i = lane; i < m; i += 32) s += xs[(size_t)(i / cg) * a.ldX + (i % cg)];
-  const float mean = warp_sum(s) / m;
-  float v = 0.f;
-  for (int i = lane; i < m; i += 32) {
-    float d = xs[(size_t)(i / cg) * a.ldX + (i % cg)] - mean;
-    v += d * d;
+  __shared__ float red[16], stat[16], red2[16];
+  const size_t row0 = (size_t)blockIdx.x * a.L;
+  const int cg = a.C / 8;
+  const float inv_m = 1.f / (float)(a.L * cg);
+  GnTile t;
+  gn_load(t, a.x, a.ldX, row0, a.L, a.C);
+  gn_stats(t, a.L, a.C, a.eps, red, stat);
+  if (threadIdx.x < 16) red2[threadIdx.x] = 0.f;
+  __syncthreads();
+  float xh[2][4], dyh[2][4], p1[2], p2[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int c = t.col[i], g = c / cg;
+    const float mean = stat[g], rstd = stat[8 + g];
+    const float4 gm = *reinterpret_cast<const float4*>(a.gamma + c), bt = *reinterpret_cast<const float4*>(a.beta + c);
+    float4 dy = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t.ok[i]) dy = *reinterpret_cast<const float4*>(a.dy + (row0 + t.row[i]) * a.ldDy + c);
+    const float xv[4] = {t.v[i].x, t.v[i].y, t.v[i].z, t.v[i].w}, dv[4] = {dy.x, dy.y, dy.z, dy.w};
+    const float gv[4] = {gm.x, gm.y, gm.z, gm.w}, bv[4] = {bt.x, bt.y, bt.z, bt.w};
+    p1[i] = 0.f; p2[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      xh[i][j] = (xv[j] - mean) * rstd;
+      float d = dv[j] * gv[j];
+      if (a.mish) d *= mish_grad_fast(xh[i][j] * gv[j] + bv[j]);
+      dyh[i][j] = t.ok[i] ? d : 0.f;
+      p1[i] += dyh[i][j];
+      p2[i] += dyh[i][j] * xh[i][j];
+    }
   }
-  const float rstd = rsqrtf(warp_sum(v) / m + a.eps);
-  float s1 = 0.f, s2 = 0.f;
-  for (int i = lane; i < m; i += 32) {
-    const int l = i / cg, c = g * cg + (i % cg);
-    const size_t row = (size_t)n * a.L + l;
-    const float xh = (a.x[row * a.ldX + c] - mean) * rstd;
-    float dyh = a.dy[row * a.ldDy + c] * a.gamma[c];
-    if (a.mish) dyh *= mish_grad_f(xh * a.gamma[c] + a.beta[c]);
-    s1 += dyh;
-    s2 += dyh * xh;
+  {
+    const int seg = cg >= 32 ? 8 : cg / 4;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const float s1 = seg_sum(p1[i], seg), s2 = seg_sum(p2[i], seg);
+      if (t.ok[i] && (threadIdx.x & (seg - 1)) == 0) { atomicAdd(&red2[t.col[i] / cg], s1); atomicAdd(&red2[8 + t.col[i] / cg], s2); }
+    }
+    __syncthreads();
   }
-  s1 = warp_sum(s1) / m;
-  s2 = warp_sum(s2) / m;
-  for (int i = lane; i < m; i += 32) {
-    const int l = i / cg, c = g * cg + (i % cg);
-    const size_t row = (size_t)n * a.L + l;
-    const float xh = (a.x[row * a.ldX + c] - mean) * rstd;
-    float dyh = a.dy[row * a.ldDy + c] * a.gamma[c];
-    if (a.mish) dyh *= mish_grad_f(xh * a.gamma[c] + a.beta[c]);
-    float dx = rstd * (dyh - s1 - xh * s2);
-    if (a.add) dx += a.add[row * a.ldAdd + c];
-    if (a.out_f32) a.out_f32[row * a.ldO + c] = dx;
-    if (a.out_hi) store_split(a.out_hi, a.out_lo, row * a.ldS + c, dx);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    if (!t.ok[i]) continue;
+    const int c = t.col[i], g = c / cg;
+    const size_t row = row0 + t.row[i];
+    const float rstd = stat[8 + g], s1 = red2[g] * inv_m, s2 = red2[8 + g] * inv_m;
+    float dx[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dx[j] = rstd * (dyh[i][j] - s1 - xh[i][j] * s2);
+    if (a.add) {
+      const float4 ad = *reinterpret_cast<const float4*>(a.add + row * a.ldAdd + c);
+      dx[0] += ad.x; dx[1] += ad.y; dx[2] += ad.z; dx[3] += ad.w;
+    }
+    gn_store(make_float4(dx[0], dx[1], dx[2], dx[3]), row, c, a.out_f32, a.ldO, a.out_hi, a.out_lo, a.ldS);
   }
 }
 int gn_backward(const GnBwdArgs& a, cudaStream_t s) {
-  RAMP_CHECK(a.C % 8 == 0, "gn: C must be a multiple of 8");
+  RAMP_CHECK(a.C % 32 == 0 && a.L * a.C <= 2048, "gn: C must be a multiple of 32 and L*C <= 2048");
+  RAMP_CHECK(a.ldX % 4 == 0 && a.ldDy % 4 == 0 && (!a.add || a.ldAdd % 4 == 0) && (!a.out_f32 || a.ldO % 4 == 0) &&
+             (!a.out_hi || a.ldS % 4 == 0), "gn: leading dimensions must be multiples of 4");
   gn_backward_kernel<<<a.n_samples, 256, 0, s>>>(a);
   RAMP_LAUNCH_OK();
   return 0;

@@ -166,7 +166,8 @@ class DynamicGaussianDiffusionModel(_DiffusionBase):
         return ops.ddim_update(x, x0, out, pins=pins, **self._ddim_scalars(ti, t_prev))
 
     # ------------------------------------------------------------------ the replan tick, device only
-    def _tick_batch(self, x_clean, history, stepp, k, B, obstacle_pts, field, noise=None, out=None):
+    def _tick_batch(self, x_clean, history, stepp, k, B, obstacle_pts, field, noise=None, out=None, pins_q=None,
+                    pins_s=None):
         """Stage II body up to (not including) the selection (:553-591): returns the batch [B, H, D].
         `field` must already hold this tick's pursuer cloud (host protocol, see ddim_p_sample_loop)."""
         H, D = x_clean.shape
@@ -175,8 +176,9 @@ class DynamicGaussianDiffusionModel(_DiffusionBase):
         ts = self.ddim_set_timesteps(self.ddim_num_inference_steps_high)
         low = ts[-self.ddim_num_inference_steps_low:]
         goal_row = x_clean[-1].clone()
-        pins_q = self._history_pins(history, goal_row, H, D, dev, zero_start_velocity=False)
-        pins_s = self._history_pins(history, goal_row, H, D, dev, zero_start_velocity=True)
+        if pins_q is None:
+            pins_q = self._history_pins(history, goal_row, H, D, dev, zero_start_velocity=False)
+            pins_s = self._history_pins(history, goal_row, H, D, dev, zero_start_velocity=True)
         if noise is None:
             noise = torch.randn((B, H, D), device=dev)
         x = torch.empty(B, H, D, device=dev) if out is None else out

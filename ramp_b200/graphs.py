@@ -1,0 +1,141 @@
+"""CUDA-graph capture of the fixed-step loops (north_star (3): "the whole fixed-step loop is captured as a CUDA
+Graph for real-time replanning latency").
+
+Every kernel of the library is enqueued on torch's current stream through the C ABI, so a loop is captured by
+running it once inside `torch.cuda.graph`: per-step scalars are kernel arguments (baked into the graph nodes), the
+noise is drawn by `torch.randn` inside the capture (graph-safe Philox offsets advance on every replay), and nothing in
+the captured region allocates through the library (weights, workspace and tensor maps exist after the warm-up pass).
+
+* `DdpmLoopGraph`  — `p_sample_loop` + `ddpm_sample_fn` of the static / 3-D samplers (diffusion_model_static.py:231-256,
+  diffusion_model_3d.py:184-218): T steps of (score network over B*(G+1) rows, fused posterior step).
+* `ReplanGraph`    — one stage-II tick of the dynamic planner (diffusion_model_dynamic.py:553-598): q_sample, pins,
+  5 DDIM steps with the point-cloud potential field on the last, smoothing, cost terms, best-of-N selection.  The moving
+  pursuer enters through two small static buffers (disc points, centre) refreshed by the host before each replay.
+"""
+import torch
+
+from . import ops
+from ._lib import RampError
+
+
+def _capture(fn, warmup=2):
+    """Warm up on a side stream (lazy initialisation, autotuned launch attributes, scene cache), then capture."""
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(warmup):
+            fn()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        out = fn()
+    return g, out
+
+
+class DdpmLoopGraph:
+    """Graph of one complete DDPM sampling (x_T draw, T reverse steps, inpainting) for a fixed batch."""
+
+    def __init__(self, model, batch, horizon, hard_conds, obstacle_pts, noise_scale=0.5, extra_steps=0):
+        if not next(model.parameters()).is_cuda:
+            raise RampError("graphs need a CUDA model")
+        self.model = model
+        dev = model.betas.device
+        B, H, D = batch, horizon, model.state_dim
+        T = model.n_diffusion_steps
+        hc = model._repeat_hard_conds(hard_conds, B)
+        self.pins = ops.Pins.from_hard_conds(hc, B, H, D, dev)
+        if not model.compose and obstacle_pts.dim() == 3:
+            obstacle_pts = obstacle_pts.unsqueeze(0)
+        self.cloud = obstacle_pts.to(dev).float().contiguous()
+        self.chain = torch.empty(T + extra_steps + 1, B, H, D, device=dev)
+        steps = [max(i, 0) for i in reversed(range(-extra_steps, T))]
+
+        def loop():
+            self.chain[0] = torch.randn((B, H, D), device=dev)
+            ops.inpaint(self.chain[0], self.pins)
+            for k, t in enumerate(steps):
+                noise = torch.randn((B, H, D), device=dev)
+                model._ddpm_step(self.chain[k], t, self.cloud, noise if t > 0 else None, noise_scale,
+                                 compose=model.compose, pins=self.pins, out=self.chain[k + 1])
+            return self.chain
+
+        self.graph, _ = _capture(loop)
+
+    def replay(self):
+        """Runs the captured loop on the current stream; returns the chain [T+1, B, H, D] (static buffer)."""
+        self.graph.replay()
+        return self.chain
+
+
+class ReplanGraph:
+    """Graph of one replan tick of DynamicGaussianDiffusionModel for tick index k (= number of executed states - 1).
+
+    Static inputs (update in place, then `replay()`): `x_clean` [H, D] current plan, `history` [k+1, D] executed states,
+    `disc_points` [Pd, 2] + `disc_center` [2] pursuer cloud, and the cost cloud whose last Pd points are the disc.
+    Outputs (static): `batch` [B, H, D], `sel` [8] (ramp_select_best), `best` [H, D]."""
+
+    def __init__(self, model, batch, horizon, k, obstacle_pts, static_points, disc_points, cost_static_points,
+                 collision_threshold=None):
+        self.model = model
+        dev = model.betas.device
+        B, H, D = batch, horizon, model.state_dim
+        self.k = k
+        self.cloud = obstacle_pts.to(dev).float().contiguous()
+        self.x_clean = torch.zeros(H, D, device=dev)
+        self.history = torch.zeros(k + 1, D, device=dev)
+        self.disc_points = disc_points.to(dev).float().contiguous().clone()
+        self.disc_center = torch.zeros(2, device=dev)
+        Pd = self.disc_points.shape[0]
+        cs = cost_static_points.to(dev).float().reshape(-1, 2)
+        self.cost_points = torch.cat([cs, self.disc_points], dim=0).contiguous()
+        self._cost_disc = self.cost_points[cs.shape[0]:]
+        self.cost_cloud = ops.CloudIndex(self.cost_points)
+        self.cost_cloud.points = self.cost_points            # pack from the live buffer on every replay
+        thr = model.collision_threshold_low if collision_threshold is None else collision_threshold
+
+        class _Field:          # the three attributes _apf_x0 reads, bound to the static buffers
+            pass
+
+        f = _Field()
+        f.static_cloud = ops.CloudIndex(static_points.to(dev).float())
+        f.dynamic_cloud = ops.CloudIndex(self.disc_points)
+        f.dynamic_cloud.points = self.disc_points
+        f.dynamic_center_dev = self.disc_center
+        f.distance_threshold = model.distance_threshold_static
+        f.distance_threshold_pred = model.distance_threshold_pred_apf
+        self.field = f
+        mask = torch.zeros(H, dtype=torch.uint8)
+        mask[:k + 1] = 1
+        mask[H - 1] = 1
+        self.pins_q = ops.Pins(mask.to(dev), torch.zeros(1, H, D, device=dev))
+        self.pins_s = ops.Pins(mask.to(dev), torch.zeros(1, H, D, device=dev))
+        self.batch = torch.empty(B, H, D, device=dev)
+        self.terms = torch.empty(B, 3, device=dev)
+        self.sel = torch.empty(8, device=dev)
+        self.best = torch.empty(H, D, device=dev)
+
+        def tick():
+            # pins from the static inputs (device-side copies: part of the graph)
+            for p, zero_v in ((self.pins_q, False), (self.pins_s, True)):
+                p.val[0, :k + 1] = self.history
+                p.val[0, H - 1] = self.x_clean[-1]
+                if zero_v:
+                    p.val[0, 0, 2:] = 0.0
+            self._cost_disc.copy_(self.disc_points)
+            self.field.dynamic_cloud.repack()
+            self.cost_cloud.repack()
+            model._tick_batch(self.x_clean, None, k, k, B, self.cloud, self.field, out=self.batch, pins_q=self.pins_q,
+                              pins_s=self.pins_s)
+            ops.cost_terms(self.batch, self.cost_cloud, thr, terms=self.terms)
+            ops.select_best(self.terms, out=self.sel)
+            idx = self.sel[0].clamp(min=0).long().reshape(1)
+            self.best.copy_(self.batch.index_select(0, idx)[0])
+            self.best[0, 2:] = 0.0                                    # diffusion_model_dynamic.py:609
+            return self.best
+
+        self.graph, _ = _capture(tick)
+
+    def replay(self):
+        self.graph.replay()
+        return self.best

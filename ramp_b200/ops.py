@@ -119,6 +119,11 @@ class CloudIndex:
         self.packed = torch.empty(n, 4, device=pts.device)
         check(lib().ramp_cloud_pack(ptr(pts), self.P, self.dim, ptr(self.packed), _stream()), "ramp_cloud_pack")
 
+    def repack(self):
+        """Re-pack after `self.points` was updated in place (a moving pursuer): one kernel, graph-capturable."""
+        check(lib().ramp_cloud_pack(ptr(self.points), self.P, self.dim, ptr(self.packed), _stream()), "ramp_cloud_pack")
+        return self
+
     def query(self, x, upper_bound, dist=None, idx=None):
         """x: [..., D] trajectories (positions = first `dim` channels).  Returns (dist, idx) shaped like x[..., 0]."""
         _need_cuda(x)
