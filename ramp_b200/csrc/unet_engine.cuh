@@ -39,7 +39,7 @@ struct STW {
 
 // forward activations kept for the backward sweep
 struct ResSave { float* c1; float* c2; };
-struct TBlockSave { float* zin; float* qkv; float* z1; float* u; float* stats1; float* stats3; };   // stats: (mean, rstd) per token
+struct TBlockSave { float* zin; float* qkv; Split qkv_s; float* z1; float* u; float* stats1; float* stats3; };   // qkv_s: planes (tensor-core attention)   // stats: (mean, rstd) per token
 struct GemmFuse {      // fused-epilogue request for UnetEngine::gemm (see GemmEpi in common.cuh)
   int epi = EPI_PLAIN;
   const float* ln_gamma = nullptr; const float* ln_beta = nullptr; float* ln_stats = nullptr; const float* ln_x = nullptr;

@@ -44,6 +44,11 @@ int attn_forward(const float* qkv, int n_samples, int L, bf16* out_hi, bf16* out
 // dqkv hi/lo [rows, 768] from d_out fp32 [rows, 256]
 int attn_backward(const float* qkv, const float* d_out, int n_samples, int L, bf16* dq_hi, bf16* dq_lo, cudaStream_t s);
 
+// tensor-core variants (attn_tc.cu, L = 64 / 32): operands and gradients are bf16 hi/lo planes end to end
+bool attn_tc_supported(int L);
+int attn_forward_tc(const bf16* qkv_hi, const bf16* qkv_lo, int n_samples, int L, bf16* out_hi, bf16* out_lo, cudaStream_t s);
+int attn_backward_tc(const bf16* qkv_hi, const bf16* qkv_lo, const bf16* do_hi, const bf16* do_lo, int n_samples, int L,
+                     bf16* dq_hi, bf16* dq_lo, cudaStream_t s);
 // any L <= 64 (one CTA per (sample, head), scalar smem loops) — used when L is not 8/16/32/64
 int attn_forward_generic(const float* qkv, int n_samples, int L, bf16* out_hi, bf16* out_lo, cudaStream_t s);
 int attn_backward_generic(const float* qkv, const float* d_out, int n_samples, int L, bf16* dq_hi, bf16* dq_lo, cudaStream_t s);

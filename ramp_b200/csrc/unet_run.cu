@@ -155,12 +155,21 @@ int UnetEngine::st_fwd(const STW& w, const Act& x, int L, const OutSpec& o, Act&
     const TBlockW& t = w.blk[b];
     TBlockSave& ts = sv.blk[b];
     ts.zin = z;
-    ts.qkv = allocf(M * 768);
+    const bool tc = attn_tc_supported(L);       // L = 64 / 32: q, k, v stay bf16 hi/lo planes for the mma.sync attention
     Act aa; aa.hi = a.hi; aa.lo = a.lo; aa.lds = 256;
-    TRY(gemm(aa, 256, t.qkv_f, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, ts.qkv, 768, nullptr,
-             nullptr, 0, L, 1, 0));
     Split ao = allocs(M * 256);
-    if (!dry_) { ProfScope ps(this, 2); TRY(attn_forward(ts.qkv, npad_, L, ao.hi, ao.lo, s_)); }
+    if (tc) {
+      ts.qkv = nullptr;
+      ts.qkv_s = allocs(M * 768);
+      TRY(gemm(aa, 256, t.qkv_f, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, nullptr, 0, ts.qkv_s.hi,
+               ts.qkv_s.lo, 768, L, 1, 0));
+      if (!dry_) { ProfScope ps(this, 2); TRY(attn_forward_tc(ts.qkv_s.hi, ts.qkv_s.lo, npad_, L, ao.hi, ao.lo, s_)); }
+    } else {
+      ts.qkv = allocf(M * 768);
+      TRY(gemm(aa, 256, t.qkv_f, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, ts.qkv, 768, nullptr,
+               nullptr, 0, L, 1, 0));
+      if (!dry_) { ProfScope ps(this, 2); TRY(attn_forward(ts.qkv, npad_, L, ao.hi, ao.lo, s_)); }
+    }
     // attn1.to_out (+ collapsed attn2 constant per scene) + residual -> z1, LayerNorm3 fused
     ts.z1 = allocf(M * 256);
     ts.stats3 = allocf(M * 2);
@@ -238,12 +247,22 @@ int UnetEngine::st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act
       TRY(gemm(dua, 2048, t.ff1_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, dz, 256, nullptr, 0, dz1, 256, dz1s.hi, dz1s.lo,
                256, L, 1, 0, &f));
     }
-    float* dout = allocf(M * 256);
     Act d1a; d1a.hi = dz1s.hi; d1a.lo = dz1s.lo; d1a.lds = 256;
-    TRY(gemm(d1a, 256, t.o_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dout, 256, nullptr, nullptr,
-             0, L, 1, 0));
     Split dqkv = allocs(M * 768);
-    if (!dry_) { ProfScope ps(this, 2); TRY(attn_backward(ts.qkv, dout, npad_, L, dqkv.hi, dqkv.lo, s_)); }
+    if (attn_tc_supported(L)) {
+      Split douts = allocs(M * 256);
+      TRY(gemm(d1a, 256, t.o_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, nullptr, 0, douts.hi,
+               douts.lo, 256, L, 1, 0));
+      if (!dry_) {
+        ProfScope ps(this, 2);
+        TRY(attn_backward_tc(ts.qkv_s.hi, ts.qkv_s.lo, douts.hi, douts.lo, npad_, L, dqkv.hi, dqkv.lo, s_));
+      }
+    } else {
+      float* dout = allocf(M * 256);
+      TRY(gemm(d1a, 256, t.o_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dout, 256, nullptr, nullptr,
+               0, L, 1, 0));
+      if (!dry_) { ProfScope ps(this, 2); TRY(attn_backward(ts.qkv, dout, npad_, L, dqkv.hi, dqkv.lo, s_)); }
+    }
     // QKV^T with the LayerNorm1 backward in the epilogue: dz = dz1 + LN1'(zin, .)
     dz = allocf(M * 256);
     dzs = allocs(M * 256);
