@@ -79,7 +79,7 @@ def build_model(device, max_rows):
 
 def run_ours(args):
     import torch.distributed as dist
-    from ramp_b200 import ops
+    from ramp_b200 import ops, sharding
     from ramp_b200._lib import lib
     from ramp_b200.sample_functions import ddpm_sample_fn
     from ramp_b200.testing import synthetic_cloud_2d
@@ -103,11 +103,7 @@ def run_ours(args):
 
     def select(final):
         terms = ops.cost_terms(final.contiguous(), cost_cloud, 0.05)
-        if world > 1:
-            allt = torch.empty(world * B, 3, device=dev)
-            dist.all_gather_into_tensor(allt, terms)
-            terms = allt
-        return ops.select_best(terms)
+        return ops.select_best(sharding.gather_terms(terms, world * B))   # NCCL all-gather of 12 B per trajectory
 
     def resident_step():
         chain = model.run_inference(None, hc, n_samples=B, horizon=H, return_chain=True, traj_normalized=zeros_traj,
@@ -166,6 +162,9 @@ def run_ours(args):
         model.model.release_engine()
         torch.cuda.empty_cache()
         replan = replan_latency(dev, args.replan_ticks, max(3, args.replan_ticks // 10))
+    field = None
+    if rank == 0 and not args.no_field:
+        field = field_roofline(dev, sampler.summary().get("sm_mhz"))
     if rank == 0:
         peak_tf, peak_bw, how = peaks()
         rows_per_step = B * (G + 1) * T
@@ -199,10 +198,51 @@ def run_ours(args):
             line["cpu_baseline"] = cpu_baseline(sample_B=args.cpu_sample)
         if replan is not None:
             line["replan"] = replan
+        if field is not None:
+            line["field"] = field
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------------
+# Potential-field kernel roofline (north_star (2)): the nearest-point query that feeds the APF push and the
+# collision test, at the sweep's cloud size.  Algorithmic work = 3d - 1 FLOPs per (waypoint, point) pair
+# (SURVEY §8d); FP32 peak = SMs x 128 lanes x 2 x the SM clock sampled under load.
+# ---------------------------------------------------------------------------------------------------
+def field_roofline(dev, sm_mhz):
+    from ramp_b200 import ops
+    out = {}
+    g = torch.Generator("cpu").manual_seed(7)
+    for dim, D_ in ((2, 4), (3, 6)):
+        P, Bq = 1 << 20, 2048
+        centres = torch.rand(256, dim, generator=g) * 2 - 1
+        pts = (centres[torch.randint(0, 256, (P,), generator=g)] + 0.05 * torch.randn(P, dim, generator=g)).to(dev)
+        x = (torch.rand(Bq, H, D_, generator=g) * 2 - 1).to(dev)
+        cloud = ops.CloudIndex(pts)
+        dist = torch.empty(Bq, H, device=dev)
+        idx = torch.empty(Bq, H, device=dev, dtype=torch.int32)
+        for _ in range(2):
+            cloud.query(x, 0.07, dist, idx)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        reps = 5
+        e0.record()
+        for _ in range(reps):
+            cloud.query(x, 0.07, dist, idx)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        pairs = float(Bq * H) * P
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        peak = sms * 128 * 2 * (sm_mhz or 1965) * 1e6 / 1e12
+        ach = pairs * (3 * dim - 1) / (ms * 1e-3) / 1e12
+        out["d%d" % dim] = {"waypoints": Bq * H, "cloud_points": P, "ms": ms, "pairs_per_s": pairs / (ms * 1e-3),
+                            "achieved_tflops": ach, "fp32_peak_tflops": peak, "frac": ach / peak,
+                            "algorithmic_flops_per_pair": 3 * dim - 1}
+    out["kernel"] = "nn_query_kernel (TMA-bulk staged cloud tiles, register-blocked waypoints, exact re-scan)"
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -339,6 +379,7 @@ def main():
     ap.add_argument("--batch", type=int, default=B_PER_GPU, help="trajectories per GPU")
     ap.add_argument("--max-rows", type=int, default=1792, help="network rows per engine call (workspace size)")
     ap.add_argument("--cpu-sample", type=int, default=2, help="trajectories in the bounded CPU sample")
+    ap.add_argument("--no-field", action="store_true", help="skip the potential-field kernel roofline section")
     ap.add_argument("--replan-ticks", type=int, default=60, help="timed replan ticks of the dynamic planner (0 = skip)")
     ap.add_argument("--dump-launches", default="", help="write the per-launch CUDA-event CSV of one profiled step here")
     args = ap.parse_args()

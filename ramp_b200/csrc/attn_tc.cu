@@ -1,4 +1,4 @@
-// Tensor-core self-attention core (layers_attention_mini.py:100-126) for L = 64 / 32 tokens, 4 heads x 64, and its
+// Tensor-core self-attention core (layers_attention_mini.py:100-126) for L = 64 / 32 / 16 tokens, 4 heads x 64, and its
 // input gradient (autograd at UnetInference.py:23-27), on mma.sync.m16n8k16 bf16 with split-precision operands:
 // every product A.B is issued as A_lo.B_hi + A_hi.B_lo + A_hi.B_hi into one fp32 accumulator (error ~2^-17), the
 // same scheme as the tcgen05 GEMM.  tcgen05 does not fit here: a (sample, head) problem is a 64x64x64 batch item and
@@ -36,10 +36,10 @@ __device__ __forceinline__ void mma3(float (&c)[4], const uint32_t (&ah)[4], con
 }
 
 // bf16 tile [rows][NCH * 8] in shared memory, 16-byte chunks XOR-swizzled so that the 8 row addresses of an
-// ldmatrix 8x8 block fall into 8 different bank groups (NCH = 8: 128-byte rows; NCH = 4: 64-byte rows).
+// ldmatrix 8x8 block fall into 8 different bank groups (NCH = 8: 128-byte rows; 4: 64-byte rows; 2: 32-byte rows).
 template <int NCH>
 __device__ __forceinline__ uint32_t tile_off(int r, int c) {
-  return (uint32_t)(r * NCH * 16 + ((c ^ (NCH == 8 ? (r & 7) : ((r >> 1) & 3))) << 4));
+  return (uint32_t)(r * NCH * 16 + ((c ^ (NCH == 8 ? (r & 7) : (NCH == 4 ? ((r >> 1) & 3) : ((r >> 2) & 1)))) << 4));
 }
 // global bf16 [L rows, ld] (64 columns used) -> tile, by the `nth` threads of one problem (cp.async, 16 B each)
 template <int L>
@@ -331,18 +331,20 @@ static int launch_bwd_tc(const bf16* qh, const bf16* ql, const bf16* dh, const b
   return 0;
 }
 
-bool attn_tc_supported(int L) { return L == 64 || L == 32; }
+bool attn_tc_supported(int L) { return L == 64 || L == 32 || L == 16; }
 
 int attn_forward_tc(const bf16* qkv_hi, const bf16* qkv_lo, int n_samples, int L, bf16* out_hi, bf16* out_lo, cudaStream_t s) {
   if (L == 64) return launch_fwd_tc<64>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
   if (L == 32) return launch_fwd_tc<32>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
-  RAMP_CHECK(false, "attn_forward_tc: L must be 64 or 32");
+  if (L == 16) return launch_fwd_tc<16>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
+  RAMP_CHECK(false, "attn_forward_tc: L must be 64, 32 or 16");
 }
 int attn_backward_tc(const bf16* qkv_hi, const bf16* qkv_lo, const bf16* do_hi, const bf16* do_lo, int n_samples, int L,
                      bf16* dq_hi, bf16* dq_lo, cudaStream_t s) {
   if (L == 64) return launch_bwd_tc<64>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
   if (L == 32) return launch_bwd_tc<32>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
-  RAMP_CHECK(false, "attn_backward_tc: L must be 64 or 32");
+  if (L == 16) return launch_bwd_tc<16>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
+  RAMP_CHECK(false, "attn_backward_tc: L must be 64, 32 or 16");
 }
 
 }  // namespace ramp

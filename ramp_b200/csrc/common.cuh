@@ -86,6 +86,19 @@ __device__ __forceinline__ float gelu_grad_f(float x) {
   return cdf + x * pdf;
 }
 
+// Phi(x) and phi(x) of the standard normal from ONE exponential: erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7,
+// no cancellation on the negative side), phi(x) = exp(-x^2/2) / sqrt(2 pi) shares the exponential.  Used by the fused
+// GEGLU epilogue, where the few epilogue warps are instruction-issue bound (erff + expf cost 2.5x as much).
+__device__ __forceinline__ void normal_cdf_pdf(float x, float& cdf, float& pdf) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = __fdividef(1.f, fmaf(0.3275911f, z, 1.f));
+  const float e = expf(-z * z);
+  const float poly = t * fmaf(t, fmaf(t, fmaf(t, fmaf(t, 1.061405429f, -1.453152027f), 1.421413741f), -0.284496736f), 0.254829592f);
+  const float half = 0.5f * poly * e;
+  cdf = x < 0.f ? half : 1.f - half;
+  pdf = 0.39894228040143268f * e;
+}
+
 // ---- tcgen05 GEMM host interface (gemm_tc.cu) ----------------------------------------------------
 // D[rows, Nout] = sum_taps A_tap[rows, K] * W_tap[Nout, K]^T  (+bias, +residual), rows = n_samples * L_out.
 // A is a channels-last activation [n_samples, L_in, ldA] given as hi/lo bf16 planes; tap t reads the
