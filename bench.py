@@ -216,7 +216,7 @@ def field_roofline(dev, sm_mhz):
     out = {}
     g = torch.Generator("cpu").manual_seed(7)
     for dim, D_ in ((2, 4), (3, 6)):
-        P, Bq = 1 << 20, 2048
+        P, Bq = 1 << 20, 8192          # the sweep's per-GPU shard: 8192 trajectories x 64 waypoints, 1 M cloud points
         centres = torch.rand(256, dim, generator=g) * 2 - 1
         pts = (centres[torch.randint(0, 256, (P,), generator=g)] + 0.05 * torch.randn(P, dim, generator=g)).to(dev)
         x = (torch.rand(Bq, H, D_, generator=g) * 2 - 1).to(dev)
@@ -377,7 +377,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=B_PER_GPU, help="trajectories per GPU")
-    ap.add_argument("--max-rows", type=int, default=1792, help="network rows per engine call (workspace size)")
+    ap.add_argument("--max-rows", type=int, default=7168, help="network rows per engine call (workspace size)")
     ap.add_argument("--cpu-sample", type=int, default=2, help="trajectories in the bounded CPU sample")
     ap.add_argument("--no-field", action="store_true", help="skip the potential-field kernel roofline section")
     ap.add_argument("--replan-ticks", type=int, default=60, help="timed replan ticks of the dynamic planner (0 = skip)")

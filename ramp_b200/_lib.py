@@ -4,7 +4,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_PATH = os.path.join(_HERE, "libramp_b200.so")
+_PATH = os.environ.get("RAMP_B200_LIB") or os.path.join(_HERE, "libramp_b200.so")   # override: A/B kernel variants
 _lib = None
 
 c_void_p, c_int, c_float, c_size_t = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_size_t

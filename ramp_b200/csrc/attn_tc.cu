@@ -1,4 +1,4 @@
-// Tensor-core self-attention core (layers_attention_mini.py:100-126) for L = 64 / 32 / 16 tokens, 4 heads x 64, and its
+// Tensor-core self-attention core (layers_attention_mini.py:100-126) for L = 64 / 32 / 16 / 8 tokens (8 runs zero-padded to 16 with masked keys), 4 heads x 64, and its
 // input gradient (autograd at UnetInference.py:23-27), on mma.sync.m16n8k16 bf16 with split-precision operands:
 // every product A.B is issued as A_lo.B_hi + A_hi.B_lo + A_hi.B_hi into one fp32 accumulator (error ~2^-17), the
 // same scheme as the tcgen05 GEMM.  tcgen05 does not fit here: a (sample, head) problem is a 64x64x64 batch item and
@@ -41,12 +41,16 @@ template <int NCH>
 __device__ __forceinline__ uint32_t tile_off(int r, int c) {
   return (uint32_t)(r * NCH * 16 + ((c ^ (NCH == 8 ? (r & 7) : (NCH == 4 ? ((r >> 1) & 3) : ((r >> 2) & 1)))) << 4));
 }
-// global bf16 [L rows, ld] (64 columns used) -> tile, by the `nth` threads of one problem (cp.async, 16 B each)
-template <int L>
+// global bf16 [LV rows, ld] (64 columns used) -> tile of L >= LV rows (rows >= LV zero-filled), by the `nth` threads of
+// one problem (cp.async, 16 B each)
+template <int L, int LV>
 __device__ __forceinline__ void load_tile(uint32_t tile, const bf16* __restrict__ g, int ld, int t, int nth) {
   for (int idx = t; idx < L * 8; idx += nth) {
     const int r = idx >> 3, c = idx & 7;
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile + tile_off<8>(r, c)), "l"(g + (size_t)r * ld + c * 8));
+    if (r < LV)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile + tile_off<8>(r, c)), "l"(g + (size_t)r * ld + c * 8));
+    else
+      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(tile + tile_off<8>(r, c)), "r"(0));
   }
 }
 __device__ __forceinline__ void cp_async_wait_all() {
@@ -108,13 +112,14 @@ __device__ __forceinline__ void qk_product(uint32_t Ah, uint32_t Al, uint32_t Xh
   }
 }
 // rows g and g + 8 of the warp's 16 x L block: p = softmax(scale * s)
-template <int L>
+template <int L, int LV>
 __device__ __forceinline__ void softmax_frag(float (&s)[L / 8][4]) {
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
     float m = -INFINITY;
 #pragma unroll
     for (int nt = 0; nt < L / 8; ++nt) {
+      if (8 * nt >= LV) { s[nt][2 * h] = -INFINITY; s[nt][2 * h + 1] = -INFINITY; }     // padded keys
       s[nt][2 * h] *= 0.125f; s[nt][2 * h + 1] *= 0.125f;
       m = fmaxf(m, fmaxf(s[nt][2 * h], s[nt][2 * h + 1]));
     }
@@ -157,7 +162,8 @@ __device__ __forceinline__ void pv_product(const float (&p)[L / 8][4], uint32_t 
   }
 }
 // 16 x 64 accumulator block -> hi / lo planes, rows row0 + {g, g + 8}, columns col0 + 8 dn + 2 t
-__device__ __forceinline__ void store_frag(const float (&o)[8][4], bf16* hi, bf16* lo, size_t row0, int ld, int col0, int lane) {
+__device__ __forceinline__ void store_frag(const float (&o)[8][4], bf16* hi, bf16* lo, size_t row0, int ld, int col0, int lane,
+                                           bool second_half = true) {
   const int g = lane >> 2, t = lane & 3;
 #pragma unroll
   for (int dn = 0; dn < 8; ++dn) {
@@ -166,7 +172,7 @@ __device__ __forceinline__ void store_frag(const float (&o)[8][4], bf16* hi, bf1
     split2_bf16(o[dn][2], o[dn][3], h1, l1);
     const size_t a = (row0 + g) * ld + col0 + 8 * dn + 2 * t, b = a + (size_t)8 * ld;
     *reinterpret_cast<uint32_t*>(hi + a) = h0; *reinterpret_cast<uint32_t*>(lo + a) = l0;
-    *reinterpret_cast<uint32_t*>(hi + b) = h1; *reinterpret_cast<uint32_t*>(lo + b) = l1;
+    if (second_half) { *reinterpret_cast<uint32_t*>(hi + b) = h1; *reinterpret_cast<uint32_t*>(lo + b) = l1; }
   }
 }
 
@@ -179,7 +185,7 @@ template <int L> struct TcShape {
   static constexpr int BWD_BYTES = 8 * TILE + 4 * PT;   // Q, K, V, dO hi/lo + P, dS hi/lo
 };
 
-template <int L>
+template <int L, int LV>     // L = tile rows (multiple of 16), LV = tokens (LV < L: zero-padded queries / masked keys)
 __global__ void __launch_bounds__(128) attn_fwd_tc(const bf16* __restrict__ qkv_hi, const bf16* __restrict__ qkv_lo,
                                                    int n_problems, bf16* __restrict__ out_hi, bf16* __restrict__ out_lo) {
   using S = TcShape<L>;
@@ -192,11 +198,11 @@ __global__ void __launch_bounds__(128) attn_fwd_tc(const bf16* __restrict__ qkv_
   const uint32_t Qh = base, Ql = base + S::TILE, Kh = base + 2 * S::TILE, Kl = base + 3 * S::TILE, Vh = base + 4 * S::TILE,
                  Vl = base + 5 * S::TILE;
   if (prob < n_problems) {
-    const size_t off = (size_t)n * L * 768 + h * 64;
+    const size_t off = (size_t)n * LV * 768 + h * 64;
     const int t = wp * 32 + lane, nth = S::W * 32;
-    load_tile<L>(Qh, qkv_hi + off, 768, t, nth);        load_tile<L>(Ql, qkv_lo + off, 768, t, nth);
-    load_tile<L>(Kh, qkv_hi + off + 256, 768, t, nth);  load_tile<L>(Kl, qkv_lo + off + 256, 768, t, nth);
-    load_tile<L>(Vh, qkv_hi + off + 512, 768, t, nth);  load_tile<L>(Vl, qkv_lo + off + 512, 768, t, nth);
+    load_tile<L, LV>(Qh, qkv_hi + off, 768, t, nth);        load_tile<L, LV>(Ql, qkv_lo + off, 768, t, nth);
+    load_tile<L, LV>(Kh, qkv_hi + off + 256, 768, t, nth);  load_tile<L, LV>(Kl, qkv_lo + off + 256, 768, t, nth);
+    load_tile<L, LV>(Vh, qkv_hi + off + 512, 768, t, nth);  load_tile<L, LV>(Vl, qkv_lo + off + 512, 768, t, nth);
   }
   cp_async_wait_all();
   __syncthreads();
@@ -204,10 +210,10 @@ __global__ void __launch_bounds__(128) attn_fwd_tc(const bf16* __restrict__ qkv_
   const int m0 = 16 * wp;
   float s[L / 8][4];
   qk_product<L>(Qh, Ql, Kh, Kl, m0, lane, s);
-  softmax_frag<L>(s);
+  softmax_frag<L, LV>(s);
   float o[8][4];
   pv_product<L>(s, Vh, Vl, lane, o);
-  store_frag(o, out_hi, out_lo, (size_t)n * L + m0, 256, h * 64, lane);
+  store_frag(o, out_hi, out_lo, (size_t)n * LV + m0, 256, h * 64, lane, m0 + 8 < LV);
 }
 
 // (row g | g + 8, columns 8 nt + 2 t) of a 16 x L fragment block -> bf16 hi / lo tiles [L][L] at rows m0 + .
@@ -247,7 +253,7 @@ __device__ __forceinline__ void tn_product(uint32_t Mh, uint32_t Ml, uint32_t Xh
   }
 }
 
-template <int L>
+template <int L, int LV>
 __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_hi, const bf16* __restrict__ qkv_lo,
                                                    const bf16* __restrict__ do_hi, const bf16* __restrict__ do_lo,
                                                    int n_problems, bf16* __restrict__ dq_hi, bf16* __restrict__ dq_lo) {
@@ -263,21 +269,22 @@ __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_
                  Vl = base + 5 * S::TILE, Dh = base + 6 * S::TILE, Dl = base + 7 * S::TILE;
   const uint32_t Ph = base + 8 * S::TILE, Pl = Ph + S::PT, Gh = Pl + S::PT, Gl = Gh + S::PT;     // G = dS
   if (live) {
-    const size_t off = (size_t)n * L * 768 + h * 64, offd = (size_t)n * L * 256 + h * 64;
+    const size_t off = (size_t)n * LV * 768 + h * 64, offd = (size_t)n * LV * 256 + h * 64;
     const int t = wp * 32 + lane, nth = S::W * 32;
-    load_tile<L>(Qh, qkv_hi + off, 768, t, nth);        load_tile<L>(Ql, qkv_lo + off, 768, t, nth);
-    load_tile<L>(Kh, qkv_hi + off + 256, 768, t, nth);  load_tile<L>(Kl, qkv_lo + off + 256, 768, t, nth);
-    load_tile<L>(Vh, qkv_hi + off + 512, 768, t, nth);  load_tile<L>(Vl, qkv_lo + off + 512, 768, t, nth);
-    load_tile<L>(Dh, do_hi + offd, 256, t, nth);        load_tile<L>(Dl, do_lo + offd, 256, t, nth);
+    load_tile<L, LV>(Qh, qkv_hi + off, 768, t, nth);        load_tile<L, LV>(Ql, qkv_lo + off, 768, t, nth);
+    load_tile<L, LV>(Kh, qkv_hi + off + 256, 768, t, nth);  load_tile<L, LV>(Kl, qkv_lo + off + 256, 768, t, nth);
+    load_tile<L, LV>(Vh, qkv_hi + off + 512, 768, t, nth);  load_tile<L, LV>(Vl, qkv_lo + off + 512, 768, t, nth);
+    load_tile<L, LV>(Dh, do_hi + offd, 256, t, nth);        load_tile<L, LV>(Dl, do_lo + offd, 256, t, nth);
   }
   cp_async_wait_all();
   __syncthreads();
   const int m0 = 16 * wp;
-  const size_t row0 = (size_t)n * L + m0;
+  const size_t row0 = (size_t)n * LV + m0;
+  const bool half2 = m0 + 8 < LV;
   if (live) {
     float p[L / 8][4], dp[L / 8][4];
     qk_product<L>(Qh, Ql, Kh, Kl, m0, lane, p);
-    softmax_frag<L>(p);
+    softmax_frag<L, LV>(p);
     qk_product<L>(Dh, Dl, Vh, Vl, m0, lane, dp);           // dP = dO V^T
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {                        // dS = P * (dP - rowsum(P * dP)) * scale
@@ -295,56 +302,58 @@ __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_
     park_frag<L>(dp, Gh, Gl, m0, lane);
     float o[8][4];
     pv_product<L>(dp, Kh, Kl, lane, o);                     // dQ = dS K
-    store_frag(o, dq_hi, dq_lo, row0, 768, h * 64, lane);
+    store_frag(o, dq_hi, dq_lo, row0, 768, h * 64, lane, half2);
   }
   __syncthreads();
   if (live) {
     float o[8][4];
     tn_product<L>(Ph, Pl, Dh, Dl, m0, lane, o);             // dV = P^T dO   (m0 doubles as the key-row block)
-    store_frag(o, dq_hi, dq_lo, row0, 768, 512 + h * 64, lane);
+    store_frag(o, dq_hi, dq_lo, row0, 768, 512 + h * 64, lane, half2);
     tn_product<L>(Gh, Gl, Qh, Ql, m0, lane, o);             // dK = dS^T Q
-    store_frag(o, dq_hi, dq_lo, row0, 768, 256 + h * 64, lane);
+    store_frag(o, dq_hi, dq_lo, row0, 768, 256 + h * 64, lane, half2);
   }
 }
 
-template <int L>
+template <int L, int LV>
 static int launch_fwd_tc(const bf16* qh, const bf16* ql, int n_samples, bf16* oh, bf16* ol, cudaStream_t s) {
   using S = TcShape<L>;
   static bool attr = false;
   const int smem = S::NP * S::FWD_BYTES;
-  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_fwd_tc<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
+  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_fwd_tc<L, LV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
   const int np = n_samples * 4;
-  attn_fwd_tc<L><<<(np + S::NP - 1) / S::NP, 128, smem, s>>>(qh, ql, np, oh, ol);
+  attn_fwd_tc<L, LV><<<(np + S::NP - 1) / S::NP, 128, smem, s>>>(qh, ql, np, oh, ol);
   RAMP_LAUNCH_OK();
   return 0;
 }
-template <int L>
+template <int L, int LV>
 static int launch_bwd_tc(const bf16* qh, const bf16* ql, const bf16* dh, const bf16* dl, int n_samples, bf16* oh, bf16* ol,
                          cudaStream_t s) {
   using S = TcShape<L>;
   static bool attr = false;
   const int smem = S::NP * S::BWD_BYTES;
-  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_bwd_tc<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
+  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_bwd_tc<L, LV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
   const int np = n_samples * 4;
-  attn_bwd_tc<L><<<(np + S::NP - 1) / S::NP, 128, smem, s>>>(qh, ql, dh, dl, np, oh, ol);
+  attn_bwd_tc<L, LV><<<(np + S::NP - 1) / S::NP, 128, smem, s>>>(qh, ql, dh, dl, np, oh, ol);
   RAMP_LAUNCH_OK();
   return 0;
 }
 
-bool attn_tc_supported(int L) { return L == 64 || L == 32 || L == 16; }
+bool attn_tc_supported(int L) { return L == 64 || L == 32 || L == 16 || L == 8; }
 
 int attn_forward_tc(const bf16* qkv_hi, const bf16* qkv_lo, int n_samples, int L, bf16* out_hi, bf16* out_lo, cudaStream_t s) {
-  if (L == 64) return launch_fwd_tc<64>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
-  if (L == 32) return launch_fwd_tc<32>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
-  if (L == 16) return launch_fwd_tc<16>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
-  RAMP_CHECK(false, "attn_forward_tc: L must be 64, 32 or 16");
+  if (L == 64) return launch_fwd_tc<64, 64>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
+  if (L == 32) return launch_fwd_tc<32, 32>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
+  if (L == 16) return launch_fwd_tc<16, 16>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
+  if (L == 8) return launch_fwd_tc<16, 8>(qkv_hi, qkv_lo, n_samples, out_hi, out_lo, s);
+  RAMP_CHECK(false, "attn_forward_tc: L must be 64, 32, 16 or 8");
 }
 int attn_backward_tc(const bf16* qkv_hi, const bf16* qkv_lo, const bf16* do_hi, const bf16* do_lo, int n_samples, int L,
                      bf16* dq_hi, bf16* dq_lo, cudaStream_t s) {
-  if (L == 64) return launch_bwd_tc<64>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
-  if (L == 32) return launch_bwd_tc<32>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
-  if (L == 16) return launch_bwd_tc<16>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
-  RAMP_CHECK(false, "attn_backward_tc: L must be 64, 32 or 16");
+  if (L == 64) return launch_bwd_tc<64, 64>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
+  if (L == 32) return launch_bwd_tc<32, 32>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
+  if (L == 16) return launch_bwd_tc<16, 16>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
+  if (L == 8) return launch_bwd_tc<16, 8>(qkv_hi, qkv_lo, do_hi, do_lo, n_samples, dq_hi, dq_lo, s);
+  RAMP_CHECK(false, "attn_backward_tc: L must be 64, 32, 16 or 8");
 }
 
 }  // namespace ramp

@@ -14,8 +14,7 @@
 //   MMAs of tile i+1; the TMA producer runs ahead across tile boundaries through the smem ring.
 // * Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + single-thread tcgen05.mma issuer,
 //   warps 2..9 = two epilogue groups (group g owns accumulator buffer g, i.e. every other tile, so a tile's
-//   epilogue may take twice the MMA time before it stalls the tensor pipe).  10 warps = at most 3 per SM
-//   sub-partition, whose 16 K-register slice caps the kernel at 168 registers per thread.  An epilogue thread owns one
+//   epilogue may take twice the MMA time before it stalls the tensor pipe).  An epilogue thread owns one
 //   accumulator row; global loads / stores are transposed through a per-warp XOR-swizzled smem staging tile
 //   so that every warp-wide access is row-contiguous.
 // * Fused epilogues (GemmEpi): GEGLU forward / backward, LayerNorm forward / backward (a thread owns the
@@ -166,7 +165,7 @@ struct EpiCtx {
   float* stg;              // this warp's staging tile (32 x 32 fp32)
   int lane;
   bool my_ok; size_t my_row; int my_sample;
-  unsigned ok8; uint32_t row8[8];
+  unsigned ok8; size_t row8[8];
 };
 
 // v[32] (this thread's row, columns col0..col0+31) -> base[row * ld + col0 ..] for every live row of the warp
@@ -179,7 +178,7 @@ __device__ __forceinline__ void chunk_store_f32(const EpiCtx& e, const float (&v
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const float4 t = s4[stg_idx(rsub + 4 * i, c4)];
-    if ((e.ok8 >> i) & 1u) *reinterpret_cast<float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4) = t;
+    if ((e.ok8 >> i) & 1u) *reinterpret_cast<float4*>(base + e.row8[i] * ld + col0 + 4 * c4) = t;
   }
   __syncwarp();
 }
@@ -200,7 +199,7 @@ __device__ __forceinline__ void chunk_store_split(const EpiCtx& e, const float (
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const uint4 t = s4[stg_idx(rsub + 4 * i, c4)];
-    if ((e.ok8 >> i) & 1u) *reinterpret_cast<uint4*>(plane + (size_t)e.row8[i] * ld + col0 + 8 * (c4 & 3)) = t;
+    if ((e.ok8 >> i) & 1u) *reinterpret_cast<uint4*>(plane + e.row8[i] * ld + col0 + 8 * (c4 & 3)) = t;
   }
   __syncwarp();
 }
@@ -211,33 +210,9 @@ __device__ __forceinline__ void chunk_load_f32(const EpiCtx& e, const float* __r
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-    if ((e.ok8 >> i) & 1u) t = *reinterpret_cast<const float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4);
+    if ((e.ok8 >> i) & 1u) t = *reinterpret_cast<const float4*>(base + e.row8[i] * ld + col0 + 4 * c4);
     s4[stg_idx(rsub + 4 * i, c4)] = t;
   }
-  __syncwarp();
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const float4 t = s4[stg_idx(e.lane, k)];
-    v[4 * k] = t.x; v[4 * k + 1] = t.y; v[4 * k + 2] = t.z; v[4 * k + 3] = t.w;
-  }
-  __syncwarp();
-}
-// the same load split in two so the global latency of chunk c+1 overlaps the math of chunk c:
-// chunk_fetch issues the 8 coalesced 16-byte loads into registers, chunk_deposit transposes them to the row owner
-struct Pref { float4 t[8]; };
-__device__ __forceinline__ void chunk_fetch(const EpiCtx& e, const float* __restrict__ base, int ld, int col0, Pref& f) {
-  const int c4 = e.lane & 7;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    f.t[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if ((e.ok8 >> i) & 1u) f.t[i] = *reinterpret_cast<const float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4);
-  }
-}
-__device__ __forceinline__ void chunk_deposit(const EpiCtx& e, const Pref& f, float (&v)[32]) {
-  const int rsub = e.lane >> 3, c4 = e.lane & 7;
-  float4* s4 = reinterpret_cast<float4*>(e.stg);
-#pragma unroll
-  for (int i = 0; i < 8; ++i) s4[stg_idx(rsub + 4 * i, c4)] = f.t[i];
   __syncwarp();
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
@@ -253,23 +228,16 @@ __device__ __forceinline__ void add_vec32(float (&v)[32], const float* __restric
     v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
   }
 }
-// acc + bias + per-scene bias (+ the rarely used second residual) for columns col .. col+31; the main residual is
-// streamed by the callers through chunk_fetch / chunk_deposit
+// acc + bias + per-scene bias + residual(s) for columns col .. col+31
 __device__ __forceinline__ void epi_affine(const GemmParams& p, const EpiCtx& e, float (&v)[32], int col) {
   if (p.bias) add_vec32(v, p.bias + col);
   if (p.bias_tab && e.my_ok) add_vec32(v, p.bias_tab + (size_t)p.row2scene[e.my_sample] * p.Nout + col);
+  if (p.residual) { float r[32]; chunk_load_f32(e, p.residual, p.ldR, col, r);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += r[i]; }
   if (p.residual2) { float r[32]; chunk_load_f32(e, p.residual2, p.ldR2, col, r);
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] += r[i]; }
-}
-// v += residual chunk held in `pr`; then start fetching the chunk at next_col (if any)
-__device__ __forceinline__ void add_residual(const GemmParams& p, const EpiCtx& e, Pref& pr, float (&v)[32], int next_col,
-                                             bool more) {
-  float r[32];
-  chunk_deposit(e, pr, r);
-  if (more) chunk_fetch(e, p.residual, p.ldR, next_col, pr);
-#pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] += r[i];
 }
 
 // L2 prefetch of everything this thread's row will read in the tile's epilogue; issued BEFORE waiting for the
@@ -296,13 +264,10 @@ __device__ __forceinline__ void epi_prefetch(const GemmParams& p, const EpiCtx& 
 
 // ---- one tile's epilogue, by mode.  acc = TMEM address of this warp's lane quarter, column 0 of the tile ----
 __device__ __forceinline__ void epi_plain(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
-  Pref pr;
-  if (p.residual) chunk_fetch(e, p.residual, p.ldR, colbase, pr);
   for (int c = 0; c < p.BN; c += 32) {
     float v[32];
     ld_acc(acc + c, v);
     epi_affine(p, e, v, colbase + c);
-    if (p.residual) add_residual(p, e, pr, v, colbase + c + 32, c + 32 < p.BN);
     if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, colbase + c);
     if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, colbase + c);
   }
@@ -376,36 +341,26 @@ __device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx&
 // GEGLU backward: acc = d(a * gelu(gate)) for natural columns colbase + c; u = (gelu(gate) | a gelu'(gate)) and du are
 // tile-interleaved
 __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
-  // one prefetch register set, alternating between the s = gelu(gate) and q = a gelu'(gate) halves of u
-  auto pcol = [&](int c) { const int j = colbase + c; return (j >> 7) * 256 + (j & 127); };
-  Pref pf;
-  chunk_fetch(e, p.u, 2048, pcol(0), pf);
   for (int c = 0; c < p.BN; c += 32) {
-    float d[32], w[32];
+    float d[32], a[32], g[32];
     ld_acc(acc + c, d);
-    const int pa = pcol(c), pg = pa + 128;
-    chunk_deposit(e, pf, w);
-    chunk_fetch(e, p.u, 2048, pg, pf);
+    const int j = colbase + c;
+    const int pa = (j >> 7) * 256 + (j & 127), pg = pa + 128;
+    chunk_load_f32(e, p.u, 2048, pa, a);
+    chunk_load_f32(e, p.u, 2048, pg, g);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) w[i] *= d[i];
-    chunk_store_split(e, w, p.out_hi, p.out_lo, p.ldS, pa);
-    chunk_deposit(e, pf, w);
-    if (c + 32 < p.BN) chunk_fetch(e, p.u, 2048, pcol(c + 32), pf);
-#pragma unroll
-    for (int i = 0; i < 32; ++i) w[i] *= d[i];
-    chunk_store_split(e, w, p.out_hi, p.out_lo, p.ldS, pg);
+    for (int i = 0; i < 32; ++i) { a[i] *= d[i]; g[i] *= d[i]; }    // u = (gelu(gate) | a * gelu'(gate))
+    chunk_store_split(e, a, p.out_hi, p.out_lo, p.ldS, pa);
+    chunk_store_split(e, g, p.out_hi, p.out_lo, p.ldS, pg);
   }
 }
 // LayerNorm forward over the 256 channels of the row this thread owns (eps 1e-5, layers_attention_mini.py:138-140)
 __device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc) {
   float shift = 0.f, s = 0.f, ss = 0.f;
-  Pref pr;
-  if (p.residual) chunk_fetch(e, p.residual, p.ldR, 0, pr);
   for (int c = 0; c < 256; c += 32) {
     float v[32];
     ld_acc(acc + c, v);
     epi_affine(p, e, v, c);
-    if (p.residual) add_residual(p, e, pr, v, c + 32, c + 32 < 256);
     if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, c);
     if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, c);
     st_acc(acc + c, v);
@@ -436,13 +391,10 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e,
   float mean = 0.f, rstd = 0.f;
   if (e.my_ok) { const float2 st = *reinterpret_cast<const float2*>(p.ln_stats + e.my_row * 2); mean = st.x; rstd = st.y; }
   float s1 = 0.f, s2 = 0.f;
-  Pref px;
-  chunk_fetch(e, p.ln_x, 256, 0, px);
   for (int c = 0; c < 256; c += 32) {
     float d[32], x[32];
     ld_acc(acc + c, d);
-    chunk_deposit(e, px, x);
-    chunk_fetch(e, p.ln_x, 256, c + 32 < 256 ? c + 32 : 0, px);      // the wrap-around fetch feeds pass 2
+    chunk_load_f32(e, p.ln_x, 256, c, x);
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
       const float4 g = *reinterpret_cast<const float4*>(p.ln_gamma + c + i);
@@ -454,20 +406,15 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e,
   }
   tmem_st_wait();
   s1 *= (1.f / 256.f); s2 *= (1.f / 256.f);
-  for (int c = 0; c < 256; c += 32) {        // one prefetch register set alternates between ln_x and the residual
+  for (int c = 0; c < 256; c += 32) {
     float d[32], x[32];
     ld_acc(acc + c, d);
-    chunk_deposit(e, px, x);
-    if (p.residual) chunk_fetch(e, p.residual, p.ldR, c, px);
-    else if (c + 32 < 256) chunk_fetch(e, p.ln_x, 256, c + 32, px);
+    chunk_load_f32(e, p.ln_x, 256, c, x);
 #pragma unroll
     for (int i = 0; i < 32; ++i) d[i] = rstd * (d[i] - s1 - (x[i] - mean) * rstd * s2);
-    if (p.residual) {
-      chunk_deposit(e, px, x);
-      if (c + 32 < 256) chunk_fetch(e, p.ln_x, 256, c + 32, px);
+    if (p.residual) { chunk_load_f32(e, p.residual, p.ldR, c, x);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) d[i] += x[i];
-    }
+      for (int i = 0; i < 32; ++i) d[i] += x[i]; }
     if (p.out_f32) chunk_store_f32(e, d, p.out_f32, p.ldO, c);
     if (p.out_hi) chunk_store_split(e, d, p.out_hi, p.out_lo, p.ldS, c);
   }
@@ -513,7 +460,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   uint32_t tmem_acc;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_acc) : "r"(tmem_slot));
-
 
   if (warp == 0) {
     // ---------------- TMA producer ----------------
@@ -578,7 +524,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
         umma_commit(tfull0 + 8 * buf);            // accumulator complete
       }
     }
-  } else if (warp >= 2) {
+  } else {
     // ---------------- epilogue: group (warp-2)/4 drains accumulator buffer `group`; TMEM lane quarter = warp % 4 ----
     const int q = warp & 3, group = (warp - 2) >> 2;
     EpiCtx e;
@@ -602,7 +548,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
           const int nl = rr / p.L_out, ll = rr - nl * p.L_out;
           const int smp = tile_m * p.nb + nl;
           if (nl < p.nb && smp < p.n_samples) e.ok8 |= 1u << i;
-          e.row8[i] = (uint32_t)((size_t)smp * p.o_L + (size_t)ll * p.o_stride + p.o_off);
+          e.row8[i] = (size_t)smp * p.o_L + (size_t)ll * p.o_stride + p.o_off;
         }
       }
       epi_prefetch(p, e, tile_n);

@@ -59,7 +59,7 @@ int UnetEngine::res_fwd(const ResW& w, const Act& x, int L, const OutSpec& o, Ac
   if (!dry_) {
     GnArgs g{}; g.x = sv.c1; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g1; g.beta = w.b1;
     g.eps = 1e-5f; g.mish = 1; g.cond = w.cond; g.out_hi = h1.hi; g.out_lo = h1.lo; g.ldS = co;
-    ProfScope ps(this, 1); TRY(gn_forward(g, s_));
+    ProfScope ps(this, 1); ps.tag("gn_fwd_C%d_L%d", g.C, g.L); TRY(gn_forward(g, s_));
   }
   sv.c2 = allocf(M * co);
   Act h1a; h1a.hi = h1.hi; h1a.lo = h1.lo; h1a.lds = co; h1a.C = co;
@@ -83,7 +83,7 @@ int UnetEngine::res_fwd(const ResW& w, const Act& x, int L, const OutSpec& o, Ac
     GnArgs g{}; g.x = sv.c2; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g2; g.beta = w.b2;
     g.eps = 1e-5f; g.mish = 1; g.add = addp; g.ldAdd = ldadd; g.out_f32 = const_cast<float*>(y.f); g.ldO = co;
     g.out_hi = oh; g.out_lo = ol; g.ldS = lds;
-    ProfScope ps(this, 1); TRY(gn_forward(g, s_));
+    ProfScope ps(this, 1); ps.tag("gn_fwd_C%d_L%d", g.C, g.L); TRY(gn_forward(g, s_));
   }
   return 0;
 }
@@ -96,7 +96,7 @@ int UnetEngine::res_bwd(const ResW& w, const ResSave& sv, const Act& dy, int L, 
   if (!dry_) {
     GnBwdArgs g{}; g.x = sv.c2; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g2; g.beta = w.b2;
     g.eps = 1e-5f; g.mish = 1; g.dy = dy.f; g.ldDy = dy.ldf; g.out_hi = t1.hi; g.out_lo = t1.lo; g.ldS = co;
-    ProfScope ps(this, 1); TRY(gn_backward(g, s_));
+    ProfScope ps(this, 1); ps.tag("gn_bwd_C%d_L%d", g.C, g.L); TRY(gn_backward(g, s_));
   }
   float* dh1 = allocf(M * co);
   Act t1a; t1a.hi = t1.hi; t1a.lo = t1.lo; t1a.lds = co;
@@ -106,7 +106,7 @@ int UnetEngine::res_bwd(const ResW& w, const ResSave& sv, const Act& dy, int L, 
   if (!dry_) {
     GnBwdArgs g{}; g.x = sv.c1; g.ldX = co; g.n_samples = npad_; g.L = L; g.C = co; g.gamma = w.g1; g.beta = w.b1;
     g.eps = 1e-5f; g.mish = 1; g.dy = dh1; g.ldDy = co; g.out_hi = t2.hi; g.out_lo = t2.lo; g.ldS = co;
-    ProfScope ps(this, 1); TRY(gn_backward(g, s_));
+    ProfScope ps(this, 1); ps.tag("gn_bwd_C%d_L%d", g.C, g.L); TRY(gn_backward(g, s_));
   }
   const float* res = dy.f; int ldr = dy.ldf;
   if (w.has_res) {
@@ -137,7 +137,7 @@ int UnetEngine::st_fwd(const STW& w, const Act& x, int L, const OutSpec& o, Act&
   if (!dry_) {
     GnArgs g{}; g.x = x.f; g.ldX = x.ldf; g.n_samples = npad_; g.L = L; g.C = C; g.gamma = w.gn_g; g.beta = w.gn_b;
     g.eps = 1e-6f; g.mish = 0; g.out_hi = xn.hi; g.out_lo = xn.lo; g.ldS = C;
-    ProfScope ps(this, 1); TRY(gn_forward(g, s_));
+    ProfScope ps(this, 1); ps.tag("gn_fwd_C%d_L%d", g.C, g.L); TRY(gn_forward(g, s_));
   }
   // proj_in -> z (fp32, residual stream) with LayerNorm1 of block 0 fused into the epilogue
   float* z = allocf(M * 256);
@@ -163,12 +163,12 @@ int UnetEngine::st_fwd(const STW& w, const Act& x, int L, const OutSpec& o, Act&
       ts.qkv_s = allocs(M * 768);
       TRY(gemm(aa, 256, t.qkv_f, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, nullptr, 0, ts.qkv_s.hi,
                ts.qkv_s.lo, 768, L, 1, 0));
-      if (!dry_) { ProfScope ps(this, 2); TRY(attn_forward_tc(ts.qkv_s.hi, ts.qkv_s.lo, npad_, L, ao.hi, ao.lo, s_)); }
+      if (!dry_) { ProfScope ps(this, 2); ps.tag("attn_fwd_tc_L%d", L); TRY(attn_forward_tc(ts.qkv_s.hi, ts.qkv_s.lo, npad_, L, ao.hi, ao.lo, s_)); }
     } else {
       ts.qkv = allocf(M * 768);
       TRY(gemm(aa, 256, t.qkv_f, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, ts.qkv, 768, nullptr,
                nullptr, 0, L, 1, 0));
-      if (!dry_) { ProfScope ps(this, 2); TRY(attn_forward(ts.qkv, npad_, L, ao.hi, ao.lo, s_)); }
+      if (!dry_) { ProfScope ps(this, 2); ps.tag("attn_fwd_f32_L%d", L); TRY(attn_forward(ts.qkv, npad_, L, ao.hi, ao.lo, s_)); }
     }
     // attn1.to_out (+ collapsed attn2 constant per scene) + residual -> z1, LayerNorm3 fused
     ts.z1 = allocf(M * 256);
@@ -255,13 +255,14 @@ int UnetEngine::st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act
                douts.lo, 256, L, 1, 0));
       if (!dry_) {
         ProfScope ps(this, 2);
+        ps.tag("attn_bwd_tc_L%d", L);
         TRY(attn_backward_tc(ts.qkv_s.hi, ts.qkv_s.lo, douts.hi, douts.lo, npad_, L, dqkv.hi, dqkv.lo, s_));
       }
     } else {
       float* dout = allocf(M * 256);
       TRY(gemm(d1a, 256, t.o_b, TAP_1X1, 1, L, L, 1, nullptr, nullptr, nullptr, 0, nullptr, 0, dout, 256, nullptr, nullptr,
                0, L, 1, 0));
-      if (!dry_) { ProfScope ps(this, 2); TRY(attn_backward(ts.qkv, dout, npad_, L, dqkv.hi, dqkv.lo, s_)); }
+      if (!dry_) { ProfScope ps(this, 2); ps.tag("attn_bwd_f32_L%d", L); TRY(attn_backward(ts.qkv, dout, npad_, L, dqkv.hi, dqkv.lo, s_)); }
     }
     // QKV^T with the LayerNorm1 backward in the epilogue: dz = dz1 + LN1'(zin, .)
     dz = allocf(M * 256);
@@ -285,7 +286,7 @@ int UnetEngine::st_bwd(const STW& w, const STSave& sv, const Act& dy, int L, Act
     GnBwdArgs g{}; g.x = sv.x; g.ldX = sv.ldx; g.n_samples = npad_; g.L = L; g.C = C; g.gamma = w.gn_g; g.beta = w.gn_b;
     g.eps = 1e-6f; g.mish = 0; g.dy = dxn; g.ldDy = C; g.add = dy.f; g.ldAdd = dy.ldf; g.out_f32 = dxf; g.ldO = C;
     g.out_hi = ds.hi; g.out_lo = ds.lo; g.ldS = C;
-    ProfScope ps(this, 1); TRY(gn_backward(g, s_));
+    ProfScope ps(this, 1); ps.tag("gn_bwd_C%d_L%d", g.C, g.L); TRY(gn_backward(g, s_));
   }
   return 0;
 }
@@ -373,7 +374,7 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
   if (!dry_) {
     GnArgs g{}; g.x = cfin; g.ldX = 32; g.n_samples = npad_; g.L = H; g.C = 32; g.gamma = final_g_; g.beta = final_b_;
     g.eps = 1e-5f; g.mish = 1; g.out_hi = hs.hi; g.out_lo = hs.lo; g.ldS = 32;
-    ProfScope ps(this, 1); TRY(gn_forward(g, s));
+    ProfScope ps(this, 1); ps.tag("gn_fwd_C%d_L%d", g.C, g.L); TRY(gn_forward(g, s));
   }
   float* fo = allocf(M * 16);
   Split fos = allocs(M * 16);
@@ -400,7 +401,7 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
   if (!dry_) {
     GnBwdArgs g{}; g.x = cfin; g.ldX = 32; g.n_samples = npad_; g.L = H; g.C = 32; g.gamma = final_g_; g.beta = final_b_;
     g.eps = 1e-5f; g.mish = 1; g.dy = dh; g.ldDy = 32; g.out_hi = dcs.hi; g.out_lo = dcs.lo; g.ldS = 32;
-    ProfScope ps(this, 1); TRY(gn_backward(g, s));
+    ProfScope ps(this, 1); ps.tag("gn_bwd_C%d_L%d", g.C, g.L); TRY(gn_backward(g, s));
   }
   Act dy; dy.C = 32;
   {
