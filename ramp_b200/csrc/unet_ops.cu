@@ -37,7 +37,7 @@ int prep_input(const float* x, int n_samples, int n_pad, int L, int D, int x_rep
 // ------------------------------------------------------------------------------------------------
 // GroupNorm(8 groups) over one sample's [L, C] tile (L*C <= 2048 floats): one 256-thread CTA per sample.
 // The tile is read ONCE with coalesced float4 loads and stays in registers (<= 2 float4 per thread); group
-// statistics are reduced by segmented warp shuffles (the lanes of one group are adjacent) + shared atomics.
+// statistics are reduced by segmented warp shuffles (the lanes of one group are adjacent) + a fixed-order pass.
 // Mish(x) = x * tanh(softplus(x)) is evaluated as x * n / (n + 2), n = e^x (e^x + 2)  (exact identity).
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float mish_fast(float x) {
@@ -68,14 +68,23 @@ __device__ __forceinline__ void gn_load(GnTile& t, const float* __restrict__ x, 
     t.v[i] = t.ok[i] ? *reinterpret_cast<const float4*>(x + (row0 + t.row[i]) * ldX + t.col[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
-// red[0..7] += per-group sums of (a[0], a[1]) (one value per owned float4); returns after a CTA barrier
-__device__ __forceinline__ void gn_group_reduce(const GnTile& t, const float (&a)[2], int cg, float* red) {
-  const int seg = cg >= 32 ? 8 : cg / 4;
+// red[g] = sum over group g of (a[0], a[1]) (one value per owned float4), in a FIXED order (no atomics, so the
+// sampler is bit-reproducible run to run): segment sums are parked in `part` (one slot per float4 of the tile), then
+// warp g adds the <= 64 segment leaders of group g lane-strided and finishes with a butterfly.  Ends with a CTA barrier.
+__device__ __forceinline__ void gn_group_reduce(const GnTile& t, const float (&a)[2], int L, int C, float* part, float* red) {
+  const int cg = C / 8, seg = cg >= 32 ? 8 : cg / 4, nl = cg >= 32 ? cg / 32 : 1;
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const float s = seg_sum(a[i], seg);
-    if (t.ok[i] && (threadIdx.x & (seg - 1)) == 0) atomicAdd(&red[t.col[i] / cg], s);
+  for (int i = 0; i < 2; ++i) part[threadIdx.x + i * 256] = seg_sum(a[i], seg);
+  __syncthreads();
+  const int g = threadIdx.x >> 5, lane = threadIdx.x & 31, n = L * nl;
+  float s = 0.f;
+  for (int k = lane; k < n; k += 32) {
+    const int r = k / nl, j = k - r * nl;
+    s += part[(r * C + g * cg) / 4 + j * seg];
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) red[g] = s;
   __syncthreads();
 }
 __device__ __forceinline__ void gn_store(float4 y, size_t row, int c, float* out_f32, int ldO, bf16* hi, bf16* lo, int ldS) {
@@ -89,15 +98,13 @@ __device__ __forceinline__ void gn_store(float4 y, size_t row, int c, float* out
   }
 }
 // mean / rstd of every group into stat[0..7] / stat[8..15]
-__device__ __forceinline__ void gn_stats(const GnTile& t, int L, int C, float eps, float* red, float* stat) {
+__device__ __forceinline__ void gn_stats(const GnTile& t, int L, int C, float eps, float* part, float* red, float* stat) {
   const int cg = C / 8;
   const float inv_m = 1.f / (float)(L * cg);
-  if (threadIdx.x < 16) red[threadIdx.x] = 0.f;
-  __syncthreads();
   float a[2];
 #pragma unroll
   for (int i = 0; i < 2; ++i) a[i] = (t.v[i].x + t.v[i].y) + (t.v[i].z + t.v[i].w);
-  gn_group_reduce(t, a, cg, red);
+  gn_group_reduce(t, a, L, C, part, red);
   if (threadIdx.x < 8) stat[threadIdx.x] = red[threadIdx.x] * inv_m;
   __syncthreads();
 #pragma unroll
@@ -106,18 +113,18 @@ __device__ __forceinline__ void gn_stats(const GnTile& t, int L, int C, float ep
     const float dx = t.v[i].x - m, dy = t.v[i].y - m, dz = t.v[i].z - m, dw = t.v[i].w - m;
     a[i] = t.ok[i] ? (dx * dx + dy * dy) + (dz * dz + dw * dw) : 0.f;
   }
-  gn_group_reduce(t, a, cg, red + 8);
+  gn_group_reduce(t, a, L, C, part, red + 8);
   if (threadIdx.x < 8) stat[8 + threadIdx.x] = rsqrtf(red[8 + threadIdx.x] * inv_m + eps);
   __syncthreads();
 }
 
 __global__ void __launch_bounds__(256) gn_forward_kernel(GnArgs a) {
-  __shared__ float red[16], stat[16];
+  __shared__ float red[16], stat[16], part[512];
   const size_t row0 = (size_t)blockIdx.x * a.L;
   const int cg = a.C / 8;
   GnTile t;
   gn_load(t, a.x, a.ldX, row0, a.L, a.C);
-  gn_stats(t, a.L, a.C, a.eps, red, stat);
+  gn_stats(t, a.L, a.C, a.eps, part, red, stat);
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     if (!t.ok[i]) continue;
@@ -151,15 +158,13 @@ int gn_forward(const GnArgs& a, cudaStream_t s) {
 }
 
 __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
-  __shared__ float red[16], stat[16], red2[16];
+  __shared__ float red[16], stat[16], red2[16], part[512];
   const size_t row0 = (size_t)blockIdx.x * a.L;
   const int cg = a.C / 8;
   const float inv_m = 1.f / (float)(a.L * cg);
   GnTile t;
   gn_load(t, a.x, a.ldX, row0, a.L, a.C);
-  gn_stats(t, a.L, a.C, a.eps, red, stat);
-  if (threadIdx.x < 16) red2[threadIdx.x] = 0.f;
-  __syncthreads();
+  gn_stats(t, a.L, a.C, a.eps, part, red, stat);
   float xh[2][4], dyh[2][4], p1[2], p2[2];
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
@@ -181,15 +186,8 @@ __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
       p2[i] += dyh[i][j] * xh[i][j];
     }
   }
-  {
-    const int seg = cg >= 32 ? 8 : cg / 4;
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const float s1 = seg_sum(p1[i], seg), s2 = seg_sum(p2[i], seg);
-      if (t.ok[i] && (threadIdx.x & (seg - 1)) == 0) { atomicAdd(&red2[t.col[i] / cg], s1); atomicAdd(&red2[8 + t.col[i] / cg], s2); }
-    }
-    __syncthreads();
-  }
+  gn_group_reduce(t, p1, a.L, a.C, part, red2);
+  gn_group_reduce(t, p2, a.L, a.C, part, red2 + 8);
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     if (!t.ok[i]) continue;

@@ -36,3 +36,19 @@ def test_energy_grad_matches_oracle(cuda, dim3, H, N):
     print("f err %.3e (|f| %.3f)  eps err %.3e (|eps| %.3f)" % (ferr, f_ref.abs().max(), eerr, e_ref.abs().max()))
     assert ferr < 2e-4 * max(1.0, f_ref.abs().max().item())
     assert eerr < 2e-4 * max(1.0, e_ref.abs().max().item())
+
+
+@pytest.mark.parametrize("dim3", [False, True])
+def test_energy_grad_is_bit_reproducible(cuda, dim3):
+    """Every reduction of the engine runs in a fixed order (no float atomics): the same inputs give the same bits."""
+    net, _, D = _setup(cuda, dim3)
+    g = torch.Generator("cpu").manual_seed(5)
+    x = torch.randn(33, 64, D, generator=g).to(cuda)
+    lat = (torch.randn(3, net.context_dim, generator=g) * 0.5).to(cuda)
+    r2s = (torch.arange(33) % 3).to(torch.int32).to(cuda)
+    net.prepare(horizon=64, max_rows=64, max_scenes=4)
+    net.set_scene_latents(lat)
+    first = net.energy_grad_rows(x, 7, r2s).clone()
+    for _ in range(3):
+        again = net.energy_grad_rows(x, 7, r2s)
+        assert torch.equal(first, again)
