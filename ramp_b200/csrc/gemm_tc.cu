@@ -13,14 +13,18 @@
 //   accumulator is double buffered in TMEM (2 x BN columns), so the epilogue of tile i overlaps the
 //   MMAs of tile i+1; the TMA producer runs ahead across tile boundaries through the smem ring.
 // * Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + single-thread tcgen05.mma issuer,
-//   warps 2..9 = two epilogue groups (group g owns accumulator buffer g, i.e. every other tile, so a tile's
-//   epilogue may take twice the MMA time before it stalls the tensor pipe).  An epilogue thread owns one
-//   accumulator row; global loads / stores are transposed through a per-warp XOR-swizzled smem staging tile
-//   so that every warp-wide access is row-contiguous.
-// * Fused epilogues (GemmEpi): GEGLU forward / backward, LayerNorm forward / backward (a thread owns the
-//   full 256-channel row when Nout == BN == 256; intermediate values are parked back in TMEM with
-//   tcgen05.st between the statistics pass and the normalisation pass).
+//   warps 2..9 = two epilogue groups of four (TMEM lane quarter = warp % 4).  For BN >= 64 both groups drain
+//   EVERY tile, each taking half of its columns ("cooperative": the tile's epilogue takes half as long and the
+//   other accumulator buffer is being filled meanwhile, so neither the tensor pipe nor the epilogue warps wait on
+//   each other as long as epilogue/2 >= MMA time or vice versa); for narrower tiles group g owns every other tile.
+//   An epilogue thread owns one accumulator row; global loads / stores are transposed through a per-warp
+//   XOR-swizzled smem staging tile so that every warp-wide access is row-contiguous.
+// * Fused epilogues (GemmEpi): GEGLU forward / backward, LayerNorm forward / backward (Nout == BN == 256: the two
+//   threads that own the halves of a row exchange partial statistics through shared memory and a 64-thread named
+//   barrier; intermediate values are parked back in TMEM with tcgen05.st between the statistics pass and the
+//   normalisation pass).
 #include "common.cuh"
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -33,6 +37,7 @@ static constexpr int BK = 64;                 // bf16 elements = 128 B = one SWI
 static constexpr int A_TILE_BYTES = BM * BK * 2;
 static constexpr int EPI_WARPS = 8;            // two groups of four: group g drains accumulator buffer g
 static constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;
+static constexpr int XCH_BYTES = 128 * 8;                 // static shared: LayerNorm partial-statistics exchange slots
 static constexpr int STG_BYTES = EPI_WARPS * 32 * 32 * 4;   // per warp a 32 x 32 fp32 tile, XOR-swizzled 16-byte groups
 
 struct GemmParams {
@@ -46,7 +51,7 @@ struct GemmParams {
   float* out_f32; int ldO;
   bf16* out_hi; bf16* out_lo; int ldS;
   int o_L, o_stride, o_off;
-  int epi;
+  int epi, coop, prefetch;                              // coop: both epilogue groups split the columns of every tile
   const float* ln_gamma; const float* ln_beta; float* ln_stats; const float* ln_x; const float* u;
   bf16* out2_hi; bf16* out2_lo; int ldS2;
 };
@@ -166,7 +171,10 @@ struct EpiCtx {
   int lane;
   bool my_ok; size_t my_row; int my_sample;
   unsigned ok8; size_t row8[8];
+  float2* xch; int bar_id;                                   // LayerNorm statistics exchange slot shared with the other half's thread
 };
+// the two warps (same lane quarter, one per group) that share a tile's rows meet here
+__device__ __forceinline__ void pair_sync(int bar_id) { asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory"); }
 
 // v[32] (this thread's row, columns col0..col0+31) -> base[row * ld + col0 ..] for every live row of the warp
 __device__ __forceinline__ void chunk_store_f32(const EpiCtx& e, const float (&v)[32], float* base, int ld, int col0) {
@@ -246,25 +254,25 @@ __device__ __forceinline__ void prefetch_row(const float* base, size_t row, int 
   const float* p0 = base + row * ld + col0;
   for (int c = 0; c < ncols; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(p0 + c));
 }
-__device__ __forceinline__ void epi_prefetch(const GemmParams& p, const EpiCtx& e, int tile_n) {
-  if (!e.my_ok || p.BN == 16) return;
+// (row = the thread's output row in that tile; [c0, c1) = the tile columns this thread's group will drain)
+__device__ __forceinline__ void epi_prefetch(const GemmParams& p, bool ok, size_t row, int tile_n, int c0, int c1) {
+  if (!ok || p.BN == 16 || !p.prefetch) return;
   const int colbase = tile_n * p.BN;
   if (p.epi == EPI_GEGLU_BWD) {
-    for (int c = 0; c < p.BN; c += 128) {
-      const int j = colbase + c;
-      prefetch_row(p.u, e.my_row, 2048, (j >> 7) * 256, 256);
-    }
+    const int j = colbase + c0, pa = (j >> 7) * 256 + (j & 127);
+    prefetch_row(p.u, row, 2048, pa, c1 - c0);
+    prefetch_row(p.u, row, 2048, pa + 128, c1 - c0);
     return;
   }
-  if (p.epi == EPI_LN_BWD) prefetch_row(p.ln_x, e.my_row, 256, 0, 256);
+  if (p.epi == EPI_LN_BWD) prefetch_row(p.ln_x, row, 256, c0, c1 - c0);
   if (p.epi == EPI_GEGLU_FWD) return;
-  if (p.residual) prefetch_row(p.residual, e.my_row, p.ldR, colbase, p.BN);
-  if (p.residual2) prefetch_row(p.residual2, e.my_row, p.ldR2, colbase, p.BN);
+  if (p.residual) prefetch_row(p.residual, row, p.ldR, colbase + c0, c1 - c0);
+  if (p.residual2) prefetch_row(p.residual2, row, p.ldR2, colbase + c0, c1 - c0);
 }
 
 // ---- one tile's epilogue, by mode.  acc = TMEM address of this warp's lane quarter, column 0 of the tile ----
-__device__ __forceinline__ void epi_plain(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
-  for (int c = 0; c < p.BN; c += 32) {
+__device__ __forceinline__ void epi_plain(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase, int c0, int c1) {
+  for (int c = c0; c < c1; c += 32) {
     float v[32];
     ld_acc(acc + c, v);
     epi_affine(p, e, v, colbase + c);
@@ -314,9 +322,9 @@ __device__ __forceinline__ void epi_plain16(const GemmParams& p, const EpiCtx& e
   }
 }
 // GEGLU forward (layers_attention_mini.py:38-45): tile columns [0,128) = a, [128,256) = gate
-__device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int tile_n) {
+__device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int tile_n, int c0, int c1) {
   const int colbase = tile_n * 256;
-  for (int c = 0; c < 128; c += 32) {
+  for (int c = c0 >> 1; c < (c1 >> 1); c += 32) {
     float a[32], g[32], s_[32];
     ld_acc(acc + c, a);
     ld_acc(acc + 128 + c, g);
@@ -340,8 +348,8 @@ __device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx&
 }
 // GEGLU backward: acc = d(a * gelu(gate)) for natural columns colbase + c; u = (gelu(gate) | a gelu'(gate)) and du are
 // tile-interleaved
-__device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
-  for (int c = 0; c < p.BN; c += 32) {
+__device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase, int c0, int c1) {
+  for (int c = c0; c < c1; c += 32) {
     float d[32], a[32], g[32];
     ld_acc(acc + c, d);
     const int j = colbase + c;
@@ -355,25 +363,44 @@ __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx&
   }
 }
 // LayerNorm forward over the 256 channels of the row this thread owns (eps 1e-5, layers_attention_mini.py:138-140)
-__device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc) {
+// This thread drains columns [c0, c1) of its row; with c1 - c0 == 128 the thread of the other half shares the statistics.
+__device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int c0, int c1) {
   float shift = 0.f, s = 0.f, ss = 0.f;
-  for (int c = 0; c < 256; c += 32) {
+  for (int c = c0; c < c1; c += 32) {
     float v[32];
     ld_acc(acc + c, v);
     epi_affine(p, e, v, c);
     if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, c);
     if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, c);
     st_acc(acc + c, v);
-    if (c == 0) shift = v[0];
+    if (c == c0) shift = v[0];
 #pragma unroll
     for (int i = 0; i < 32; ++i) { const float d = v[i] - shift; s += d; ss = fmaf(d, d, ss); }
   }
   tmem_st_wait();
-  const float m0 = s * (1.f / 256.f);
-  const float mean = shift + m0;
-  const float rstd = rsqrtf(fmaxf(ss * (1.f / 256.f) - m0 * m0, 0.f) + 1e-5f);
-  if (p.ln_stats && e.my_ok) *reinterpret_cast<float2*>(p.ln_stats + e.my_row * 2) = make_float2(mean, rstd);
-  for (int c = 0; c < 256; c += 32) {
+  float mean, rstd;
+  if (c1 - c0 == 256) {
+    const float m0 = s * (1.f / 256.f);
+    mean = shift + m0;
+    rstd = rsqrtf(fmaxf(ss * (1.f / 256.f) - m0 * m0, 0.f) + 1e-5f);
+  } else {
+    // upper half sends (mean, M2) of its 128 values; lower half merges (Chan's update) and returns (mean, rstd)
+    const float ml = s * (1.f / 128.f);
+    const float2 mine = make_float2(shift + ml, fmaxf(ss - s * ml, 0.f));
+    if (c0 != 0) *e.xch = mine;
+    pair_sync(e.bar_id);
+    if (c0 == 0) {
+      const float2 peer = *e.xch;
+      const float dm = peer.x - mine.x;
+      mean = mine.x + 0.5f * dm;
+      rstd = rsqrtf((mine.y + peer.y + dm * dm * 64.f) * (1.f / 256.f) + 1e-5f);
+      *e.xch = make_float2(mean, rstd);
+    }
+    pair_sync(e.bar_id);
+    if (c0 != 0) { const float2 t = *e.xch; mean = t.x; rstd = t.y; }
+  }
+  if (p.ln_stats && e.my_ok && c0 == 0) *reinterpret_cast<float2*>(p.ln_stats + e.my_row * 2) = make_float2(mean, rstd);
+  for (int c = c0; c < c1; c += 32) {
     float v[32];
     ld_acc(acc + c, v);
 #pragma unroll
@@ -387,11 +414,11 @@ __device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx& e,
   }
 }
 // out = residual + LayerNorm_backward(ln_x, acc): dx = rstd * (dyh - mean(dyh) - xh * mean(dyh * xh)), dyh = acc * gamma
-__device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc) {
+__device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int c0, int c1) {
   float mean = 0.f, rstd = 0.f;
   if (e.my_ok) { const float2 st = *reinterpret_cast<const float2*>(p.ln_stats + e.my_row * 2); mean = st.x; rstd = st.y; }
   float s1 = 0.f, s2 = 0.f;
-  for (int c = 0; c < 256; c += 32) {
+  for (int c = c0; c < c1; c += 32) {
     float d[32], x[32];
     ld_acc(acc + c, d);
     chunk_load_f32(e, p.ln_x, 256, c, x);
@@ -405,8 +432,15 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e,
     st_acc(acc + c, d);
   }
   tmem_st_wait();
+  if (c1 - c0 != 256) {
+    if (c0 != 0) *e.xch = make_float2(s1, s2);
+    pair_sync(e.bar_id);
+    if (c0 == 0) { const float2 peer = *e.xch; s1 += peer.x; s2 += peer.y; *e.xch = make_float2(s1, s2); }
+    pair_sync(e.bar_id);
+    if (c0 != 0) { const float2 t = *e.xch; s1 = t.x; s2 = t.y; }
+  }
   s1 *= (1.f / 256.f); s2 *= (1.f / 256.f);
-  for (int c = 0; c < 256; c += 32) {
+  for (int c = c0; c < c1; c += 32) {
     float d[32], x[32];
     ld_acc(acc + c, d);
     chunk_load_f32(e, p.ln_x, 256, c, x);
@@ -445,7 +479,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(tfull0 + 8 * b, 1); mbar_init(tempty0 + 8 * b, 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull0 + 8 * b, 1); mbar_init(tempty0 + 8 * b, p.coop ? 8 : 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAhi) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBhi) : "memory");
@@ -525,42 +559,58 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
       }
     }
   } else {
-    // ---------------- epilogue: group (warp-2)/4 drains accumulator buffer `group`; TMEM lane quarter = warp % 4 ----
+    // ---------------- epilogue: TMEM lane quarter = warp % 4, group = (warp - 2) / 4 ----------------
     const int q = warp & 3, group = (warp - 2) >> 2;
+    __shared__ float2 xch[128];                             // XCH_BYTES static: one slot per tile row
     EpiCtx e;
     e.lane = lane;
     e.stg = reinterpret_cast<float*>(smem_gen + p.stages * stage_bytes) + (warp - 2) * 32 * 32;
-    int lt = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-      if ((lt & 1) != group) continue;
+    e.bar_id = 1 + q;
+    e.xch = &xch[q * 32 + lane];
+    // columns of a tile this group drains
+    const int c0 = p.coop ? group * (p.BN >> 1) : 0, c1 = p.coop ? c0 + (p.BN >> 1) : p.BN;
+    const int r = q * 32 + lane;
+    const int n_local = r / p.L_out, l = r - n_local * p.L_out;
+    auto my_row_of = [&](int tile_m, bool& ok) -> size_t {
+      const int smp = tile_m * p.nb + n_local;
+      ok = n_local < p.nb && smp < p.n_samples;
+      return (size_t)smp * p.o_L + (size_t)l * p.o_stride + p.o_off;
+    };
+    const int step = p.coop ? (int)gridDim.x : 2 * (int)gridDim.x;
+    int lt = p.coop ? 0 : group;
+    int tile = blockIdx.x + lt * (int)gridDim.x;
+    if (tile < total_tiles) {       // inputs of the first tile; later tiles are prefetched one tile ahead
+      bool ok; const size_t row = my_row_of(tile / p.n_tiles, ok);
+      epi_prefetch(p, ok, row, tile % p.n_tiles, c0, c1);
+    }
+    for (; tile < total_tiles; tile += step, lt += p.coop ? 1 : 2) {
       const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
-      const int buf = group;
-      {
-        const int r = q * 32 + lane;
-        const int n_local = r / p.L_out, l = r - n_local * p.L_out;
-        e.my_sample = tile_m * p.nb + n_local;
-        e.my_ok = n_local < p.nb && e.my_sample < p.n_samples;
-        e.my_row = (size_t)e.my_sample * p.o_L + (size_t)l * p.o_stride + p.o_off;
-        e.ok8 = 0;
+      const int buf = lt & 1;
+      e.my_sample = tile_m * p.nb + n_local;
+      e.my_row = my_row_of(tile_m, e.my_ok);
+      e.ok8 = 0;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int rr = q * 32 + (lane >> 3) + 4 * i;
-          const int nl = rr / p.L_out, ll = rr - nl * p.L_out;
-          const int smp = tile_m * p.nb + nl;
-          if (nl < p.nb && smp < p.n_samples) e.ok8 |= 1u << i;
-          e.row8[i] = (size_t)smp * p.o_L + (size_t)ll * p.o_stride + p.o_off;
-        }
+      for (int i = 0; i < 8; ++i) {
+        const int rr = q * 32 + (lane >> 3) + 4 * i;
+        const int nl = rr / p.L_out, ll = rr - nl * p.L_out;
+        const int smp = tile_m * p.nb + nl;
+        if (nl < p.nb && smp < p.n_samples) e.ok8 |= 1u << i;
+        e.row8[i] = (size_t)smp * p.o_L + (size_t)ll * p.o_stride + p.o_off;
       }
-      epi_prefetch(p, e, tile_n);
+      if (tile + step < total_tiles) {
+        const int nt = tile + step;
+        bool ok; const size_t row = my_row_of(nt / p.n_tiles, ok);
+        epi_prefetch(p, ok, row, nt % p.n_tiles, c0, c1);
+      }
       mbar_wait(tfull0 + 8 * buf, (lt >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t acc = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);
       if (p.BN == 16) epi_plain16(p, e, acc, tile_n * 16);
-      else if (p.epi == EPI_PLAIN) epi_plain(p, e, acc, tile_n * p.BN);
-      else if (p.epi == EPI_GEGLU_FWD) epi_geglu_fwd(p, e, acc, tile_n);
-      else if (p.epi == EPI_GEGLU_BWD) epi_geglu_bwd(p, e, acc, tile_n * p.BN);
-      else if (p.epi == EPI_LN_FWD) epi_ln_fwd(p, e, acc);
-      else epi_ln_bwd(p, e, acc);
+      else if (p.epi == EPI_PLAIN) epi_plain(p, e, acc, tile_n * p.BN, c0, c1);
+      else if (p.epi == EPI_GEGLU_FWD) epi_geglu_fwd(p, e, acc, tile_n, c0, c1);
+      else if (p.epi == EPI_GEGLU_BWD) epi_geglu_bwd(p, e, acc, tile_n * p.BN, c0, c1);
+      else if (p.epi == EPI_LN_FWD) epi_ln_fwd(p, e, acc, c0, c1);
+      else epi_ln_bwd(p, e, acc, c0, c1);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
@@ -583,6 +633,9 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 static EncodeTiledFn g_encode = nullptr;
 static int g_max_smem = 0;
 static int g_num_sms = 148;
+// tuning knobs (environment, read once): RAMP_GEMM_PREFETCH=<bit mask over GemmEpi> enables the epilogue L2 prefetch per mode, RAMP_GEMM_COOP=0 the
+// cooperative epilogue, RAMP_GEMM_L2PROMO=128|256 picks the tensor-map L2 promotion
+static int g_prefetch = 0, g_coop = 1, g_l2promo = 256;
 
 int gemm_init() {
   if (g_encode) return 0;
@@ -594,7 +647,10 @@ int gemm_init() {
   RAMP_CUDA_OK(cudaGetDevice(&dev));
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, g_max_smem));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, g_max_smem - XCH_BYTES));
+  if (const char* v = getenv("RAMP_GEMM_PREFETCH")) g_prefetch = atoi(v);
+  if (const char* v = getenv("RAMP_GEMM_COOP")) g_coop = atoi(v);
+  if (const char* v = getenv("RAMP_GEMM_L2PROMO")) g_l2promo = atoi(v);
   g_encode = (EncodeTiledFn)fn;
   return 0;
 }
@@ -628,7 +684,8 @@ static int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t*
   for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; }
   for (int i = 0; i < rank - 1; ++i) gs[i] = strides_bytes[i];
   CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gd, gs, bx, es,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        g_l2promo == 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[256];
@@ -687,10 +744,12 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
     p.BN = 256;
   }
   p.n_tiles = d.Nout / p.BN;
+  p.coop = (p.BN >= 64 && g_coop) ? 1 : 0;
+  p.prefetch = (g_prefetch >> d.epi) & 1;
   p.nplanes = d.precision == 3 ? 2 : 1;
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + p.BN * BK * 2);
   const int fixed = 1024 + STG_BYTES + 256;
-  int stages = (g_max_smem - fixed) / stage_bytes;
+  int stages = (g_max_smem - XCH_BYTES - fixed) / stage_bytes;
   if (stages > 6) stages = 6;
   const long total_iters = (long)p.ntaps * p.kblocks * ((long)p.m_tiles * p.n_tiles + g_num_sms - 1) / g_num_sms;
   if (stages > total_iters) stages = (int)total_iters;
