@@ -51,7 +51,7 @@ struct GemmParams {
   float* out_f32; int ldO;
   bf16* out_hi; bf16* out_lo; int ldS;
   int o_L, o_stride, o_off;
-  int epi, coop, prefetch;                              // coop: both epilogue groups split the columns of every tile
+  int epi, coop;                              // coop: both epilogue groups split the columns of every tile
   const float* ln_gamma; const float* ln_beta; float* ln_stats; const float* ln_x; const float* u;
   bf16* out2_hi; bf16* out2_lo; int ldS2;
 };
@@ -170,7 +170,7 @@ struct EpiCtx {
   float* stg;              // this warp's staging tile (32 x 32 fp32)
   int lane;
   bool my_ok; size_t my_row; int my_sample;
-  unsigned ok8; size_t row8[8];
+  unsigned ok8; uint32_t row8[8];
   float2* xch; int bar_id;                                   // LayerNorm statistics exchange slot shared with the other half's thread
 };
 // the two warps (same lane quarter, one per group) that share a tile's rows meet here
@@ -186,7 +186,7 @@ __device__ __forceinline__ void chunk_store_f32(const EpiCtx& e, const float (&v
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const float4 t = s4[stg_idx(rsub + 4 * i, c4)];
-    if ((e.ok8 >> i) & 1u) *reinterpret_cast<float4*>(base + e.row8[i] * ld + col0 + 4 * c4) = t;
+    if ((e.ok8 >> i) & 1u) *reinterpret_cast<float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4) = t;
   }
   __syncwarp();
 }
@@ -207,7 +207,7 @@ __device__ __forceinline__ void chunk_store_split(const EpiCtx& e, const float (
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const uint4 t = s4[stg_idx(rsub + 4 * i, c4)];
-    if ((e.ok8 >> i) & 1u) *reinterpret_cast<uint4*>(plane + e.row8[i] * ld + col0 + 8 * (c4 & 3)) = t;
+    if ((e.ok8 >> i) & 1u) *reinterpret_cast<uint4*>(plane + (size_t)e.row8[i] * ld + col0 + 8 * (c4 & 3)) = t;
   }
   __syncwarp();
 }
@@ -218,7 +218,7 @@ __device__ __forceinline__ void chunk_load_f32(const EpiCtx& e, const float* __r
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-    if ((e.ok8 >> i) & 1u) t = *reinterpret_cast<const float4*>(base + e.row8[i] * ld + col0 + 4 * c4);
+    if ((e.ok8 >> i) & 1u) t = *reinterpret_cast<const float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4);
     s4[stg_idx(rsub + 4 * i, c4)] = t;
   }
   __syncwarp();
@@ -226,6 +226,30 @@ __device__ __forceinline__ void chunk_load_f32(const EpiCtx& e, const float* __r
   for (int k = 0; k < 8; ++k) {
     const float4 t = s4[stg_idx(e.lane, k)];
     v[4 * k] = t.x; v[4 * k + 1] = t.y; v[4 * k + 2] = t.z; v[4 * k + 3] = t.w;
+  }
+  __syncwarp();
+}
+// two-phase form: `chunk_ld_issue` puts the 8 row-contiguous 16-byte loads of the chunk in flight (registers),
+// `chunk_ld_finish` transposes them through the staging tile into the thread's own row.  Issuing the next chunk's loads
+// before the current chunk's arithmetic and stores keeps ~8 KB per warp in flight, which is what hides HBM latency here.
+__device__ __forceinline__ void chunk_ld_issue(const EpiCtx& e, const float* __restrict__ base, int ld, int col0, float4 (&t)[8]) {
+  const int c4 = e.lane & 7;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    t[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if ((e.ok8 >> i) & 1u) t[i] = __ldg(reinterpret_cast<const float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4));
+  }
+}
+__device__ __forceinline__ void chunk_ld_finish(const EpiCtx& e, const float4 (&t)[8], float (&v)[32]) {
+  const int rsub = e.lane >> 3, c4 = e.lane & 7;
+  float4* s4 = reinterpret_cast<float4*>(e.stg);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s4[stg_idx(rsub + 4 * i, c4)] = t[i];
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const float4 x = s4[stg_idx(e.lane, k)];
+    v[4 * k] = x.x; v[4 * k + 1] = x.y; v[4 * k + 2] = x.z; v[4 * k + 3] = x.w;
   }
   __syncwarp();
 }
@@ -248,34 +272,32 @@ __device__ __forceinline__ void epi_affine(const GemmParams& p, const EpiCtx& e,
     for (int i = 0; i < 32; ++i) v[i] += r[i]; }
 }
 
-// L2 prefetch of everything this thread's row will read in the tile's epilogue; issued BEFORE waiting for the
-// accumulator, so the HBM latency of the epilogue inputs hides behind the tile's MMAs.
-__device__ __forceinline__ void prefetch_row(const float* base, size_t row, int ld, int col0, int ncols) {
-  const float* p0 = base + row * ld + col0;
-  for (int c = 0; c < ncols; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(p0 + c));
-}
-// (row = the thread's output row in that tile; [c0, c1) = the tile columns this thread's group will drain)
-__device__ __forceinline__ void epi_prefetch(const GemmParams& p, bool ok, size_t row, int tile_n, int c0, int c1) {
-  if (!ok || p.BN == 16 || !p.prefetch) return;
-  const int colbase = tile_n * p.BN;
-  if (p.epi == EPI_GEGLU_BWD) {
-    const int j = colbase + c0, pa = (j >> 7) * 256 + (j & 127);
-    prefetch_row(p.u, row, 2048, pa, c1 - c0);
-    prefetch_row(p.u, row, 2048, pa + 128, c1 - c0);
-    return;
+// same with the residual chunk carried in flight: `t` holds the loads of columns `col` on entry and of `next_col` on exit
+__device__ __forceinline__ void epi_affine_pf(const GemmParams& p, const EpiCtx& e, float (&v)[32], int col, float4 (&t)[8],
+                                              int next_col, bool has_next) {
+  if (p.bias) add_vec32(v, p.bias + col);
+  if (p.bias_tab && e.my_ok) add_vec32(v, p.bias_tab + (size_t)p.row2scene[e.my_sample] * p.Nout + col);
+  if (p.residual) {
+    float r[32];
+    chunk_ld_finish(e, t, r);
+    if (has_next) chunk_ld_issue(e, p.residual, p.ldR, next_col, t);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += r[i];
   }
-  if (p.epi == EPI_LN_BWD) prefetch_row(p.ln_x, row, 256, c0, c1 - c0);
-  if (p.epi == EPI_GEGLU_FWD) return;
-  if (p.residual) prefetch_row(p.residual, row, p.ldR, colbase + c0, c1 - c0);
-  if (p.residual2) prefetch_row(p.residual2, row, p.ldR2, colbase + c0, c1 - c0);
+  if (p.residual2) { float r[32]; chunk_load_f32(e, p.residual2, p.ldR2, col, r);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += r[i]; }
 }
 
 // ---- one tile's epilogue, by mode.  acc = TMEM address of this warp's lane quarter, column 0 of the tile ----
 __device__ __forceinline__ void epi_plain(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase, int c0, int c1) {
+  float4 t[8];
+  if (p.residual) chunk_ld_issue(e, p.residual, p.ldR, colbase + c0, t);
+#pragma unroll 1
   for (int c = c0; c < c1; c += 32) {
     float v[32];
     ld_acc(acc + c, v);
-    epi_affine(p, e, v, colbase + c);
+    epi_affine_pf(p, e, v, colbase + c, t, colbase + c + 32, c + 32 < c1);
     if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, colbase + c);
     if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, colbase + c);
   }
@@ -349,27 +371,37 @@ __device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx&
 // GEGLU backward: acc = d(a * gelu(gate)) for natural columns colbase + c; u = (gelu(gate) | a gelu'(gate)) and du are
 // tile-interleaved
 __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase, int c0, int c1) {
+  auto u_col = [&](int c) { const int j = colbase + c; return (j >> 7) * 256 + (j & 127); };
+  float4 t[8];                                   // the loads in flight: gelu(gate) of chunk c, then a gelu'(gate), then chunk c + 32 ...
+  chunk_ld_issue(e, p.u, 2048, u_col(c0), t);
+#pragma unroll 1
   for (int c = c0; c < c1; c += 32) {
-    float d[32], a[32], g[32];
+    float d[32], x[32];
+    const int pa = u_col(c), pg = pa + 128;
     ld_acc(acc + c, d);
-    const int j = colbase + c;
-    const int pa = (j >> 7) * 256 + (j & 127), pg = pa + 128;
-    chunk_load_f32(e, p.u, 2048, pa, a);
-    chunk_load_f32(e, p.u, 2048, pg, g);
+    chunk_ld_finish(e, t, x);
+    chunk_ld_issue(e, p.u, 2048, pg, t);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) { a[i] *= d[i]; g[i] *= d[i]; }    // u = (gelu(gate) | a * gelu'(gate))
-    chunk_store_split(e, a, p.out_hi, p.out_lo, p.ldS, pa);
-    chunk_store_split(e, g, p.out_hi, p.out_lo, p.ldS, pg);
+    for (int i = 0; i < 32; ++i) x[i] *= d[i];                      // u = (gelu(gate) | a * gelu'(gate))
+    chunk_store_split(e, x, p.out_hi, p.out_lo, p.ldS, pa);
+    chunk_ld_finish(e, t, x);
+    if (c + 32 < c1) chunk_ld_issue(e, p.u, 2048, u_col(c + 32), t);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) x[i] *= d[i];
+    chunk_store_split(e, x, p.out_hi, p.out_lo, p.ldS, pg);
   }
 }
 // LayerNorm forward over the 256 channels of the row this thread owns (eps 1e-5, layers_attention_mini.py:138-140)
 // This thread drains columns [c0, c1) of its row; with c1 - c0 == 128 the thread of the other half shares the statistics.
 __device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int c0, int c1) {
   float shift = 0.f, s = 0.f, ss = 0.f;
+  float4 t[8];
+  if (p.residual) chunk_ld_issue(e, p.residual, p.ldR, c0, t);
+#pragma unroll 1
   for (int c = c0; c < c1; c += 32) {
     float v[32];
     ld_acc(acc + c, v);
-    epi_affine(p, e, v, c);
+    epi_affine_pf(p, e, v, c, t, c + 32, c + 32 < c1);
     if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, c);
     if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, c);
     st_acc(acc + c, v);
@@ -418,10 +450,14 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e,
   float mean = 0.f, rstd = 0.f;
   if (e.my_ok) { const float2 st = *reinterpret_cast<const float2*>(p.ln_stats + e.my_row * 2); mean = st.x; rstd = st.y; }
   float s1 = 0.f, s2 = 0.f;
+  float4 t[8];                                  // loads in flight (next ln_x chunk, or the residual chunk)
+  chunk_ld_issue(e, p.ln_x, 256, c0, t);
+#pragma unroll 1
   for (int c = c0; c < c1; c += 32) {
     float d[32], x[32];
     ld_acc(acc + c, d);
-    chunk_load_f32(e, p.ln_x, 256, c, x);
+    chunk_ld_finish(e, t, x);
+    chunk_ld_issue(e, p.ln_x, 256, c + 32 < c1 ? c + 32 : c0, t);      // the last one is the first chunk of pass 2
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
       const float4 g = *reinterpret_cast<const float4*>(p.ln_gamma + c + i);
@@ -437,18 +473,25 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e,
     pair_sync(e.bar_id);
     if (c0 == 0) { const float2 peer = *e.xch; s1 += peer.x; s2 += peer.y; *e.xch = make_float2(s1, s2); }
     pair_sync(e.bar_id);
-    if (c0 != 0) { const float2 t = *e.xch; s1 = t.x; s2 = t.y; }
+    if (c0 != 0) { const float2 t2 = *e.xch; s1 = t2.x; s2 = t2.y; }
   }
   s1 *= (1.f / 256.f); s2 *= (1.f / 256.f);
+#pragma unroll 1
   for (int c = c0; c < c1; c += 32) {
     float d[32], x[32];
+    const bool more = c + 32 < c1;
     ld_acc(acc + c, d);
-    chunk_load_f32(e, p.ln_x, 256, c, x);
+    chunk_ld_finish(e, t, x);
+    if (p.residual) chunk_ld_issue(e, p.residual, p.ldR, c, t);
+    else if (more) chunk_ld_issue(e, p.ln_x, 256, c + 32, t);
 #pragma unroll
     for (int i = 0; i < 32; ++i) d[i] = rstd * (d[i] - s1 - (x[i] - mean) * rstd * s2);
-    if (p.residual) { chunk_load_f32(e, p.residual, p.ldR, c, x);
+    if (p.residual) {
+      chunk_ld_finish(e, t, x);
+      if (more) chunk_ld_issue(e, p.ln_x, 256, c + 32, t);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) d[i] += x[i]; }
+      for (int i = 0; i < 32; ++i) d[i] += x[i];
+    }
     if (p.out_f32) chunk_store_f32(e, d, p.out_f32, p.ldO, c);
     if (p.out_hi) chunk_store_split(e, d, p.out_hi, p.out_lo, p.ldS, c);
   }
@@ -457,6 +500,8 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e,
 // ---------------------------------------------------------------------------------------------
 // kernel
 // ---------------------------------------------------------------------------------------------
+// One instantiation per epilogue mode: each gets its own register allocation (the modes' live sets differ a lot).
+template <int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant__ CUtensorMap mapAlo,
                const __grid_constant__ CUtensorMap mapBhi, const __grid_constant__ CUtensorMap mapBlo,
@@ -579,10 +624,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
     const int step = p.coop ? (int)gridDim.x : 2 * (int)gridDim.x;
     int lt = p.coop ? 0 : group;
     int tile = blockIdx.x + lt * (int)gridDim.x;
-    if (tile < total_tiles) {       // inputs of the first tile; later tiles are prefetched one tile ahead
-      bool ok; const size_t row = my_row_of(tile / p.n_tiles, ok);
-      epi_prefetch(p, ok, row, tile % p.n_tiles, c0, c1);
-    }
     for (; tile < total_tiles; tile += step, lt += p.coop ? 1 : 2) {
       const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
       const int buf = lt & 1;
@@ -595,21 +636,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
         const int nl = rr / p.L_out, ll = rr - nl * p.L_out;
         const int smp = tile_m * p.nb + nl;
         if (nl < p.nb && smp < p.n_samples) e.ok8 |= 1u << i;
-        e.row8[i] = (size_t)smp * p.o_L + (size_t)ll * p.o_stride + p.o_off;
-      }
-      if (tile + step < total_tiles) {
-        const int nt = tile + step;
-        bool ok; const size_t row = my_row_of(nt / p.n_tiles, ok);
-        epi_prefetch(p, ok, row, nt % p.n_tiles, c0, c1);
+        e.row8[i] = (uint32_t)(smp * p.o_L + ll * p.o_stride + p.o_off);
       }
       mbar_wait(tfull0 + 8 * buf, (lt >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t acc = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);
       if (p.BN == 16) epi_plain16(p, e, acc, tile_n * 16);
-      else if (p.epi == EPI_PLAIN) epi_plain(p, e, acc, tile_n * p.BN, c0, c1);
-      else if (p.epi == EPI_GEGLU_FWD) epi_geglu_fwd(p, e, acc, tile_n, c0, c1);
-      else if (p.epi == EPI_GEGLU_BWD) epi_geglu_bwd(p, e, acc, tile_n * p.BN, c0, c1);
-      else if (p.epi == EPI_LN_FWD) epi_ln_fwd(p, e, acc, c0, c1);
+      else if (EPI == EPI_PLAIN) epi_plain(p, e, acc, tile_n * p.BN, c0, c1);
+      else if (EPI == EPI_GEGLU_FWD) epi_geglu_fwd(p, e, acc, tile_n, c0, c1);
+      else if (EPI == EPI_GEGLU_BWD) epi_geglu_bwd(p, e, acc, tile_n * p.BN, c0, c1);
+      else if (EPI == EPI_LN_FWD) epi_ln_fwd(p, e, acc, c0, c1);
       else epi_ln_bwd(p, e, acc, c0, c1);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
@@ -633,9 +669,9 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 static EncodeTiledFn g_encode = nullptr;
 static int g_max_smem = 0;
 static int g_num_sms = 148;
-// tuning knobs (environment, read once): RAMP_GEMM_PREFETCH=<bit mask over GemmEpi> enables the epilogue L2 prefetch per mode, RAMP_GEMM_COOP=0 the
-// cooperative epilogue, RAMP_GEMM_L2PROMO=128|256 picks the tensor-map L2 promotion
-static int g_prefetch = 0, g_coop = 1, g_l2promo = 256;
+// tuning knobs (environment, read once): RAMP_GEMM_COOP=0 disables the cooperative epilogue, RAMP_GEMM_L2PROMO=128|256
+// picks the tensor-map L2 promotion
+static int g_coop = 1, g_l2promo = 256;
 
 int gemm_init() {
   if (g_encode) return 0;
@@ -647,8 +683,12 @@ int gemm_init() {
   RAMP_CUDA_OK(cudaGetDevice(&dev));
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, g_max_smem - XCH_BYTES));
-  if (const char* v = getenv("RAMP_GEMM_PREFETCH")) g_prefetch = atoi(v);
+  const int dyn = g_max_smem - XCH_BYTES;
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_GEGLU_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_GEGLU_BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_LN_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_LN_BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
   if (const char* v = getenv("RAMP_GEMM_COOP")) g_coop = atoi(v);
   if (const char* v = getenv("RAMP_GEMM_L2PROMO")) g_l2promo = atoi(v);
   g_encode = (EncodeTiledFn)fn;
@@ -723,6 +763,7 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   RAMP_CHECK(d.precision == 1 || d.precision == 3, "gemm: precision must be 1 or 3");
   RAMP_CHECK(d.L_in % d.a_pstride == 0, "gemm: L_in must be a multiple of a_pstride");
   RAMP_CHECK(d.epi >= EPI_PLAIN && d.epi <= EPI_LN_BWD, "gemm: unknown epilogue");
+  RAMP_CHECK((long)(d.n_samples + BM) * d.o_L + d.o_off < (1l << 31), "gemm: output row index must fit 31 bits");
   GemmParams p;
   std::memset(&p, 0, sizeof(p));
   p.n_samples = d.n_samples; p.L_out = d.L_out; p.nb = BM / d.L_out;
@@ -745,7 +786,6 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   }
   p.n_tiles = d.Nout / p.BN;
   p.coop = (p.BN >= 64 && g_coop) ? 1 : 0;
-  p.prefetch = (g_prefetch >> d.epi) & 1;
   p.nplanes = d.precision == 3 ? 2 : 1;
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + p.BN * BK * 2);
   const int fixed = 1024 + STG_BYTES + 256;
@@ -785,7 +825,13 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   const size_t smem = (size_t)stages * stage_bytes + fixed;
   const long tiles = (long)p.m_tiles * p.n_tiles;
   dim3 grid((unsigned)(tiles < g_num_sms ? tiles : g_num_sms));
-  gemm_tc_kernel<<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p);
+  switch (d.epi) {
+    case EPI_PLAIN: gemm_tc_kernel<EPI_PLAIN><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
+    case EPI_GEGLU_FWD: gemm_tc_kernel<EPI_GEGLU_FWD><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
+    case EPI_GEGLU_BWD: gemm_tc_kernel<EPI_GEGLU_BWD><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
+    case EPI_LN_FWD: gemm_tc_kernel<EPI_LN_FWD><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
+    default: gemm_tc_kernel<EPI_LN_BWD><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
+  }
   RAMP_LAUNCH_OK();
   return 0;
 }
