@@ -13,16 +13,17 @@
 //   accumulator is double buffered in TMEM (2 x BN columns), so the epilogue of tile i overlaps the
 //   MMAs of tile i+1; the TMA producer runs ahead across tile boundaries through the smem ring.
 // * Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + single-thread tcgen05.mma issuer,
-//   warps 2..9 = two epilogue groups of four (TMEM lane quarter = warp % 4).  For BN >= 64 both groups drain
-//   EVERY tile, each taking half of its columns ("cooperative": the tile's epilogue takes half as long and the
-//   other accumulator buffer is being filled meanwhile, so neither the tensor pipe nor the epilogue warps wait on
-//   each other as long as epilogue/2 >= MMA time or vice versa); for narrower tiles group g owns every other tile.
-//   An epilogue thread owns one accumulator row; global loads / stores are transposed through a per-warp
-//   XOR-swizzled smem staging tile so that every warp-wide access is row-contiguous.
-// * Fused epilogues (GemmEpi): GEGLU forward / backward, LayerNorm forward / backward (Nout == BN == 256: the two
-//   threads that own the halves of a row exchange partial statistics through shared memory and a 64-thread named
-//   barrier; intermediate values are parked back in TMEM with tcgen05.st between the statistics pass and the
-//   normalisation pass).
+//   warps 2..17 = four epilogue groups of four (TMEM lane quarter = warp % 4).  All groups drain EVERY tile, each a
+//   quarter of its columns in chunks of 16 ("cooperative": the other accumulator buffer is being filled meanwhile, so
+//   neither the tensor pipe nor the epilogue warps wait on each other).  The epilogues are latency-bound chains
+//   (tcgen05.ld -> math -> smem transpose -> global), so four warps per SM sub-partition at <= 112 registers beat two
+//   fatter ones.  An epilogue thread owns one accumulator row; global loads / stores are transposed through a
+//   per-warp XOR-swizzled smem staging tile so that every warp-wide access covers whole row segments, and global
+//   loads are issued one chunk ahead of their use.
+// * Fused epilogues (GemmEpi), one kernel instantiation each: GEGLU forward / backward, LayerNorm forward /
+//   backward (Nout == BN == 256: the four threads that own the quarters of a row exchange partial statistics
+//   through the staging tiles and a 128-thread named barrier; intermediate values are parked back in TMEM with
+//   tcgen05.st between the statistics pass and the normalisation pass).
 #include "common.cuh"
 #include <cstdlib>
 #include <cstring>
@@ -35,10 +36,13 @@ namespace ramp {
 static constexpr int BM = 128;
 static constexpr int BK = 64;                 // bf16 elements = 128 B = one SWIZZLE_128B row
 static constexpr int A_TILE_BYTES = BM * BK * 2;
-static constexpr int EPI_WARPS = 8;            // two groups of four: group g drains accumulator buffer g
-static constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;
-static constexpr int XCH_BYTES = 128 * 8;                 // static shared: LayerNorm partial-statistics exchange slots
-static constexpr int STG_BYTES = EPI_WARPS * 32 * 32 * 4;   // per warp a 32 x 32 fp32 tile, XOR-swizzled 16-byte groups
+// Two epilogue configurations (template parameter CW = accumulator columns a thread handles per step):
+//   CW = 32:  8 epilogue warps (2 groups), 128-byte row segments per global access - the memory-heavy epilogues
+//   CW = 16: 16 epilogue warps (4 groups),  64-byte row segments, <= 96 registers  - the math-heavy GEGLU forward
+// Both use 32 KB of staging tiles (one 32 x CW fp32 tile per warp).
+__host__ __device__ constexpr int epi_warps(int cw) { return cw == 32 ? 8 : 16; }
+__host__ __device__ constexpr int gemm_threads(int cw) { return 64 + 32 * epi_warps(cw); }
+static constexpr int STG_BYTES = 32 * 1024;
 
 struct GemmParams {
   int n_samples, L_out, nb;                   // nb = samples per 128-row tile
@@ -51,7 +55,7 @@ struct GemmParams {
   float* out_f32; int ldO;
   bf16* out_hi; bf16* out_lo; int ldS;
   int o_L, o_stride, o_off;
-  int epi, coop;                              // coop: both epilogue groups split the columns of every tile
+  int epi, ngroups;                           // ngroups = epilogue groups that drain a tile: min(BN / CW, epilogue warps / 4)
   const float* ln_gamma; const float* ln_beta; float* ln_stats; const float* ln_x; const float* u;
   bf16* out2_hi; bf16* out2_lo; int ldS2;
 };
@@ -146,354 +150,354 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void ld_acc(uint32_t taddr, float (&v)[32]) {
-  uint32_t r[32];
-  tmem_ld32(taddr, r);
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+        "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+// CW = epilogue chunk width: accumulator columns a thread handles per step (32 or 16)
+template <int CW>
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t* r) {
+  if constexpr (CW == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
+}
+template <int CW>
+__device__ __forceinline__ void ld_acc(uint32_t taddr, float (&v)[CW]) {
+  uint32_t r[CW];
+  tmem_ld<CW>(taddr, r);
   tmem_ld_wait();
 #pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+  for (int i = 0; i < CW; ++i) v[i] = __uint_as_float(r[i]);
 }
-__device__ __forceinline__ void st_acc(uint32_t taddr, const float (&v)[32]) {
-  uint32_t r[32];
+// two accumulator chunks with one wait
+template <int CW>
+__device__ __forceinline__ void ld_acc2(uint32_t t0, float (&v0)[CW], uint32_t t1, float (&v1)[CW]) {
+  uint32_t r0[CW], r1[CW];
+  tmem_ld<CW>(t0, r0);
+  tmem_ld<CW>(t1, r1);
+  tmem_ld_wait();
 #pragma unroll
-  for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(v[i]);
-  tmem_st32(taddr, r);
+  for (int i = 0; i < CW; ++i) { v0[i] = __uint_as_float(r0[i]); v1[i] = __uint_as_float(r1[i]); }
+}
+template <int CW>
+__device__ __forceinline__ void st_acc(uint32_t taddr, const float (&v)[CW]) {
+  uint32_t r[CW];
+#pragma unroll
+  for (int i = 0; i < CW; ++i) r[i] = __float_as_uint(v[i]);
+  if constexpr (CW == 32) tmem_st32(taddr, r); else tmem_st16(taddr, r);
 }
 
 // ---------------------------------------------------------------------------------------------
-// epilogue plumbing: a thread owns accumulator row (q*32 + lane) of the tile; for global traffic the
-// warp re-maps to (row = (lane >> 3) + 4 i, 16-byte column group = lane & 7) through its staging tile.
+// epilogue plumbing: a thread owns accumulator row (q*32 + lane) of the tile and works on it in chunks of CW columns
+// (G = CW/4 16-byte groups).  For global traffic the warp re-maps to (row = lane / G + (32/G) i, group = lane % G)
+// through its staging tile, so every warp-wide access covers whole row segments of 4 CW bytes.
 // ---------------------------------------------------------------------------------------------
-// staging tile: float4 group k of row r lives at float4 index r * 8 + (k ^ (r & 7))  (conflict-free both ways)
-__device__ __forceinline__ int stg_idx(int r, int k) { return r * 8 + (k ^ (r & 7)); }
+// staging tile (32 rows x 4 CW bytes): group k of row r is XOR-swizzled so that both the row-owner accesses and the
+// transposed accesses are bank-conflict free
+template <int CW>
+__device__ __forceinline__ int stg_idx(int r, int k) {
+  if constexpr (CW == 32) return r * 8 + (k ^ (r & 7));
+  else return r * 4 + (k ^ ((r >> 1) & 3));
+}
+template <int CW>
 struct EpiCtx {
-  float* stg;              // this warp's staging tile (32 x 32 fp32)
-  int lane;
+  static constexpr int G = CW / 4, RP = 32 / G, NP = G;   // groups per row, rows per pass, passes
+  float* stg;              // this warp's staging tile
+  float* stg_q;            // staging tile of group 0's warp for this lane quarter (+ 4 * 32 * CW floats per group)
+  int lane, bar_id;
   bool my_ok; size_t my_row; int my_sample;
-  unsigned ok8; uint32_t row8[8];
-  float2* xch; int bar_id;                                   // LayerNorm statistics exchange slot shared with the other half's thread
+  unsigned okn; uint32_t rown[NP];
 };
-// the two warps (same lane quarter, one per group) that share a tile's rows meet here
-__device__ __forceinline__ void pair_sync(int bar_id) { asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory"); }
+// the NG warps (same TMEM lane quarter, one per group) that share a tile's rows meet here
+template <int NG>
+__device__ __forceinline__ void row_sync(int bar_id) { asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(32 * NG) : "memory"); }
 
-// v[32] (this thread's row, columns col0..col0+31) -> base[row * ld + col0 ..] for every live row of the warp
-__device__ __forceinline__ void chunk_store_f32(const EpiCtx& e, const float (&v)[32], float* base, int ld, int col0) {
+// v[CW] (this thread's row, columns col0..col0+CW-1) -> base[row * ld + col0 ..] for every live row of the warp
+template <int CW>
+__device__ __forceinline__ void chunk_store_f32(const EpiCtx<CW>& e, const float (&v)[CW], float* base, int ld, int col0) {
+  using E = EpiCtx<CW>;
   float4* s4 = reinterpret_cast<float4*>(e.stg);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) s4[stg_idx(e.lane, k)] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+  for (int k = 0; k < E::G; ++k) s4[stg_idx<CW>(e.lane, k)] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
   __syncwarp();
-  const int rsub = e.lane >> 3, c4 = e.lane & 7;
+  const int rsub = e.lane / E::G, c4 = e.lane % E::G;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const float4 t = s4[stg_idx(rsub + 4 * i, c4)];
-    if ((e.ok8 >> i) & 1u) *reinterpret_cast<float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4) = t;
+  for (int i = 0; i < E::NP; ++i) {
+    const float4 t = s4[stg_idx<CW>(rsub + E::RP * i, c4)];
+    if ((e.okn >> i) & 1u) *reinterpret_cast<float4*>(base + (size_t)e.rown[i] * ld + col0 + 4 * c4) = t;
   }
   __syncwarp();
 }
-// same, as bf16 hi / lo planes (ld, col0 in bf16 elements)
-__device__ __forceinline__ void chunk_store_split(const EpiCtx& e, const float (&v)[32], bf16* hi, bf16* lo, int ld, int col0) {
+// same, as bf16 hi / lo planes (ld, col0 in bf16 elements): staging row = [hi 2 CW bytes | lo 2 CW bytes]
+template <int CW>
+__device__ __forceinline__ void chunk_store_split(const EpiCtx<CW>& e, const float (&v)[CW], bf16* hi, bf16* lo, int ld, int col0) {
+  using E = EpiCtx<CW>;
+  constexpr int H = E::G / 2;
   uint4* s4 = reinterpret_cast<uint4*>(e.stg);
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
+  for (int k = 0; k < H; ++k) {
     uint32_t h[4], l[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) split2_bf16(v[8 * k + 2 * j], v[8 * k + 2 * j + 1], h[j], l[j]);
-    s4[stg_idx(e.lane, k)] = make_uint4(h[0], h[1], h[2], h[3]);
-    s4[stg_idx(e.lane, 4 + k)] = make_uint4(l[0], l[1], l[2], l[3]);
+    s4[stg_idx<CW>(e.lane, k)] = make_uint4(h[0], h[1], h[2], h[3]);
+    s4[stg_idx<CW>(e.lane, H + k)] = make_uint4(l[0], l[1], l[2], l[3]);
   }
   __syncwarp();
-  const int rsub = e.lane >> 3, c4 = e.lane & 7;
-  bf16* plane = (c4 < 4) ? hi : lo;
+  const int rsub = e.lane / E::G, c4 = e.lane % E::G;
+  bf16* plane = (c4 < H) ? hi : lo;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const uint4 t = s4[stg_idx(rsub + 4 * i, c4)];
-    if ((e.ok8 >> i) & 1u) *reinterpret_cast<uint4*>(plane + (size_t)e.row8[i] * ld + col0 + 8 * (c4 & 3)) = t;
-  }
-  __syncwarp();
-}
-// base[row * ld + col0 ..] -> v[32] for this thread's row (zeros for dead rows)
-__device__ __forceinline__ void chunk_load_f32(const EpiCtx& e, const float* __restrict__ base, int ld, int col0, float (&v)[32]) {
-  const int rsub = e.lane >> 3, c4 = e.lane & 7;
-  float4* s4 = reinterpret_cast<float4*>(e.stg);
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-    if ((e.ok8 >> i) & 1u) t = *reinterpret_cast<const float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4);
-    s4[stg_idx(rsub + 4 * i, c4)] = t;
-  }
-  __syncwarp();
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const float4 t = s4[stg_idx(e.lane, k)];
-    v[4 * k] = t.x; v[4 * k + 1] = t.y; v[4 * k + 2] = t.z; v[4 * k + 3] = t.w;
+  for (int i = 0; i < E::NP; ++i) {
+    const uint4 t = s4[stg_idx<CW>(rsub + E::RP * i, c4)];
+    if ((e.okn >> i) & 1u) *reinterpret_cast<uint4*>(plane + (size_t)e.rown[i] * ld + col0 + 8 * (c4 % H)) = t;
   }
   __syncwarp();
 }
-// two-phase form: `chunk_ld_issue` puts the 8 row-contiguous 16-byte loads of the chunk in flight (registers),
-// `chunk_ld_finish` transposes them through the staging tile into the thread's own row.  Issuing the next chunk's loads
-// before the current chunk's arithmetic and stores keeps ~8 KB per warp in flight, which is what hides HBM latency here.
-__device__ __forceinline__ void chunk_ld_issue(const EpiCtx& e, const float* __restrict__ base, int ld, int col0, float4 (&t)[8]) {
-  const int c4 = e.lane & 7;
+// Loads come in two phases: `chunk_ld_issue` puts the row-contiguous 16-byte loads of a chunk in flight (registers),
+// `chunk_ld_finish` transposes them through the staging tile into the thread's own row (zeros for dead rows).
+// Issuing the next chunk's loads before the current chunk's arithmetic and stores is what hides HBM latency here.
+template <int CW>
+__device__ __forceinline__ void chunk_ld_issue(const EpiCtx<CW>& e, const float* __restrict__ base, int ld, int col0,
+                                               float4 (&t)[CW / 4]) {
+  using E = EpiCtx<CW>;
+  const int c4 = e.lane % E::G;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
+  for (int i = 0; i < E::NP; ++i) {
     t[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if ((e.ok8 >> i) & 1u) t[i] = __ldg(reinterpret_cast<const float4*>(base + (size_t)e.row8[i] * ld + col0 + 4 * c4));
+    if ((e.okn >> i) & 1u) t[i] = __ldg(reinterpret_cast<const float4*>(base + (size_t)e.rown[i] * ld + col0 + 4 * c4));
   }
 }
-__device__ __forceinline__ void chunk_ld_finish(const EpiCtx& e, const float4 (&t)[8], float (&v)[32]) {
-  const int rsub = e.lane >> 3, c4 = e.lane & 7;
+template <int CW>
+__device__ __forceinline__ void chunk_ld_finish(const EpiCtx<CW>& e, const float4 (&t)[CW / 4], float (&v)[CW]) {
+  using E = EpiCtx<CW>;
+  const int rsub = e.lane / E::G, c4 = e.lane % E::G;
   float4* s4 = reinterpret_cast<float4*>(e.stg);
 #pragma unroll
-  for (int i = 0; i < 8; ++i) s4[stg_idx(rsub + 4 * i, c4)] = t[i];
+  for (int i = 0; i < E::NP; ++i) s4[stg_idx<CW>(rsub + E::RP * i, c4)] = t[i];
   __syncwarp();
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const float4 x = s4[stg_idx(e.lane, k)];
+  for (int k = 0; k < E::G; ++k) {
+    const float4 x = s4[stg_idx<CW>(e.lane, k)];
     v[4 * k] = x.x; v[4 * k + 1] = x.y; v[4 * k + 2] = x.z; v[4 * k + 3] = x.w;
   }
   __syncwarp();
 }
-__device__ __forceinline__ void add_vec32(float (&v)[32], const float* __restrict__ b) {
+template <int CW>
+__device__ __forceinline__ void chunk_load_f32(const EpiCtx<CW>& e, const float* __restrict__ base, int ld, int col0, float (&v)[CW]) {
+  float4 t[CW / 4];
+  chunk_ld_issue<CW>(e, base, ld, col0, t);
+  chunk_ld_finish<CW>(e, t, v);
+}
+template <int CW>
+__device__ __forceinline__ void add_vec(float (&v)[CW], const float* __restrict__ b) {
 #pragma unroll
-  for (int i = 0; i < 32; i += 4) {
-    const float4 t = *reinterpret_cast<const float4*>(b + i);
+  for (int i = 0; i < CW; i += 4) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(b + i));
     v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
   }
 }
-// acc + bias + per-scene bias + residual(s) for columns col .. col+31
-__device__ __forceinline__ void epi_affine(const GemmParams& p, const EpiCtx& e, float (&v)[32], int col) {
-  if (p.bias) add_vec32(v, p.bias + col);
-  if (p.bias_tab && e.my_ok) add_vec32(v, p.bias_tab + (size_t)p.row2scene[e.my_sample] * p.Nout + col);
-  if (p.residual) { float r[32]; chunk_load_f32(e, p.residual, p.ldR, col, r);
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] += r[i]; }
-  if (p.residual2) { float r[32]; chunk_load_f32(e, p.residual2, p.ldR2, col, r);
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] += r[i]; }
-}
-
-// same with the residual chunk carried in flight: `t` holds the loads of columns `col` on entry and of `next_col` on exit
-__device__ __forceinline__ void epi_affine_pf(const GemmParams& p, const EpiCtx& e, float (&v)[32], int col, float4 (&t)[8],
-                                              int next_col, bool has_next) {
-  if (p.bias) add_vec32(v, p.bias + col);
-  if (p.bias_tab && e.my_ok) add_vec32(v, p.bias_tab + (size_t)p.row2scene[e.my_sample] * p.Nout + col);
+// acc + bias + per-scene bias + residual(s) for columns col .. col+CW-1; the residual chunk is carried in flight: `t`
+// holds the loads of columns `col` on entry and of `next_col` on exit
+template <int CW>
+__device__ __forceinline__ void epi_affine_pf(const GemmParams& p, const EpiCtx<CW>& e, float (&v)[CW], int col,
+                                              float4 (&t)[CW / 4], int next_col, bool has_next) {
+  if (p.bias) add_vec<CW>(v, p.bias + col);
+  if (p.bias_tab && e.my_ok) add_vec<CW>(v, p.bias_tab + (size_t)p.row2scene[e.my_sample] * p.Nout + col);
   if (p.residual) {
-    float r[32];
-    chunk_ld_finish(e, t, r);
-    if (has_next) chunk_ld_issue(e, p.residual, p.ldR, next_col, t);
+    float r[CW];
+    chunk_ld_finish<CW>(e, t, r);
+    if (has_next) chunk_ld_issue<CW>(e, p.residual, p.ldR, next_col, t);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] += r[i];
+    for (int i = 0; i < CW; ++i) v[i] += r[i];
   }
-  if (p.residual2) { float r[32]; chunk_load_f32(e, p.residual2, p.ldR2, col, r);
+  if (p.residual2) {
+    float r[CW];
+    chunk_load_f32<CW>(e, p.residual2, p.ldR2, col, r);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] += r[i]; }
+    for (int i = 0; i < CW; ++i) v[i] += r[i];
+  }
 }
 
-// ---- one tile's epilogue, by mode.  acc = TMEM address of this warp's lane quarter, column 0 of the tile ----
-__device__ __forceinline__ void epi_plain(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase, int c0, int c1) {
-  float4 t[8];
-  if (p.residual) chunk_ld_issue(e, p.residual, p.ldR, colbase + c0, t);
+// ---- one tile's epilogue, by mode.  acc = TMEM address of this warp's lane quarter, column 0 of the tile;
+//      [c0, c1) = the tile columns this warp's group drains ----
+template <int CW>
+__device__ __forceinline__ void epi_plain(const GemmParams& p, const EpiCtx<CW>& e, uint32_t acc, int colbase, int c0, int c1) {
+  float4 t[CW / 4];
+  if (p.residual) chunk_ld_issue<CW>(e, p.residual, p.ldR, colbase + c0, t);
 #pragma unroll 1
-  for (int c = c0; c < c1; c += 32) {
-    float v[32];
-    ld_acc(acc + c, v);
-    epi_affine_pf(p, e, v, colbase + c, t, colbase + c + 32, c + 32 < c1);
-    if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, colbase + c);
-    if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, colbase + c);
+  for (int c = c0; c < c1; c += CW) {
+    float v[CW];
+    ld_acc<CW>(acc + c, v);
+    epi_affine_pf<CW>(p, e, v, colbase + c, t, colbase + c + CW, c + CW < c1);
+    if (p.out_f32) chunk_store_f32<CW>(e, v, p.out_f32, p.ldO, colbase + c);
+    if (p.out_hi) chunk_store_split<CW>(e, v, p.out_hi, p.out_lo, p.ldS, colbase + c);
   }
 }
-// BN == 16 tiles (Nout == 16): tiny outputs, direct per-row stores
-__device__ __forceinline__ void epi_plain16(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase) {
-  uint32_t r[16];
-  tmem_ld16(acc, r);
-  tmem_ld_wait();
-  if (!e.my_ok) return;
-  float v[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-  if (p.bias)
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] += p.bias[colbase + i];
-  if (p.bias_tab) {
-    const float* bt = p.bias_tab + (size_t)p.row2scene[e.my_sample] * p.Nout + colbase;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] += bt[i];
-  }
-  if (p.residual)
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] += p.residual[e.my_row * p.ldR + colbase + i];
-  if (p.residual2)
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] += p.residual2[e.my_row * p.ldR2 + colbase + i];
-  if (p.out_f32) {
-    float* o = p.out_f32 + e.my_row * p.ldO + colbase;
-#pragma unroll
-    for (int i = 0; i < 16; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-  }
-  if (p.out_hi) {
-    __align__(16) bf16 h[16];
-    __align__(16) bf16 l[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) split_bf16(v[i], h[i], l[i]);
-    bf16* oh = p.out_hi + e.my_row * p.ldS + colbase;
-    bf16* ol = p.out_lo + e.my_row * p.ldS + colbase;
-    *reinterpret_cast<uint4*>(oh) = *reinterpret_cast<const uint4*>(h);
-    *reinterpret_cast<uint4*>(oh + 8) = *reinterpret_cast<const uint4*>(h + 8);
-    *reinterpret_cast<uint4*>(ol) = *reinterpret_cast<const uint4*>(l);
-    *reinterpret_cast<uint4*>(ol + 8) = *reinterpret_cast<const uint4*>(l + 8);
-  }
-}
-// GEGLU forward (layers_attention_mini.py:38-45): tile columns [0,128) = a, [128,256) = gate
-__device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int tile_n, int c0, int c1) {
+// GEGLU forward (layers_attention_mini.py:38-45): tile columns [0,128) = a, [128,256) = gate; a group drains the same
+// sub-range of both
+template <int CW>
+__device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx<CW>& e, uint32_t acc, int tile_n, int c0, int c1) {
   const int colbase = tile_n * 256;
-  for (int c = c0 >> 1; c < (c1 >> 1); c += 32) {
-    float a[32], g[32], s_[32];
-    ld_acc(acc + c, a);
-    ld_acc(acc + 128 + c, g);
-    if (p.bias) { add_vec32(a, p.bias + colbase + c); add_vec32(g, p.bias + colbase + 128 + c); }
+#pragma unroll 1
+  for (int c = c0 >> 1; c < (c1 >> 1); c += CW) {
+    float a[CW], g[CW], s_[CW];
+    ld_acc2<CW>(acc + c, a, acc + 128 + c, g);
+    if (p.bias) { add_vec<CW>(a, p.bias + colbase + c); add_vec<CW>(g, p.bias + colbase + 128 + c); }
     // s = gelu(gate), q = a * gelu'(gate): everything the backward needs, so it is two multiplies per element there
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
+    for (int i = 0; i < CW; ++i) {
       float cdf, pdf;
       normal_cdf_pdf(g[i], cdf, pdf);
       const float sgl = g[i] * cdf;
       g[i] = a[i] * (cdf + g[i] * pdf);
       a[i] *= sgl;
-      if (p.out_f32) s_[i] = sgl;
+      s_[i] = sgl;
     }
     if (p.out_f32) {
-      chunk_store_f32(e, s_, p.out_f32, p.ldO, colbase + c);
-      chunk_store_f32(e, g, p.out_f32, p.ldO, colbase + 128 + c);
+      chunk_store_f32<CW>(e, s_, p.out_f32, p.ldO, colbase + c);
+      chunk_store_f32<CW>(e, g, p.out_f32, p.ldO, colbase + 128 + c);
     }
-    chunk_store_split(e, a, p.out2_hi, p.out2_lo, p.ldS2, tile_n * 128 + c);
+    chunk_store_split<CW>(e, a, p.out2_hi, p.out2_lo, p.ldS2, tile_n * 128 + c);
   }
 }
 // GEGLU backward: acc = d(a * gelu(gate)) for natural columns colbase + c; u = (gelu(gate) | a gelu'(gate)) and du are
 // tile-interleaved
-__device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int colbase, int c0, int c1) {
+template <int CW>
+__device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx<CW>& e, uint32_t acc, int colbase, int c0, int c1) {
   auto u_col = [&](int c) { const int j = colbase + c; return (j >> 7) * 256 + (j & 127); };
-  float4 t[8];                                   // the loads in flight: gelu(gate) of chunk c, then a gelu'(gate), then chunk c + 32 ...
-  chunk_ld_issue(e, p.u, 2048, u_col(c0), t);
+  float4 t[CW / 4];                              // the loads in flight: gelu(gate) of chunk c, then a gelu'(gate), then chunk c + CW ...
+  chunk_ld_issue<CW>(e, p.u, 2048, u_col(c0), t);
 #pragma unroll 1
-  for (int c = c0; c < c1; c += 32) {
-    float d[32], x[32];
+  for (int c = c0; c < c1; c += CW) {
+    float d[CW], x[CW];
     const int pa = u_col(c), pg = pa + 128;
-    ld_acc(acc + c, d);
-    chunk_ld_finish(e, t, x);
-    chunk_ld_issue(e, p.u, 2048, pg, t);
+    ld_acc<CW>(acc + c, d);
+    chunk_ld_finish<CW>(e, t, x);
+    chunk_ld_issue<CW>(e, p.u, 2048, pg, t);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) x[i] *= d[i];                      // u = (gelu(gate) | a * gelu'(gate))
-    chunk_store_split(e, x, p.out_hi, p.out_lo, p.ldS, pa);
-    chunk_ld_finish(e, t, x);
-    if (c + 32 < c1) chunk_ld_issue(e, p.u, 2048, u_col(c + 32), t);
+    for (int i = 0; i < CW; ++i) x[i] *= d[i];                      // u = (gelu(gate) | a * gelu'(gate))
+    chunk_store_split<CW>(e, x, p.out_hi, p.out_lo, p.ldS, pa);
+    chunk_ld_finish<CW>(e, t, x);
+    if (c + CW < c1) chunk_ld_issue<CW>(e, p.u, 2048, u_col(c + CW), t);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) x[i] *= d[i];
-    chunk_store_split(e, x, p.out_hi, p.out_lo, p.ldS, pg);
+    for (int i = 0; i < CW; ++i) x[i] *= d[i];
+    chunk_store_split<CW>(e, x, p.out_hi, p.out_lo, p.ldS, pg);
   }
 }
-// LayerNorm forward over the 256 channels of the row this thread owns (eps 1e-5, layers_attention_mini.py:138-140)
-// This thread drains columns [c0, c1) of its row; with c1 - c0 == 128 the thread of the other half shares the statistics.
-__device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int c0, int c1) {
+// The NG threads that own the parts of a 256-channel row publish a float2 each (through their warps' staging tiles,
+// idle at that point) and read all of them back: everyone combines them in the same order, so they agree to the bit.
+template <int CW, int NG>
+__device__ __forceinline__ void row_exchange(const EpiCtx<CW>& e, float2 mine, float2 (&all)[NG]) {
+  reinterpret_cast<float2*>(e.stg)[e.lane] = mine;
+  row_sync<NG>(e.bar_id);
+#pragma unroll
+  for (int g = 0; g < NG; ++g) all[g] = reinterpret_cast<const float2*>(e.stg_q + g * (4 * 32 * CW))[e.lane];
+  row_sync<NG>(e.bar_id);                        // nobody re-uses a staging tile before all have read it
+}
+// LayerNorm forward over the 256 channels of a row (eps 1e-5, layers_attention_mini.py:138-140); this thread drains
+// columns [c0, c1) = 256 / NG of them
+template <int CW, int NG>
+__device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx<CW>& e, uint32_t acc, int c0, int c1) {
   float shift = 0.f, s = 0.f, ss = 0.f;
-  float4 t[8];
-  if (p.residual) chunk_ld_issue(e, p.residual, p.ldR, c0, t);
+  float4 t[CW / 4];
+  if (p.residual) chunk_ld_issue<CW>(e, p.residual, p.ldR, c0, t);
 #pragma unroll 1
-  for (int c = c0; c < c1; c += 32) {
-    float v[32];
-    ld_acc(acc + c, v);
-    epi_affine_pf(p, e, v, c, t, c + 32, c + 32 < c1);
-    if (p.out_f32) chunk_store_f32(e, v, p.out_f32, p.ldO, c);
-    if (p.out_hi) chunk_store_split(e, v, p.out_hi, p.out_lo, p.ldS, c);
-    st_acc(acc + c, v);
+  for (int c = c0; c < c1; c += CW) {
+    float v[CW];
+    ld_acc<CW>(acc + c, v);
+    epi_affine_pf<CW>(p, e, v, c, t, c + CW, c + CW < c1);
+    if (p.out_f32) chunk_store_f32<CW>(e, v, p.out_f32, p.ldO, c);
+    if (p.out_hi) chunk_store_split<CW>(e, v, p.out_hi, p.out_lo, p.ldS, c);
+    st_acc<CW>(acc + c, v);
     if (c == c0) shift = v[0];
 #pragma unroll
-    for (int i = 0; i < 32; ++i) { const float d = v[i] - shift; s += d; ss = fmaf(d, d, ss); }
+    for (int i = 0; i < CW; ++i) { const float d = v[i] - shift; s += d; ss = fmaf(d, d, ss); }
   }
   tmem_st_wait();
-  float mean, rstd;
-  if (c1 - c0 == 256) {
-    const float m0 = s * (1.f / 256.f);
-    mean = shift + m0;
-    rstd = rsqrtf(fmaxf(ss * (1.f / 256.f) - m0 * m0, 0.f) + 1e-5f);
+  // (mean, M2) of this thread's 256 / NG values, merged pairwise with the other parts (Chan's update)
+  constexpr float n = 256.f / NG;
+  const float ml = s * (1.f / n);
+  float2 part[NG];
+  row_exchange<CW, NG>(e, make_float2(shift + ml, fmaxf(ss - s * ml, 0.f)), part);
+  float mean, m2;
+  if constexpr (NG == 2) {
+    const float dm = part[1].x - part[0].x;
+    mean = part[0].x + 0.5f * dm;
+    m2 = part[0].y + part[1].y + dm * dm * (0.5f * n);
   } else {
-    // upper half sends (mean, M2) of its 128 values; lower half merges (Chan's update) and returns (mean, rstd)
-    const float ml = s * (1.f / 128.f);
-    const float2 mine = make_float2(shift + ml, fmaxf(ss - s * ml, 0.f));
-    if (c0 != 0) *e.xch = mine;
-    pair_sync(e.bar_id);
-    if (c0 == 0) {
-      const float2 peer = *e.xch;
-      const float dm = peer.x - mine.x;
-      mean = mine.x + 0.5f * dm;
-      rstd = rsqrtf((mine.y + peer.y + dm * dm * 64.f) * (1.f / 256.f) + 1e-5f);
-      *e.xch = make_float2(mean, rstd);
-    }
-    pair_sync(e.bar_id);
-    if (c0 != 0) { const float2 t = *e.xch; mean = t.x; rstd = t.y; }
+    const float d01 = part[1].x - part[0].x, d23 = part[3].x - part[2].x;
+    const float m01 = part[0].x + 0.5f * d01, m23 = part[2].x + 0.5f * d23;
+    const float q01 = part[0].y + part[1].y + d01 * d01 * (0.5f * n), q23 = part[2].y + part[3].y + d23 * d23 * (0.5f * n);
+    const float dm = m23 - m01;
+    mean = m01 + 0.5f * dm;
+    m2 = q01 + q23 + dm * dm * n;
   }
+  const float rstd = rsqrtf(m2 * (1.f / 256.f) + 1e-5f);
   if (p.ln_stats && e.my_ok && c0 == 0) *reinterpret_cast<float2*>(p.ln_stats + e.my_row * 2) = make_float2(mean, rstd);
-  for (int c = c0; c < c1; c += 32) {
-    float v[32];
-    ld_acc(acc + c, v);
+#pragma unroll 1
+  for (int c = c0; c < c1; c += CW) {
+    float v[CW];
+    ld_acc<CW>(acc + c, v);
 #pragma unroll
-    for (int i = 0; i < 32; i += 4) {
-      const float4 g = *reinterpret_cast<const float4*>(p.ln_gamma + c + i);
-      const float4 b = *reinterpret_cast<const float4*>(p.ln_beta + c + i);
+    for (int i = 0; i < CW; i += 4) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + c + i));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.ln_beta + c + i));
       v[i] = (v[i] - mean) * rstd * g.x + b.x; v[i + 1] = (v[i + 1] - mean) * rstd * g.y + b.y;
       v[i + 2] = (v[i + 2] - mean) * rstd * g.z + b.z; v[i + 3] = (v[i + 3] - mean) * rstd * g.w + b.w;
     }
-    chunk_store_split(e, v, p.out2_hi, p.out2_lo, p.ldS2, c);
+    chunk_store_split<CW>(e, v, p.out2_hi, p.out2_lo, p.ldS2, c);
   }
 }
 // out = residual + LayerNorm_backward(ln_x, acc): dx = rstd * (dyh - mean(dyh) - xh * mean(dyh * xh)), dyh = acc * gamma
-__device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e, uint32_t acc, int c0, int c1) {
+template <int CW, int NG>
+__device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx<CW>& e, uint32_t acc, int c0, int c1) {
   float mean = 0.f, rstd = 0.f;
   if (e.my_ok) { const float2 st = *reinterpret_cast<const float2*>(p.ln_stats + e.my_row * 2); mean = st.x; rstd = st.y; }
   float s1 = 0.f, s2 = 0.f;
-  float4 t[8];                                  // loads in flight (next ln_x chunk, or the residual chunk)
-  chunk_ld_issue(e, p.ln_x, 256, c0, t);
+  float4 t[CW / 4];                             // loads in flight (next ln_x chunk, or the residual chunk)
+  chunk_ld_issue<CW>(e, p.ln_x, 256, c0, t);
 #pragma unroll 1
-  for (int c = c0; c < c1; c += 32) {
-    float d[32], x[32];
-    ld_acc(acc + c, d);
-    chunk_ld_finish(e, t, x);
-    chunk_ld_issue(e, p.ln_x, 256, c + 32 < c1 ? c + 32 : c0, t);      // the last one is the first chunk of pass 2
+  for (int c = c0; c < c1; c += CW) {
+    float d[CW], x[CW];
+    ld_acc<CW>(acc + c, d);
+    chunk_ld_finish<CW>(e, t, x);
+    chunk_ld_issue<CW>(e, p.ln_x, 256, c + CW < c1 ? c + CW : c0, t);      // the last one is the first chunk of pass 2
 #pragma unroll
-    for (int i = 0; i < 32; i += 4) {
-      const float4 g = *reinterpret_cast<const float4*>(p.ln_gamma + c + i);
+    for (int i = 0; i < CW; i += 4) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + c + i));
       d[i] *= g.x; d[i + 1] *= g.y; d[i + 2] *= g.z; d[i + 3] *= g.w;
     }
 #pragma unroll
-    for (int i = 0; i < 32; ++i) { s1 += d[i]; s2 = fmaf(d[i], (x[i] - mean) * rstd, s2); }
-    st_acc(acc + c, d);
+    for (int i = 0; i < CW; ++i) { s1 += d[i]; s2 = fmaf(d[i], (x[i] - mean) * rstd, s2); }
+    st_acc<CW>(acc + c, d);
   }
   tmem_st_wait();
-  if (c1 - c0 != 256) {
-    if (c0 != 0) *e.xch = make_float2(s1, s2);
-    pair_sync(e.bar_id);
-    if (c0 == 0) { const float2 peer = *e.xch; s1 += peer.x; s2 += peer.y; *e.xch = make_float2(s1, s2); }
-    pair_sync(e.bar_id);
-    if (c0 != 0) { const float2 t2 = *e.xch; s1 = t2.x; s2 = t2.y; }
+  {
+    float2 part[NG];
+    row_exchange<CW, NG>(e, make_float2(s1, s2), part);
+    if constexpr (NG == 2) { s1 = part[0].x + part[1].x; s2 = part[0].y + part[1].y; }
+    else { s1 = (part[0].x + part[1].x) + (part[2].x + part[3].x); s2 = (part[0].y + part[1].y) + (part[2].y + part[3].y); }
+    s1 *= (1.f / 256.f); s2 *= (1.f / 256.f);
   }
-  s1 *= (1.f / 256.f); s2 *= (1.f / 256.f);
 #pragma unroll 1
-  for (int c = c0; c < c1; c += 32) {
-    float d[32], x[32];
-    const bool more = c + 32 < c1;
-    ld_acc(acc + c, d);
-    chunk_ld_finish(e, t, x);
-    if (p.residual) chunk_ld_issue(e, p.residual, p.ldR, c, t);
-    else if (more) chunk_ld_issue(e, p.ln_x, 256, c + 32, t);
+  for (int c = c0; c < c1; c += CW) {
+    float d[CW], x[CW];
+    const bool more = c + CW < c1;
+    ld_acc<CW>(acc + c, d);
+    chunk_ld_finish<CW>(e, t, x);
+    if (p.residual) chunk_ld_issue<CW>(e, p.residual, p.ldR, c, t);
+    else if (more) chunk_ld_issue<CW>(e, p.ln_x, 256, c + CW, t);
 #pragma unroll
-    for (int i = 0; i < 32; ++i) d[i] = rstd * (d[i] - s1 - (x[i] - mean) * rstd * s2);
+    for (int i = 0; i < CW; ++i) d[i] = rstd * (d[i] - s1 - (x[i] - mean) * rstd * s2);
     if (p.residual) {
-      chunk_ld_finish(e, t, x);
-      if (more) chunk_ld_issue(e, p.ln_x, 256, c + 32, t);
+      chunk_ld_finish<CW>(e, t, x);
+      if (more) chunk_ld_issue<CW>(e, p.ln_x, 256, c + CW, t);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) d[i] += x[i];
+      for (int i = 0; i < CW; ++i) d[i] += x[i];
     }
-    if (p.out_f32) chunk_store_f32(e, d, p.out_f32, p.ldO, c);
-    if (p.out_hi) chunk_store_split(e, d, p.out_hi, p.out_lo, p.ldS, c);
+    if (p.out_f32) chunk_store_f32<CW>(e, d, p.out_f32, p.ldO, c);
+    if (p.out_hi) chunk_store_split<CW>(e, d, p.out_hi, p.out_lo, p.ldS, c);
   }
 }
 
@@ -501,8 +505,8 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx& e,
 // kernel
 // ---------------------------------------------------------------------------------------------
 // One instantiation per epilogue mode: each gets its own register allocation (the modes' live sets differ a lot).
-template <int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+template <int EPI, int CW>
+__global__ void __launch_bounds__(gemm_threads(CW), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant__ CUtensorMap mapAlo,
                const __grid_constant__ CUtensorMap mapBhi, const __grid_constant__ CUtensorMap mapBlo,
                const GemmParams p) {
@@ -512,7 +516,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b_tile_bytes = p.BN * BK * 2;
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + b_tile_bytes);
-  const uint32_t stg_base = smem_base + p.stages * stage_bytes;            // EPI_WARPS staging tiles
+  const uint32_t stg_base = smem_base + p.stages * stage_bytes;            // the epilogue warps' staging tiles
   const uint32_t bar_base = stg_base + STG_BYTES;
   const uint32_t full0 = bar_base, empty0 = bar_base + 8 * p.stages;
   const uint32_t tfull0 = bar_base + 16 * p.stages, tempty0 = tfull0 + 16;  // 2 + 2 accumulator barriers
@@ -524,7 +528,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(tfull0 + 8 * b, 1); mbar_init(tempty0 + 8 * b, p.coop ? 8 : 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull0 + 8 * b, 1); mbar_init(tempty0 + 8 * b, 4 * p.ngroups); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAhi) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBhi) : "memory");
@@ -604,52 +608,49 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
       }
     }
   } else {
-    // ---------------- epilogue: TMEM lane quarter = warp % 4, group = (warp - 2) / 4 ----------------
+    // ---------------- epilogue: TMEM lane quarter q = warp % 4, group = (warp - 2) / 4 ----------------
+    constexpr int NG = epi_warps(CW) / 4;
     const int q = warp & 3, group = (warp - 2) >> 2;
-    __shared__ float2 xch[128];                             // XCH_BYTES static: one slot per tile row
-    EpiCtx e;
-    e.lane = lane;
-    e.stg = reinterpret_cast<float*>(smem_gen + p.stages * stage_bytes) + (warp - 2) * 32 * 32;
-    e.bar_id = 1 + q;
-    e.xch = &xch[q * 32 + lane];
-    // columns of a tile this group drains
-    const int c0 = p.coop ? group * (p.BN >> 1) : 0, c1 = p.coop ? c0 + (p.BN >> 1) : p.BN;
-    const int r = q * 32 + lane;
-    const int n_local = r / p.L_out, l = r - n_local * p.L_out;
-    auto my_row_of = [&](int tile_m, bool& ok) -> size_t {
-      const int smp = tile_m * p.nb + n_local;
-      ok = n_local < p.nb && smp < p.n_samples;
-      return (size_t)smp * p.o_L + (size_t)l * p.o_stride + p.o_off;
-    };
-    const int step = p.coop ? (int)gridDim.x : 2 * (int)gridDim.x;
-    int lt = p.coop ? 0 : group;
-    int tile = blockIdx.x + lt * (int)gridDim.x;
-    for (; tile < total_tiles; tile += step, lt += p.coop ? 1 : 2) {
-      const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
-      const int buf = lt & 1;
-      e.my_sample = tile_m * p.nb + n_local;
-      e.my_row = my_row_of(tile_m, e.my_ok);
-      e.ok8 = 0;
+    if (group < p.ngroups) {
+      float* stg_all = reinterpret_cast<float*>(smem_gen + p.stages * stage_bytes);
+      EpiCtx<CW> e;
+      using E = EpiCtx<CW>;
+      e.lane = lane;
+      e.bar_id = 1 + q;
+      e.stg = stg_all + (warp - 2) * (32 * CW);
+      e.stg_q = stg_all + ((warp - 2) & 3) * (32 * CW);
+      const int cols = p.BN / p.ngroups;                      // tile columns this group drains
+      const int c0 = group * cols, c1 = c0 + cols;
+      const int r = q * 32 + lane;
+      const int n_local = r / p.L_out, l = r - n_local * p.L_out;
+      int lt = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
+        const int buf = lt & 1;
+        e.my_sample = tile_m * p.nb + n_local;
+        e.my_ok = n_local < p.nb && e.my_sample < p.n_samples;
+        e.my_row = (size_t)e.my_sample * p.o_L + (size_t)l * p.o_stride + p.o_off;
+        e.okn = 0;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int rr = q * 32 + (lane >> 3) + 4 * i;
-        const int nl = rr / p.L_out, ll = rr - nl * p.L_out;
-        const int smp = tile_m * p.nb + nl;
-        if (nl < p.nb && smp < p.n_samples) e.ok8 |= 1u << i;
-        e.row8[i] = (uint32_t)(smp * p.o_L + ll * p.o_stride + p.o_off);
+        for (int i = 0; i < E::NP; ++i) {
+          const int rr = q * 32 + lane / E::G + E::RP * i;
+          const int nl = rr / p.L_out, ll = rr - nl * p.L_out;
+          const int smp = tile_m * p.nb + nl;
+          if (nl < p.nb && smp < p.n_samples) e.okn |= 1u << i;
+          e.rown[i] = (uint32_t)(smp * p.o_L + ll * p.o_stride + p.o_off);
+        }
+        mbar_wait(tfull0 + 8 * buf, (lt >> 1) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t acc = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);
+        if (EPI == EPI_PLAIN) epi_plain<CW>(p, e, acc, tile_n * p.BN, c0, c1);
+        else if (EPI == EPI_GEGLU_FWD) epi_geglu_fwd<CW>(p, e, acc, tile_n, c0, c1);
+        else if (EPI == EPI_GEGLU_BWD) epi_geglu_bwd<CW>(p, e, acc, tile_n * p.BN, c0, c1);
+        else if (EPI == EPI_LN_FWD) epi_ln_fwd<CW, NG>(p, e, acc, c0, c1);
+        else epi_ln_bwd<CW, NG>(p, e, acc, c0, c1);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
       }
-      mbar_wait(tfull0 + 8 * buf, (lt >> 1) & 1);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t acc = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.BN);
-      if (p.BN == 16) epi_plain16(p, e, acc, tile_n * 16);
-      else if (EPI == EPI_PLAIN) epi_plain(p, e, acc, tile_n * p.BN, c0, c1);
-      else if (EPI == EPI_GEGLU_FWD) epi_geglu_fwd(p, e, acc, tile_n, c0, c1);
-      else if (EPI == EPI_GEGLU_BWD) epi_geglu_bwd(p, e, acc, tile_n * p.BN, c0, c1);
-      else if (EPI == EPI_LN_FWD) epi_ln_fwd(p, e, acc, c0, c1);
-      else epi_ln_bwd(p, e, acc, c0, c1);
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -669,9 +670,8 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 static EncodeTiledFn g_encode = nullptr;
 static int g_max_smem = 0;
 static int g_num_sms = 148;
-// tuning knobs (environment, read once): RAMP_GEMM_COOP=0 disables the cooperative epilogue, RAMP_GEMM_L2PROMO=128|256
-// picks the tensor-map L2 promotion
-static int g_coop = 1, g_l2promo = 256;
+// tuning knob (environment, read once): RAMP_GEMM_L2PROMO=128|256 picks the tensor-map L2 promotion
+static int g_l2promo = 256;
 
 int gemm_init() {
   if (g_encode) return 0;
@@ -683,13 +683,13 @@ int gemm_init() {
   RAMP_CUDA_OK(cudaGetDevice(&dev));
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-  const int dyn = g_max_smem - XCH_BYTES;
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_GEGLU_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_GEGLU_BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_LN_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_LN_BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  if (const char* v = getenv("RAMP_GEMM_COOP")) g_coop = atoi(v);
+  const int dyn = g_max_smem;
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_PLAIN, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_PLAIN, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_GEGLU_FWD, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_GEGLU_BWD, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_LN_FWD, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_LN_BWD, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
   if (const char* v = getenv("RAMP_GEMM_L2PROMO")) g_l2promo = atoi(v);
   g_encode = (EncodeTiledFn)fn;
   return 0;
@@ -785,11 +785,12 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
     p.BN = 256;
   }
   p.n_tiles = d.Nout / p.BN;
-  p.coop = (p.BN >= 64 && g_coop) ? 1 : 0;
+  const int cw = (d.epi == EPI_GEGLU_FWD || p.BN == 16) ? 16 : 32;     // epilogue configuration (see epi_warps)
+  p.ngroups = p.BN / cw < epi_warps(cw) / 4 ? p.BN / cw : epi_warps(cw) / 4;
   p.nplanes = d.precision == 3 ? 2 : 1;
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + p.BN * BK * 2);
   const int fixed = 1024 + STG_BYTES + 256;
-  int stages = (g_max_smem - XCH_BYTES - fixed) / stage_bytes;
+  int stages = (g_max_smem - fixed) / stage_bytes;
   if (stages > 6) stages = 6;
   const long total_iters = (long)p.ntaps * p.kblocks * ((long)p.m_tiles * p.n_tiles + g_num_sms - 1) / g_num_sms;
   if (stages > total_iters) stages = (int)total_iters;
@@ -804,7 +805,7 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   p.o_L = d.o_L; p.o_stride = d.o_stride; p.o_off = d.o_off;
   p.ln_gamma = d.ln_gamma; p.ln_beta = d.ln_beta; p.ln_stats = d.ln_stats; p.ln_x = d.ln_x; p.u = d.u;
   p.out2_hi = d.out2_hi; p.out2_lo = d.out2_lo; p.ldS2 = d.ldS2;
-  RAMP_CHECK(p.BN == 16 || ((d.ldO % 4 == 0) && (d.ldS % 8 == 0) && (d.ldR % 4 == 0) && (d.ldR2 % 4 == 0) && (d.ldS2 % 8 == 0)),
+  RAMP_CHECK((d.ldO % 4 == 0) && (d.ldS % 8 == 0) && (d.ldR % 4 == 0) && (d.ldR2 % 4 == 0) && (d.ldS2 % 8 == 0),
              "gemm: output / residual leading dimensions must keep 16-byte alignment");
 
   CUtensorMap mAhi, mAlo, mBhi, mBlo;
@@ -825,13 +826,15 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   const size_t smem = (size_t)stages * stage_bytes + fixed;
   const long tiles = (long)p.m_tiles * p.n_tiles;
   dim3 grid((unsigned)(tiles < g_num_sms ? tiles : g_num_sms));
+#define RAMP_GEMM_LAUNCH(E, C) gemm_tc_kernel<E, C><<<grid, gemm_threads(C), smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p)
   switch (d.epi) {
-    case EPI_PLAIN: gemm_tc_kernel<EPI_PLAIN><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
-    case EPI_GEGLU_FWD: gemm_tc_kernel<EPI_GEGLU_FWD><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
-    case EPI_GEGLU_BWD: gemm_tc_kernel<EPI_GEGLU_BWD><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
-    case EPI_LN_FWD: gemm_tc_kernel<EPI_LN_FWD><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
-    default: gemm_tc_kernel<EPI_LN_BWD><<<grid, GEMM_THREADS, smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p); break;
+    case EPI_PLAIN: if (cw == 16) RAMP_GEMM_LAUNCH(EPI_PLAIN, 16); else RAMP_GEMM_LAUNCH(EPI_PLAIN, 32); break;
+    case EPI_GEGLU_FWD: RAMP_GEMM_LAUNCH(EPI_GEGLU_FWD, 16); break;
+    case EPI_GEGLU_BWD: RAMP_GEMM_LAUNCH(EPI_GEGLU_BWD, 32); break;
+    case EPI_LN_FWD: RAMP_GEMM_LAUNCH(EPI_LN_FWD, 32); break;
+    default: RAMP_GEMM_LAUNCH(EPI_LN_BWD, 32); break;
   }
+#undef RAMP_GEMM_LAUNCH
   RAMP_LAUNCH_OK();
   return 0;
 }
