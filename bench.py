@@ -346,8 +346,18 @@ def _cpu_once(sample_B):
     return time.perf_counter() - t0
 
 
+def _use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1: the CPU arm uses every host core this process may run on."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        n = os.cpu_count() or 1
+    torch.set_num_threads(max(1, n))
+    return torch.get_num_threads()
+
+
 def cpu_baseline(sample_B=2):
-    threads = torch.get_num_threads()
+    threads = _use_all_host_threads()
     dt = _cpu_once(sample_B)
     return {"value": sample_B / dt, "unit": "trajectories/s", "cores": threads, "kind": "port",
             "sample": "%d trajectories x %d network rows x %d DDPM steps (same model/config), %.1f s on %d threads"
@@ -359,7 +369,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    threads = torch.get_num_threads()
+    threads = _use_all_host_threads()
     sample_B = args.cpu_sample
     for _ in range(min(args.warmup, 1)):
         _cpu_once(sample_B)
