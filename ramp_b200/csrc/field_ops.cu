@@ -382,9 +382,9 @@ int ramp_cloud_pack(const float* cloud, int P, int dim, void* packed, void* stre
 
 int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int qstride, float upper_bound,
                   float* out_dist, int32_t* out_idx, void* stream) {
-  RAMP_CHECK(packed && q && out_dist && out_idx, "ramp_nn_query: null argument");
   RAMP_CHECK(dim == 2 || dim == 3, "ramp_nn_query: dim must be 2 or 3");
   if (Q == 0) return 0;
+  RAMP_CHECK(packed && q && out_dist && out_idx, "ramp_nn_query: null argument");
   const int Ppad = (int)ramp_cloud_packed_points(P);
   const float4* c4 = (const float4*)packed;
   cudaStream_t s = (cudaStream_t)stream;

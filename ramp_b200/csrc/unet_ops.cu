@@ -42,12 +42,12 @@ int prep_input(const float* x, int n_samples, int n_pad, int L, int D, int x_rep
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float mish_fast(float x) {
   if (x > 20.f) return x;
-  const float w = expf(x), n = w * (w + 2.f);
-  return x * (n / (n + 2.f));
+  const float w = __expf(x), n = w * (w + 2.f);
+  return x * __fdividef(n, n + 2.f);
 }
 __device__ __forceinline__ float mish_grad_fast(float x) {
   if (x > 20.f) return 1.f;
-  const float w = expf(x), n = w * (w + 2.f), d = 1.f / (n + 2.f);
+  const float w = __expf(x), n = w * (w + 2.f), d = __fdividef(1.f, n + 2.f);
   return n * d + x * (4.f * w * (w + 1.f)) * d * d;
 }
 // sum of v over the lanes that share a group: groups are `seg` adjacent lanes (seg = 1, 2, 4 or 8)
@@ -118,13 +118,17 @@ __device__ __forceinline__ void gn_stats(const GnTile& t, int L, int C, float ep
   __syncthreads();
 }
 
+// CT = the channel count when it is one of the U-Net's (32 / 64 / 128 / 256: every index computation folds to shifts;
+// the generic CT = 0 instantiation divides by runtime values and spends most of its issue slots on that)
+template <int CT>
 __global__ void __launch_bounds__(256) gn_forward_kernel(GnArgs a) {
   __shared__ float red[16], stat[16], part[512];
   const size_t row0 = (size_t)blockIdx.x * a.L;
-  const int cg = a.C / 8;
+  const int C = CT ? CT : a.C;
+  const int cg = C / 8;
   GnTile t;
-  gn_load(t, a.x, a.ldX, row0, a.L, a.C);
-  gn_stats(t, a.L, a.C, a.eps, part, red, stat);
+  gn_load(t, a.x, a.ldX, row0, a.L, C);
+  gn_stats(t, a.L, C, a.eps, part, red, stat);
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     if (!t.ok[i]) continue;
@@ -152,19 +156,27 @@ int gn_forward(const GnArgs& a, cudaStream_t s) {
   RAMP_CHECK(a.C % 32 == 0 && a.L * a.C <= 2048, "gn: C must be a multiple of 32 and L*C <= 2048");
   RAMP_CHECK(a.ldX % 4 == 0 && (!a.add || a.ldAdd % 4 == 0) && (!a.out_f32 || a.ldO % 4 == 0) && (!a.out_hi || a.ldS % 4 == 0),
              "gn: leading dimensions must be multiples of 4");
-  gn_forward_kernel<<<a.n_samples, 256, 0, s>>>(a);
+  switch (a.C) {
+    case 32: gn_forward_kernel<32><<<a.n_samples, 256, 0, s>>>(a); break;
+    case 64: gn_forward_kernel<64><<<a.n_samples, 256, 0, s>>>(a); break;
+    case 128: gn_forward_kernel<128><<<a.n_samples, 256, 0, s>>>(a); break;
+    case 256: gn_forward_kernel<256><<<a.n_samples, 256, 0, s>>>(a); break;
+    default: gn_forward_kernel<0><<<a.n_samples, 256, 0, s>>>(a); break;
+  }
   RAMP_LAUNCH_OK();
   return 0;
 }
 
+template <int CT>
 __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
   __shared__ float red[16], stat[16], red2[16], part[512];
   const size_t row0 = (size_t)blockIdx.x * a.L;
-  const int cg = a.C / 8;
+  const int C = CT ? CT : a.C;
+  const int cg = C / 8;
   const float inv_m = 1.f / (float)(a.L * cg);
   GnTile t;
-  gn_load(t, a.x, a.ldX, row0, a.L, a.C);
-  gn_stats(t, a.L, a.C, a.eps, part, red, stat);
+  gn_load(t, a.x, a.ldX, row0, a.L, C);
+  gn_stats(t, a.L, C, a.eps, part, red, stat);
   float xh[2][4], dyh[2][4], p1[2], p2[2];
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
@@ -186,8 +198,8 @@ __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
       p2[i] += dyh[i][j] * xh[i][j];
     }
   }
-  gn_group_reduce(t, p1, a.L, a.C, part, red2);
-  gn_group_reduce(t, p2, a.L, a.C, part, red2 + 8);
+  gn_group_reduce(t, p1, a.L, C, part, red2);
+  gn_group_reduce(t, p2, a.L, C, part, red2 + 8);
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     if (!t.ok[i]) continue;
@@ -208,7 +220,13 @@ int gn_backward(const GnBwdArgs& a, cudaStream_t s) {
   RAMP_CHECK(a.C % 32 == 0 && a.L * a.C <= 2048, "gn: C must be a multiple of 32 and L*C <= 2048");
   RAMP_CHECK(a.ldX % 4 == 0 && a.ldDy % 4 == 0 && (!a.add || a.ldAdd % 4 == 0) && (!a.out_f32 || a.ldO % 4 == 0) &&
              (!a.out_hi || a.ldS % 4 == 0), "gn: leading dimensions must be multiples of 4");
-  gn_backward_kernel<<<a.n_samples, 256, 0, s>>>(a);
+  switch (a.C) {
+    case 32: gn_backward_kernel<32><<<a.n_samples, 256, 0, s>>>(a); break;
+    case 64: gn_backward_kernel<64><<<a.n_samples, 256, 0, s>>>(a); break;
+    case 128: gn_backward_kernel<128><<<a.n_samples, 256, 0, s>>>(a); break;
+    case 256: gn_backward_kernel<256><<<a.n_samples, 256, 0, s>>>(a); break;
+    default: gn_backward_kernel<0><<<a.n_samples, 256, 0, s>>>(a); break;
+  }
   RAMP_LAUNCH_OK();
   return 0;
 }
