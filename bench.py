@@ -157,6 +157,9 @@ def run_ours(args):
     prof_ms, prof_n = model.model.profile(False, fetch=True)
     sampler.join(timeout=2)
 
+    scene = None
+    if rank == 0 and not args.no_field:
+        scene = scene_encoder_latency(dev, model, sampler.summary().get("sm_mhz"))
     replan = None
     if rank == 0 and args.replan_ticks > 0:
         model.model.release_engine()
@@ -211,6 +214,8 @@ def run_ours(args):
             line["replan"] = replan
         if field is not None:
             line["field"] = field
+        if scene is not None:
+            line["scene_encoder"] = scene
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -254,6 +259,51 @@ def field_roofline(dev, sm_mhz):
                             "algorithmic_flops_per_pair": 3 * dim - 1}
     out["kernel"] = "nn_query_kernel (TMA-bulk staged cloud tiles, register-blocked waypoints, exact re-scan)"
     return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# Scene encoder: ObstacleEncoderSet on the 7 conditioning clouds of the headline workload (6 groups +
+# an unclustered one), i.e. what a moving conditioning cloud would put on the replan path every tick.
+# Algorithmic work = 2 x MACs of every Linear / attention product (0.70 GF per scene), on the FP32 CUDA cores.
+# ---------------------------------------------------------------------------------------------------
+def scene_encoder_latency(dev, model, sm_mhz):
+    from ramp_b200.testing import synthetic_cloud_2d
+    enc = model.model.scene_encoder
+    pts = torch.cat([synthetic_cloud_2d(seed=5, groups=G), torch.rand(1, 6, 64, 2) * 2 - 1]).to(dev)
+    S = pts.shape[0]
+    for _ in range(3):
+        enc(pts)
+    reps = 20
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        enc(pts)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    tok, hid = 384, 64
+    per_block = 2 * tok * hid * 3 * hid + 2 * 2 * tok * tok * hid + 2 * tok * hid * hid + 2 * 2 * tok * hid * 4 * hid
+    flops = S * (9 * per_block + 2 * tok * 3 * hid * hid + 2 * tok * 2 * hid)
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    peak = sms * 128 * 2 * (sm_mhz or 1965) * 1e6 / 1e12
+    cpu_ms = 1e3 * _cpu_scene_encoder(pts.cpu())
+    return {"scenes": S, "ms": ms, "launches": 8, "algorithmic_gflop": flops / 1e9,
+            "achieved_tflops": flops / (ms * 1e-3) / 1e12, "fp32_peak_tflops": peak,
+            "frac": flops / (ms * 1e-3) / 1e12 / peak, "cpu_port_ms": cpu_ms,
+            "kernel": "se2d_embed / se2d_qkv / se2d_block / se2d_pool (csrc/scene_enc.cu)"}
+
+
+def _cpu_scene_encoder(pts):
+    from oracle import ramp_oracle as O
+    from ramp_b200.testing import synthetic_state_dict
+    from ramp_b200.diffusion import StaticGaussianDiffusionModel
+    from ramp_b200.unet import TemporalUnetInference
+    net = TemporalUnetInference(n_support_points=H, state_dim=D)
+    sd = synthetic_state_dict(StaticGaussianDiffusionModel(model=net, n_diffusion_steps=T, predict_epsilon=True), 0)
+    t0 = time.perf_counter()
+    O.scene_encoder_2d(sd, pts)
+    return time.perf_counter() - t0
 
 
 # ---------------------------------------------------------------------------------------------------

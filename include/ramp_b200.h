@@ -135,6 +135,20 @@ int ramp_cost_terms(const float* x, int B, int H, int D, int dim, const float* d
 int ramp_select_best(const float* terms, int n, float w_smooth, float w_len, int normalize, float* out8,
                      float* costs_out, void* stream);
 
+/* ---- scene encoder, 2-D: ObstacleEncoderSet.forward -----------------------------------------------
+ * Replaces mpd/models/diffusion_models/obstacle_encoder.py:52-152 (ObstaclePositionalEncoding, SetAttention,
+ * SetTransformerBlock, ObstacleEncoderSet): pts [n_scenes, 6, 64, 2] -> out [n_scenes, 320], fp32, eval mode.
+ * params = ONE flat fp32 device buffer holding the module's state-dict tensors ([out, in] row-major, as stored)
+ * concatenated in the order ramp_scene2d_param_name(0 .. count-1) (names are the keys under "scene_encoder.",
+ * e.g. "set_transformers.1.2.attn.qkv.weight"; "pos_encoder.div_term" is the registered buffer).
+ * workspace: ramp_scene2d_workspace_floats(n_scenes) floats of caller scratch. */
+int ramp_scene2d_param_count(void);
+const char* ramp_scene2d_param_name(int i);
+size_t ramp_scene2d_param_numel(int i);
+size_t ramp_scene2d_param_floats(void);
+size_t ramp_scene2d_workspace_floats(int n_scenes);
+int ramp_scene2d_encode(const float* params, const float* pts, int n_scenes, float* workspace, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

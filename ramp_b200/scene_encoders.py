@@ -1,21 +1,25 @@
 """Scene encoders (point cloud -> conditioning latent).
 
-Cached precompute, evaluated once per distinct scene and never inside the diffusion loop
-(reference: UnetInference.py:146-156 caches the encoder output).  They stay as PyTorch modules
-on the model's device; the per-step hot path is CUDA only.
-Parameter names and shapes match the reference so its checkpoints load unchanged:
-  2-D: mpd/models/diffusion_models/obstacle_encoder.py:94-152  (ObstacleEncoderSet)
-  3-D: mpd/models/diffusion_models/obstacle_encoder3d.py:55-94 (ObstacleEncoder)
+Evaluated once per distinct scene and cached (reference: UnetInference.py:146-156), or every tick when the
+conditioning cloud moves.  The modules below only HOLD the parameters, under the reference's names
+and shapes so its checkpoints load unchanged:
+  2-D: mpd/models/diffusion_models/obstacle_encoder.py:94-152  (ObstacleEncoderSet) -> csrc/scene_enc.cu through
+       ramp_scene2d_encode (8 launches, FP32); CUDA tensors only, no CPU path
+  3-D: mpd/models/diffusion_models/obstacle_encoder3d.py:55-94 (ObstacleEncoder) -> PyTorch module on the model's
+       device (0.03 GF per scene)
 """
+import ctypes
 import math
 
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ._lib import RampError, check, lib, ptr, stream_ptr
+
 
 class _SetAttention(nn.Module):
-    """4-head attention over set tokens; names ``qkv`` (no bias) / ``proj`` (obstacle_encoder.py:6-32)."""
+    """Parameters of the 4-head set attention: ``qkv`` (no bias) / ``proj`` (obstacle_encoder.py:6-32)."""
 
     def __init__(self, dim, heads=4):
         super().__init__()
@@ -23,15 +27,9 @@ class _SetAttention(nn.Module):
         self.qkv = nn.Linear(dim, 3 * dim, bias=False)
         self.proj = nn.Linear(dim, dim)
 
-    def forward(self, x):
-        S, n, c = x.shape
-        q, k, v = self.qkv(x).view(S, n, 3, self.heads, c // self.heads).permute(2, 0, 3, 1, 4)
-        o = F.scaled_dot_product_attention(q, k, v)  # scale = head_dim ** -0.5
-        return self.proj(o.transpose(1, 2).reshape(S, n, c))
-
 
 class _SetBlock(nn.Module):
-    """Pre-norm transformer block; ``mlp`` indices 0 and 3 hold the linears (obstacle_encoder.py:34-50)."""
+    """Parameters of a pre-norm transformer block; ``mlp`` indices 0 and 3 hold the linears (obstacle_encoder.py:34-50)."""
 
     def __init__(self, dim):
         super().__init__()
@@ -40,29 +38,13 @@ class _SetBlock(nn.Module):
         self.norm2 = nn.LayerNorm(dim)
         self.mlp = nn.Sequential(nn.Linear(dim, 4 * dim), nn.GELU(), nn.Identity(), nn.Linear(4 * dim, dim))
 
-    def forward(self, x):
-        x = x + self.attn(self.norm1(x))
-        return x + self.mlp(self.norm2(x))
-
 
 class _CentrePE(nn.Module):
-    """Sinusoidal code of obstacle centres and of max-normalised offsets (obstacle_encoder.py:52-92)."""
+    """``div_term`` buffer of the sinusoidal code of obstacle centres / max-normalised offsets (obstacle_encoder.py:52-92)."""
 
     def __init__(self, d_model):
         super().__init__()
         self.register_buffer("div_term", torch.exp(torch.arange(0, d_model, 2) * -(math.log(10000.0) / d_model)))
-
-    def _code(self, v):
-        s = torch.sin(v[..., 0:1] * self.div_term) + torch.sin(v[..., 1:2] * self.div_term)
-        c = torch.cos(v[..., 0:1] * self.div_term) + torch.cos(v[..., 1:2] * self.div_term)
-        return torch.stack([s, c], dim=-1).flatten(-2)  # even slots = sin sum, odd slots = cos sum
-
-    def forward(self, pts):
-        centres = pts.mean(dim=2)
-        rel = pts - centres.unsqueeze(2)
-        peak = rel.abs().flatten(2).amax(dim=-1)
-        rel = rel / (peak[..., None, None] + 1e-8)
-        return self._code(centres), self._code(rel)
 
 
 class ObstacleEncoderSet(nn.Module):
@@ -81,14 +63,41 @@ class ObstacleEncoderSet(nn.Module):
         self.poolings = nn.ModuleList(
             [nn.Sequential(nn.Linear(hidden_dim, d), nn.GELU(), nn.Linear(d, d)) for d in output_dims])
 
+    def _flat_params(self):
+        """The state-dict tensors concatenated in the C ABI's order (rebuilt when a parameter changed or moved)."""
+        L = lib()
+        L.ramp_scene2d_param_name.restype = ctypes.c_char_p
+        L.ramp_scene2d_param_numel.restype = ctypes.c_size_t
+        sd = dict(self.state_dict())
+        key = tuple((t.data_ptr(), t._version) for t in sd.values())
+        if getattr(self, "_flat_key", None) != key:
+            parts = []
+            for i in range(L.ramp_scene2d_param_count()):
+                name = L.ramp_scene2d_param_name(i).decode()
+                t = sd[name]
+                if t.numel() != L.ramp_scene2d_param_numel(i):
+                    raise RampError("scene encoder parameter %s has %d elements, expected %d"
+                                    % (name, t.numel(), L.ramp_scene2d_param_numel(i)))
+                parts.append(t.detach().reshape(-1).to(torch.float32))
+            self._flat = torch.cat(parts).contiguous()
+            self._flat_key = key
+        return self._flat
+
     def forward(self, pts):
+        if not pts.is_cuda:
+            raise RampError("ObstacleEncoderSet runs on CUDA tensors only (csrc/scene_enc.cu); there is no CPU path")
+        if tuple(pts.shape[1:]) != (self.num_obstacles, self.num_points, 2) or self.num_obstacles != 6 \
+                or self.num_points != 64:
+            raise RampError("ObstacleEncoderSet is hard-wired to clouds [S, 6, 64, 2] (obstacle_encoder.py:95,132-134)")
+        L = lib()
+        L.ramp_scene2d_workspace_floats.restype = ctypes.c_size_t
         S = pts.shape[0]
-        pe_obs, pe_rel = self.pos_encoder(pts)
-        emb = self.point_embedding(pts)
-        tok = torch.cat([emb, pe_obs.unsqueeze(2).expand(-1, -1, self.num_points, -1), pe_rel], dim=-1)
-        tok = self.combined_encoder(tok).reshape(S, self.num_obstacles * self.num_points, -1)
-        return torch.cat([pool(stack(tok).mean(dim=1)) for stack, pool in zip(self.set_transformers, self.poolings)],
-                         dim=-1)
+        pts = pts.detach().to(torch.float32).contiguous()
+        flat = self._flat_params()
+        ws = torch.empty(max(1, L.ramp_scene2d_workspace_floats(S)), device=pts.device)
+        out = torch.empty(S, 320, device=pts.device)
+        check(L.ramp_scene2d_encode(ptr(flat), ptr(pts), S, ptr(ws), ptr(out), stream_ptr()), "ramp_scene2d_encode")
+        return out
 
 
 class _PointNet(nn.Module):
