@@ -149,6 +149,18 @@ size_t ramp_scene2d_param_floats(void);
 size_t ramp_scene2d_workspace_floats(int n_scenes);
 int ramp_scene2d_encode(const float* params, const float* pts, int n_scenes, float* workspace, float* out, void* stream);
 
+/* ---- scene encoder, 3-D: ObstacleEncoder.forward (eval mode) -----------------------------------------
+ * Replaces mpd/models/diffusion_models/obstacle_encoder3d.py:5-94 (PointNetEncoder with running-stat BatchNorm,
+ * SetTransformerBlock on nn.MultiheadAttention, ObstacleEncoder): pts [n_scenes, n_obs, n_pts, 3] -> out
+ * [n_scenes, 256]; 1 <= n_obs <= 32, n_pts >= 1.  params / names / workspace as for the 2-D encoder. */
+int ramp_scene3d_param_count(void);
+const char* ramp_scene3d_param_name(int i);
+size_t ramp_scene3d_param_numel(int i);
+size_t ramp_scene3d_param_floats(void);
+size_t ramp_scene3d_workspace_floats(int n_scenes, int n_obs);
+int ramp_scene3d_encode(const float* params, const float* pts, int n_scenes, int n_obs, int n_pts, float* workspace,
+                        float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -390,6 +390,307 @@ __global__ void __launch_bounds__(256) se2d_pool_kernel(SePoolArgs a) {
   }
 }
 
+
+// =====================================================================================================================
+// 3-D: ObstacleEncoder (mpd/models/diffusion_models/obstacle_encoder3d.py:5-94): per-obstacle PointNet (1x1 convs
+// 3 -> 64 -> 256, eval-mode BatchNorm, SELU, max over points), two nn.MultiheadAttention blocks over the obstacles
+// (E = 256, 4 heads x 64, FFN 256 -> 512 -> 256 with SELU), Linear, max over obstacles, Linear - SELU - Linear.
+// Two launches: one CTA per (scene, obstacle) for the PointNet, one CTA per scene for everything after it (<= 32
+// obstacle tokens live in shared memory; every Linear streams its weights through a transposed 64-output tile).
+// =====================================================================================================================
+static constexpr int S3_E = 256, S3_FF = 512, S3_MAXT = 32;
+struct S3Block { size_t n1w, n1b, inw, inb, ow, ob, n2w, n2b, f1w, f1b, f2w, f2b; };
+struct Se3dLayout {
+  SeTable t;
+  size_t c1w, c1b, c2w, c2b, bn1w, bn1b, bn1m, bn1v, bn2w, bn2b, bn2m, bn2v, opw, opb, g0w, g0b, g2w, g2b;
+  S3Block blk[2];
+  Se3dLayout() {
+    auto A = [&](const std::string& n, size_t k) { size_t o = t.total; t.add(n, k); return o; };
+    c1w = A("point_processor.conv1.weight", 64 * 3); c1b = A("point_processor.conv1.bias", 64);
+    c2w = A("point_processor.conv2.weight", S3_E * 64); c2b = A("point_processor.conv2.bias", S3_E);
+    bn1w = A("point_processor.bn1.weight", 64); bn1b = A("point_processor.bn1.bias", 64);
+    bn1m = A("point_processor.bn1.running_mean", 64); bn1v = A("point_processor.bn1.running_var", 64);
+    bn2w = A("point_processor.bn2.weight", S3_E); bn2b = A("point_processor.bn2.bias", S3_E);
+    bn2m = A("point_processor.bn2.running_mean", S3_E); bn2v = A("point_processor.bn2.running_var", S3_E);
+    for (int b = 0; b < 2; ++b) {
+      const std::string q = "set_transformer_blocks." + std::to_string(b) + ".";
+      S3Block& o = blk[b];
+      o.n1w = A(q + "norm1.weight", S3_E); o.n1b = A(q + "norm1.bias", S3_E);
+      o.inw = A(q + "mha.in_proj_weight", 3 * S3_E * S3_E); o.inb = A(q + "mha.in_proj_bias", 3 * S3_E);
+      o.ow = A(q + "mha.out_proj.weight", S3_E * S3_E); o.ob = A(q + "mha.out_proj.bias", S3_E);
+      o.n2w = A(q + "norm2.weight", S3_E); o.n2b = A(q + "norm2.bias", S3_E);
+      o.f1w = A(q + "ffn.0.weight", S3_FF * S3_E); o.f1b = A(q + "ffn.0.bias", S3_FF);
+      o.f2w = A(q + "ffn.3.weight", S3_E * S3_FF); o.f2b = A(q + "ffn.3.bias", S3_E);
+    }
+    opw = A("output_proj.weight", S3_E * S3_E); opb = A("output_proj.bias", S3_E);
+    g0w = A("global_pooling.0.weight", S3_E * S3_E); g0b = A("global_pooling.0.bias", S3_E);
+    g2w = A("global_pooling.2.weight", S3_E * S3_E); g2b = A("global_pooling.2.bias", S3_E);
+  }
+};
+static const Se3dLayout& se3d() { static Se3dLayout l; return l; }
+
+__device__ __forceinline__ float se_selu(float x) {
+  return 1.0507009873554805f * (x > 0.f ? x : 1.6732632423543772f * expm1f(x));
+}
+
+// ---- PointNet: one CTA per (scene, obstacle) -----------------------------------------------------------------------
+struct S3PointArgs { const float* prm; const float* pts; float* x0; int n_pts; size_t c1w, c1b, c2w, c2b, bn1w, bn1b, bn1m, bn1v, bn2w, bn2b, bn2m, bn2v; };
+__global__ void __launch_bounds__(256) se3d_pointnet_kernel(S3PointArgs a) {
+  extern __shared__ float sm[];
+  float* sW = sm;                                  // conv2 weight transposed [64][257]
+  float* sH = sW + 64 * 257;                       // [8 warps][4 points][64]
+  float* sMax = sH + 8 * 4 * 64;                   // [8 warps][256]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float* P = a.prm;
+  se_stage_t(sW, P + a.c2w, S3_E, 64);
+  __syncthreads();
+  const float* pts = a.pts + (size_t)blockIdx.x * a.n_pts * 3;
+  // eval-mode BatchNorm folded into scale / shift per channel
+  float s1[2], t1[2], s2[8], t2[8], cb2[8], mx[8];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int c = lane + 32 * j;
+    s1[j] = P[a.bn1w + c] * rsqrtf(P[a.bn1v + c] + 1e-5f);
+    t1[j] = P[a.bn1b + c] - P[a.bn1m + c] * s1[j];
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = lane + 32 * j;
+    s2[j] = P[a.bn2w + c] * rsqrtf(P[a.bn2v + c] + 1e-5f);
+    t2[j] = P[a.bn2b + c] - P[a.bn2m + c] * s2[j];
+    cb2[j] = P[a.c2b + c];
+    mx[j] = -INFINITY;
+  }
+  float* h = sH + warp * 4 * 64;
+  for (int p0 = warp * 4; p0 < a.n_pts; p0 += 32) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int p = min(p0 + t, a.n_pts - 1);      // a repeated point does not change the max
+      const float x = pts[3 * p], y = pts[3 * p + 1], z = pts[3 * p + 2];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int c = lane + 32 * j;
+        const float v = P[a.c1w + 3 * c] * x + P[a.c1w + 3 * c + 1] * y + P[a.c1w + 3 * c + 2] * z + P[a.c1b + c];
+        h[t * 64 + c] = se_selu(v * s1[j] + t1[j]);
+      }
+    }
+    __syncwarp();
+    float acc[4][8];
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[t][j] = cb2[j];
+#pragma unroll 2
+    for (int k = 0; k < 64; ++k) {
+      float w[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = sW[k * 257 + lane + 32 * j];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float v = h[t * 64 + k];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[t][j] = fmaf(v, w[j], acc[t][j]);
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) mx[j] = fmaxf(mx[j], se_selu(acc[t][j] * s2[j] + t2[j]));
+    __syncwarp();
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sMax[warp * 256 + lane + 32 * j] = mx[j];
+  __syncthreads();
+  {
+    float m = sMax[threadIdx.x];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) m = fmaxf(m, sMax[w * 256 + threadIdx.x]);
+    a.x0[(size_t)blockIdx.x * S3_E + threadIdx.x] = m;
+  }
+}
+
+// ---- everything after the PointNet: one CTA per scene --------------------------------------------------------------
+struct S3SceneArgs { const float* prm; const float* x0; float* out; int n_obs; S3Block blk[2]; size_t opw, opb, g0w, g0b, g2w, g2b; };
+// acc[t][j] += sum_k in[4 warp + t][k] * W[n0 + lane + 32 j][k], k < K (chunks of 256 staged transposed in sW)
+__device__ __forceinline__ void s3_linear_tile(const float* sIn, int ldIn, const float* __restrict__ W, int K, int n0, float* sW,
+                                               float (&acc)[4][2]) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int kc = 0; kc < K; kc += 256) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 64 * 256; i += 256) {
+      const int n = i >> 8, k = i & 255;
+      sW[k * 65 + n] = __ldg(W + (size_t)(n0 + n) * K + kc + k);
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int k = 0; k < 256; ++k) {
+      const float w0 = sW[k * 65 + lane], w1 = sW[k * 65 + lane + 32];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float v = sIn[(warp * 4 + t) * ldIn + kc + k];
+        acc[t][0] = fmaf(v, w0, acc[t][0]);
+        acc[t][1] = fmaf(v, w1, acc[t][1]);
+      }
+    }
+  }
+}
+// LayerNorm over 256 channels of token `tok` (one warp), eps 1e-5
+__device__ __forceinline__ void s3_ln_token(const float* x, float* y, const float* __restrict__ w, const float* __restrict__ b, int lane) {
+  float v[8], s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { v[j] = x[lane + 32 * j]; s += v[j]; }
+  const float mean = se_warp_sum(s) * (1.f / 256.f);
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { v[j] -= mean; q = fmaf(v[j], v[j], q); }
+  const float r = rsqrtf(se_warp_sum(q) * (1.f / 256.f) + 1e-5f);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) y[lane + 32 * j] = v[j] * r * w[lane + 32 * j] + b[lane + 32 * j];
+}
+__global__ void __launch_bounds__(256) se3d_scene_kernel(S3SceneArgs a) {
+  extern __shared__ float sm[];
+  float* sX = sm;                                  // [32][256] residual stream
+  float* sA = sX + 32 * 256;                       // [32][256] LayerNorm output / attention output
+  float* sB = sA + 32 * 256;                       // [32][768] qkv, or [32][512] FFN hidden, or [32][256] projected tokens
+  float* sW = sB + 32 * 768;                       // [256][65] weight tile
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int T = a.n_obs;
+  const float* P = a.prm;
+  for (int i = threadIdx.x; i < 32 * 256; i += 256) {
+    const int t = i >> 8;
+    sX[i] = t < T ? a.x0[((size_t)blockIdx.x * T + t) * S3_E + (i & 255)] : 0.f;
+    sA[i] = 0.f;
+  }
+  __syncthreads();
+  for (int b = 0; b < 2; ++b) {
+    const S3Block& o = a.blk[b];
+    for (int t = warp; t < T; t += 8) s3_ln_token(sX + t * 256, sA + t * 256, P + o.n1w, P + o.n1b, lane);
+    // qkv = in_proj(a)
+    for (int n0 = 0; n0 < 3 * S3_E; n0 += 64) {
+      float acc[4][2];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { acc[t][0] = P[o.inb + n0 + lane]; acc[t][1] = P[o.inb + n0 + lane + 32]; }
+      s3_linear_tile(sA, 256, P + o.inw, S3_E, n0, sW, acc);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { sB[(warp * 4 + t) * 768 + n0 + lane] = acc[t][0]; sB[(warp * 4 + t) * 768 + n0 + lane + 32] = acc[t][1]; }
+    }
+    __syncthreads();
+    // attention: thread = (head, query), 4 x 32 threads; keys / values broadcast from shared memory
+    if (threadIdx.x < 128) {
+      const int h = threadIdx.x >> 5, tq = lane;
+      float q[64], p[S3_MAXT], out[64];
+#pragma unroll
+      for (int d = 0; d < 64; ++d) q[d] = sB[tq * 768 + h * 64 + d] * 0.125f;
+      float m = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < S3_MAXT; ++j) {
+        float s = -INFINITY;
+        if (j < T) {
+          s = 0.f;
+          const float4* kr = reinterpret_cast<const float4*>(sB + j * 768 + 256 + h * 64);
+#pragma unroll
+          for (int d4 = 0; d4 < 16; ++d4) {
+            const float4 kk = kr[d4];
+            s = fmaf(q[4 * d4], kk.x, s); s = fmaf(q[4 * d4 + 1], kk.y, s);
+            s = fmaf(q[4 * d4 + 2], kk.z, s); s = fmaf(q[4 * d4 + 3], kk.w, s);
+          }
+        }
+        p[j] = s; m = fmaxf(m, s);
+      }
+      float l = 0.f;
+#pragma unroll
+      for (int j = 0; j < S3_MAXT; ++j) { p[j] = j < T ? expf(p[j] - m) : 0.f; l += p[j]; }
+      const float invl = 1.f / l;
+#pragma unroll
+      for (int d = 0; d < 64; ++d) out[d] = 0.f;
+#pragma unroll
+      for (int j = 0; j < S3_MAXT; ++j) {
+        if (j < T) {
+          const float4* vr = reinterpret_cast<const float4*>(sB + j * 768 + 512 + h * 64);
+          const float pj = p[j] * invl;
+#pragma unroll
+          for (int d4 = 0; d4 < 16; ++d4) {
+            const float4 vv = vr[d4];
+            out[4 * d4] = fmaf(pj, vv.x, out[4 * d4]); out[4 * d4 + 1] = fmaf(pj, vv.y, out[4 * d4 + 1]);
+            out[4 * d4 + 2] = fmaf(pj, vv.z, out[4 * d4 + 2]); out[4 * d4 + 3] = fmaf(pj, vv.w, out[4 * d4 + 3]);
+          }
+        }
+      }
+      if (tq < T)
+#pragma unroll
+        for (int d = 0; d < 64; ++d) sA[tq * 256 + h * 64 + d] = out[d];
+    }
+    __syncthreads();
+    // x += out_proj(attention)
+    for (int n0 = 0; n0 < S3_E; n0 += 64) {
+      float acc[4][2];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { acc[t][0] = P[o.ob + n0 + lane]; acc[t][1] = P[o.ob + n0 + lane + 32]; }
+      s3_linear_tile(sA, 256, P + o.ow, S3_E, n0, sW, acc);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { sX[(warp * 4 + t) * 256 + n0 + lane] += acc[t][0]; sX[(warp * 4 + t) * 256 + n0 + lane + 32] += acc[t][1]; }
+    }
+    __syncthreads();
+    for (int t = warp; t < T; t += 8) s3_ln_token(sX + t * 256, sA + t * 256, P + o.n2w, P + o.n2b, lane);
+    // hidden = SELU(ffn.0(a))
+    for (int n0 = 0; n0 < S3_FF; n0 += 64) {
+      float acc[4][2];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { acc[t][0] = P[o.f1b + n0 + lane]; acc[t][1] = P[o.f1b + n0 + lane + 32]; }
+      s3_linear_tile(sA, 256, P + o.f1w, S3_E, n0, sW, acc);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        sB[(warp * 4 + t) * 768 + n0 + lane] = se_selu(acc[t][0]);
+        sB[(warp * 4 + t) * 768 + n0 + lane + 32] = se_selu(acc[t][1]);
+      }
+    }
+    // x += ffn.3(hidden)
+    for (int n0 = 0; n0 < S3_E; n0 += 64) {
+      float acc[4][2];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { acc[t][0] = P[o.f2b + n0 + lane]; acc[t][1] = P[o.f2b + n0 + lane + 32]; }
+      s3_linear_tile(sB, 768, P + o.f2w, S3_FF, n0, sW, acc);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { sX[(warp * 4 + t) * 256 + n0 + lane] += acc[t][0]; sX[(warp * 4 + t) * 256 + n0 + lane + 32] += acc[t][1]; }
+    }
+    __syncthreads();
+  }
+  // output_proj, then max over the obstacles
+  for (int n0 = 0; n0 < S3_E; n0 += 64) {
+    float acc[4][2];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { acc[t][0] = P[a.opb + n0 + lane]; acc[t][1] = P[a.opb + n0 + lane + 32]; }
+    s3_linear_tile(sX, 256, P + a.opw, S3_E, n0, sW, acc);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { sB[(warp * 4 + t) * 768 + n0 + lane] = acc[t][0]; sB[(warp * 4 + t) * 768 + n0 + lane + 32] = acc[t][1]; }
+  }
+  __syncthreads();
+  float* vec = sA;                                 // [256] pooled, [256..511] hidden
+  {
+    float m = -INFINITY;
+    for (int t = 0; t < T; ++t) m = fmaxf(m, sB[t * 768 + threadIdx.x]);
+    vec[threadIdx.x] = m;
+  }
+  __syncthreads();
+  // global_pooling: Linear - SELU - Linear; warp-cooperative mat-vec (lanes over k)
+  for (int stage = 0; stage < 2; ++stage) {
+    const float* W = P + (stage == 0 ? a.g0w : a.g2w);
+    const float* B = P + (stage == 0 ? a.g0b : a.g2b);
+    const float* in = vec + stage * 256;
+    for (int n = warp; n < S3_E; n += 8) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s = fmaf(in[lane + 32 * j], __ldg(W + (size_t)n * S3_E + lane + 32 * j), s);
+      s = se_warp_sum(s) + B[n];
+      if (lane == 0) {
+        if (stage == 0) vec[256 + n] = se_selu(s);
+        else a.out[(size_t)blockIdx.x * S3_E + n] = s;
+      }
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace ramp
 
 // ---- C ABI ---------------------------------------------------------------------------------------------------------
@@ -453,6 +754,45 @@ int ramp_scene2d_encode(const float* params, const float* pts, int n_scenes, flo
     se2d_pool_kernel<<<n_scenes * SE_STACKS, 256, 0, s>>>(pa);
     RAMP_LAUNCH_OK();
   }
+  return 0;
+}
+
+int ramp_scene3d_param_count(void) { return (int)se3d().t.p.size(); }
+const char* ramp_scene3d_param_name(int i) {
+  const auto& p = se3d().t.p;
+  return (i >= 0 && i < (int)p.size()) ? p[i].name.c_str() : nullptr;
+}
+size_t ramp_scene3d_param_numel(int i) {
+  const auto& p = se3d().t.p;
+  return (i >= 0 && i < (int)p.size()) ? p[i].numel : 0;
+}
+size_t ramp_scene3d_param_floats(void) { return se3d().t.total; }
+size_t ramp_scene3d_workspace_floats(int n_scenes, int n_obs) {
+  return (size_t)(n_scenes > 0 ? n_scenes : 0) * (n_obs > 0 ? n_obs : 0) * S3_E;
+}
+
+int ramp_scene3d_encode(const float* params, const float* pts, int n_scenes, int n_obs, int n_pts, float* workspace, float* out,
+                        void* stream) {
+  if (n_scenes == 0) return 0;
+  RAMP_CHECK(params && pts && workspace && out, "ramp_scene3d_encode: null argument");
+  RAMP_CHECK(n_scenes > 0 && n_obs >= 1 && n_obs <= S3_MAXT && n_pts >= 1, "ramp_scene3d_encode: need 1..32 obstacles with >= 1 point");
+  const Se3dLayout& L = se3d();
+  cudaStream_t s = (cudaStream_t)stream;
+  static bool attr = false;
+  const int smem_p = (64 * 257 + 8 * 4 * 64 + 8 * 256) * 4, smem_s = (2 * 32 * 256 + 32 * 768 + 256 * 65) * 4;
+  if (!attr) {
+    RAMP_CUDA_OK(cudaFuncSetAttribute(se3d_pointnet_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_p));
+    RAMP_CUDA_OK(cudaFuncSetAttribute(se3d_scene_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_s));
+    attr = true;
+  }
+  S3PointArgs pa{params, pts, workspace, n_pts, L.c1w, L.c1b, L.c2w, L.c2b, L.bn1w, L.bn1b, L.bn1m, L.bn1v, L.bn2w, L.bn2b, L.bn2m, L.bn2v};
+  se3d_pointnet_kernel<<<n_scenes * n_obs, 256, smem_p, s>>>(pa);
+  RAMP_LAUNCH_OK();
+  S3SceneArgs sa{}; sa.prm = params; sa.x0 = workspace; sa.out = out; sa.n_obs = n_obs;
+  sa.blk[0] = L.blk[0]; sa.blk[1] = L.blk[1];
+  sa.opw = L.opw; sa.opb = L.opb; sa.g0w = L.g0w; sa.g0b = L.g0b; sa.g2w = L.g2w; sa.g2b = L.g2b;
+  se3d_scene_kernel<<<n_scenes, 256, smem_s, s>>>(sa);
+  RAMP_LAUNCH_OK();
   return 0;
 }
 

@@ -5,17 +5,38 @@ conditioning cloud moves.  The modules below only HOLD the para
 and shapes so its checkpoints load unchanged:
   2-D: mpd/models/diffusion_models/obstacle_encoder.py:94-152  (ObstacleEncoderSet) -> csrc/scene_enc.cu through
        ramp_scene2d_encode (8 launches, FP32); CUDA tensors only, no CPU path
-  3-D: mpd/models/diffusion_models/obstacle_encoder3d.py:55-94 (ObstacleEncoder) -> PyTorch module on the model's
-       device (0.03 GF per scene)
+  3-D: mpd/models/diffusion_models/obstacle_encoder3d.py:55-94 (ObstacleEncoder) -> ramp_scene3d_encode (2 launches)
 """
 import ctypes
 import math
 
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
 from ._lib import RampError, check, lib, ptr, stream_ptr
+
+
+def _flat_params(module, which):
+    """The module's state-dict tensors concatenated in the C ABI's order (rebuilt when a tensor changed or moved)."""
+    L = lib()
+    count = getattr(L, "ramp_scene%s_param_count" % which)
+    name_of = getattr(L, "ramp_scene%s_param_name" % which)
+    numel_of = getattr(L, "ramp_scene%s_param_numel" % which)
+    name_of.restype = ctypes.c_char_p
+    numel_of.restype = ctypes.c_size_t
+    sd = dict(module.state_dict())
+    key = tuple((t.data_ptr(), t._version) for t in sd.values())
+    if getattr(module, "_flat_key", None) != key:
+        parts = []
+        for i in range(count()):
+            name = name_of(i).decode()
+            t = sd[name]
+            if t.numel() != numel_of(i):
+                raise RampError("scene encoder parameter %s has %d elements, expected %d" % (name, t.numel(), numel_of(i)))
+            parts.append(t.detach().reshape(-1).to(torch.float32))
+        module._flat = torch.cat(parts).contiguous()
+        module._flat_key = key
+    return module._flat
 
 
 class _SetAttention(nn.Module):
@@ -63,26 +84,6 @@ class ObstacleEncoderSet(nn.Module):
         self.poolings = nn.ModuleList(
             [nn.Sequential(nn.Linear(hidden_dim, d), nn.GELU(), nn.Linear(d, d)) for d in output_dims])
 
-    def _flat_params(self):
-        """The state-dict tensors concatenated in the C ABI's order (rebuilt when a parameter changed or moved)."""
-        L = lib()
-        L.ramp_scene2d_param_name.restype = ctypes.c_char_p
-        L.ramp_scene2d_param_numel.restype = ctypes.c_size_t
-        sd = dict(self.state_dict())
-        key = tuple((t.data_ptr(), t._version) for t in sd.values())
-        if getattr(self, "_flat_key", None) != key:
-            parts = []
-            for i in range(L.ramp_scene2d_param_count()):
-                name = L.ramp_scene2d_param_name(i).decode()
-                t = sd[name]
-                if t.numel() != L.ramp_scene2d_param_numel(i):
-                    raise RampError("scene encoder parameter %s has %d elements, expected %d"
-                                    % (name, t.numel(), L.ramp_scene2d_param_numel(i)))
-                parts.append(t.detach().reshape(-1).to(torch.float32))
-            self._flat = torch.cat(parts).contiguous()
-            self._flat_key = key
-        return self._flat
-
     def forward(self, pts):
         if not pts.is_cuda:
             raise RampError("ObstacleEncoderSet runs on CUDA tensors only (csrc/scene_enc.cu); there is no CPU path")
@@ -93,7 +94,7 @@ class ObstacleEncoderSet(nn.Module):
         L.ramp_scene2d_workspace_floats.restype = ctypes.c_size_t
         S = pts.shape[0]
         pts = pts.detach().to(torch.float32).contiguous()
-        flat = self._flat_params()
+        flat = _flat_params(self, "2d")
         ws = torch.empty(max(1, L.ramp_scene2d_workspace_floats(S)), device=pts.device)
         out = torch.empty(S, 320, device=pts.device)
         check(L.ramp_scene2d_encode(ptr(flat), ptr(pts), S, ptr(ws), ptr(out), stream_ptr()), "ramp_scene2d_encode")
@@ -101,7 +102,7 @@ class ObstacleEncoderSet(nn.Module):
 
 
 class _PointNet(nn.Module):
-    """Shared 1x1 convs + eval-mode BatchNorm + SELU + max over points (obstacle_encoder3d.py:5-21)."""
+    """Parameters of the shared 1x1 convs + BatchNorm (obstacle_encoder3d.py:5-21)."""
 
     def __init__(self, input_dim, output_dim):
         super().__init__()
@@ -110,15 +111,9 @@ class _PointNet(nn.Module):
         self.bn1 = nn.BatchNorm1d(64)
         self.bn2 = nn.BatchNorm1d(output_dim)
 
-    def forward(self, x):  # [S*n_obs, n_pts, 3]
-        x = x.transpose(1, 2)
-        x = F.selu(self.bn1(self.conv1(x)))
-        x = F.selu(self.bn2(self.conv2(x)))
-        return x.amax(dim=2)
-
 
 class _ObstacleBlock(nn.Module):
-    """nn.MultiheadAttention block over obstacles (obstacle_encoder3d.py:23-53); ``ffn`` indices 0/3."""
+    """Parameters of the nn.MultiheadAttention block over obstacles (obstacle_encoder3d.py:23-53); ``ffn`` indices 0/3."""
 
     def __init__(self, dim, heads=4):
         super().__init__()
@@ -127,14 +122,9 @@ class _ObstacleBlock(nn.Module):
         self.norm1 = nn.LayerNorm(dim)
         self.norm2 = nn.LayerNorm(dim)
 
-    def forward(self, x):  # [S, n_obs, dim]
-        a = self.norm1(x).transpose(0, 1)
-        x = x + self.mha(a, a, a, need_weights=False)[0].transpose(0, 1)
-        return x + self.ffn(self.norm2(x))
-
 
 class ObstacleEncoder(nn.Module):
-    """[S, n_obs, n_pts, 3] -> [S, 256]."""
+    """[S, n_obs, n_pts, 3] -> [S, 256] (eval-mode semantics: BatchNorm running statistics, no dropout)."""
 
     def __init__(self, embedding_dim=256, point_dim=3, num_layers=2):
         super().__init__()
@@ -146,8 +136,19 @@ class ObstacleEncoder(nn.Module):
                                             nn.Linear(embedding_dim, embedding_dim))
 
     def forward(self, pts):
-        S, n_obs, n_pts, dim = pts.shape
-        x = self.point_processor(pts.reshape(-1, n_pts, dim)).view(S, n_obs, self.embedding_dim)
-        for blk in self.set_transformer_blocks:
-            x = blk(x)
-        return self.global_pooling(self.output_proj(x).amax(dim=1))
+        if not pts.is_cuda:
+            raise RampError("ObstacleEncoder runs on CUDA tensors only (csrc/scene_enc.cu); there is no CPU path")
+        if pts.dim() != 4 or pts.shape[-1] != 3 or self.embedding_dim != 256 or len(self.set_transformer_blocks) != 2:
+            raise RampError("ObstacleEncoder expects clouds [S, n_obs, n_pts, 3] and the reference's 256-wide, 2-block model")
+        S, n_obs, n_pts, _ = pts.shape
+        if not 1 <= n_obs <= 32:
+            raise RampError("ObstacleEncoder kernels hold at most 32 obstacles per scene (got %d)" % n_obs)
+        L = lib()
+        L.ramp_scene3d_workspace_floats.restype = ctypes.c_size_t
+        pts = pts.detach().to(torch.float32).contiguous()
+        flat = _flat_params(self, "3d")
+        ws = torch.empty(max(1, L.ramp_scene3d_workspace_floats(S, n_obs)), device=pts.device)
+        out = torch.empty(S, 256, device=pts.device)
+        check(L.ramp_scene3d_encode(ptr(flat), ptr(pts), S, n_obs, n_pts, ptr(ws), ptr(out), stream_ptr()),
+              "ramp_scene3d_encode")
+        return out
