@@ -161,6 +161,23 @@ size_t ramp_scene3d_workspace_floats(int n_scenes, int n_obs);
 int ramp_scene3d_encode(const float* params, const float* pts, int n_scenes, int n_obs, int n_pts, float* workspace,
                         float* out, void* stream);
 
+/* ---- evaluation metrics of the sampled batch (scripts/inference/core/metrics.py) ------------------------
+ * ramp_collision_intensity: Metrics.compute_collision_intensity (metrics.py:48-82): out[b] = fraction of the H
+ *     waypoints of trajectory b inside any axis-aligned box [centre - size/2, centre + size/2] (inclusive);
+ *     box_sizes is [n_boxes] (size_stride 1, square boxes) or [n_boxes, 2] (size_stride 2).
+ * ramp_path_sums: out[b] = sum_t |x[b,t+1,c0:c1] - x[b,t,c0:c1]|  (compute_path_length with columns 0:2,
+ *     compute_smoothness with the velocity columns; metrics.py:21-45).
+ * ramp_waypoint_variance: Metrics.compute_variance_waypoints (metrics.py:9-19) over n >= 2 trajectories:
+ *     out1[0] = sum_h var(triu(cdist(p_h, p_h), 1).view(-1) + eps), unbiased, population = all n*n entries.
+ *     workspace: ramp_waypoint_variance_workspace_bytes(n, H) bytes, 8-byte aligned.
+ * ramp_vector_stats: out3 = (mean, unbiased std, sum) of v[0..n)  (path-length mean / std, metrics.py:112-114). */
+int ramp_collision_intensity(const float* x, int B, int H, int D, const float* box_centers, const float* box_sizes,
+                             int size_stride, int n_boxes, float* out, void* stream);
+int ramp_path_sums(const float* x, int B, int H, int D, int c0, int c1, float* out, void* stream);
+size_t ramp_waypoint_variance_workspace_bytes(int n, int H);
+int ramp_waypoint_variance(const float* x, int n, int H, int D, void* workspace, float* out1, void* stream);
+int ramp_vector_stats(const float* v, int n, float* out3, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -588,3 +588,41 @@ def dynamic_tick_batch(sd, sch, T, scene_latent, x_clean, history, stepp, k, noi
         x = _pin_history(x, history, goal_row, zero_start_velocity=True)
     x[:, stepp + 1:stepp + 3] = smooth_segment(x[:, stepp], x[:, stepp + 2], 2)
     return x
+
+
+# --------------------------------------------------------------------------------------
+# evaluation metrics (scripts/inference/core/metrics.py)
+# --------------------------------------------------------------------------------------
+
+def metric_collision_intensity(x, centers, sizes):
+    """Metrics.compute_collision_intensity (metrics.py:48-82): fraction of waypoints inside any inclusive box."""
+    centers = torch.as_tensor(centers, dtype=torch.float32).reshape(-1, 2)
+    sizes = torch.as_tensor(sizes, dtype=torch.float32)
+    if sizes.dim() == 1:
+        sizes = sizes[:, None].repeat(1, 2)
+    lo, hi = centers - sizes / 2, centers + sizes / 2
+    p = x[:, :, None, :2]
+    inside = ((p >= lo) & (p <= hi)).all(dim=-1)
+    return inside.any(dim=-1).float().mean(dim=1)
+
+
+def metric_variance_waypoints(x, eps=1e-8):
+    """Metrics.compute_variance_waypoints (metrics.py:9-19), restated with exact fp64 pair distances: per horizon step the
+    unbiased variance over ALL n*n entries of triu(cdist, 1) + eps (zeros included), summed over the horizon."""
+    p = x[..., :2].double().permute(1, 0, 2)                       # [H, n, 2]
+    d = (p[:, :, None, :] - p[:, None, :, :]).norm(dim=-1)
+    d = torch.triu(d, diagonal=1).reshape(d.shape[0], -1) + eps
+    return d.var(dim=1).sum().float()
+
+
+def metric_success(x, ci, thr=0.01):
+    """Metrics.trajectory_success_and_metrics (metrics.py:84-126), scalar fields only."""
+    ok = ci <= thr
+    free = x[ok]
+    out = {"success": int(ok.any()), "collision_intensity": ci.mean().item() * 100, "n_free_trajectories": len(free),
+           "path_length": None, "path_length_std": None, "waypoint_variance": None}
+    if len(free) > 0:
+        pl = path_length(free, 2)
+        out["path_length"], out["path_length_std"] = pl.mean().item(), pl.std().item()
+        out["waypoint_variance"] = 0.0 if len(free) == 1 else metric_variance_waypoints(free).item()
+    return out

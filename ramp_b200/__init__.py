@@ -9,3 +9,4 @@ from .dynamic import DynamicGaussianDiffusionModel  # noqa: F401
 from .cost import compute_trajectory_costs, compute_collision_with_pointcloud, compute_path_length, compute_smoothness  # noqa: F401
 from .apf import ObstacleField, avoidance  # noqa: F401
 from .sample_functions import apply_hard_conditioning, ddpm_sample_fn, extract, guide_gradient_steps  # noqa: F401
+from .metrics import Metrics, DynamicMetrics  # noqa: F401

@@ -12,7 +12,7 @@ import importlib
 import sys
 import types
 
-from . import apf, apf_dynamic, cost, diffusion, dynamic, sample_functions, unet
+from . import apf, apf_dynamic, cost, diffusion, dynamic, metrics, sample_functions, unet
 
 _HOT = {
     "mpd.models": dict(
@@ -49,6 +49,8 @@ _HOT = {
         GaussianDiffusionModel3d=diffusion.GaussianDiffusionModel3d, make_timesteps=diffusion.make_timesteps),
     "mpd.models.diffusion_models.diffusion_model_dynamic": dict(
         DynamicGaussianDiffusionModel=dynamic.DynamicGaussianDiffusionModel, make_timesteps=diffusion.make_timesteps),
+    # `from core.metrics import Metrics` / `DynamicMetrics` (inference_static.py:16, inference_dynamic.py:17)
+    "core.metrics": dict(Metrics=metrics.Metrics, DynamicMetrics=metrics.DynamicMetrics),
 }
 
 

@@ -3,7 +3,7 @@ import sys
 
 
 def test_reference_imports_resolve_to_ramp_b200():
-    for k in [k for k in sys.modules if k == "mpd" or k.startswith("mpd.")]:
+    for k in [k for k in sys.modules if k == "mpd" or k.startswith("mpd.") or k == "core" or k.startswith("core.")]:
         del sys.modules[k]
     import ramp_b200
     import ramp_b200.compat as compat
@@ -21,6 +21,9 @@ def test_reference_imports_resolve_to_ramp_b200():
         assert getattr(mpd.models, cls) is getattr(ramp_b200, cls)     # get_model's lookup, train_loaders.py:11-25
     assert compute_trajectory_costs is ramp_b200.compute_trajectory_costs and ObstacleField is ramp_b200.ObstacleField
     assert callable(avoidance)
+    from core.metrics import DynamicMetrics, Metrics                                     # inference_static.py:16, inference_dynamic.py:17
+    import ramp_b200.metrics
+    assert Metrics is ramp_b200.metrics.Metrics and issubclass(DynamicMetrics, Metrics)
     # constructor contract of the scripts (inference_static.py:85-105): kwargs accepted, state-dict keys of the reference
     net = TemporalUnetInference(state_dim=4, n_support_points=64, unet_input_dim=32, dim_mults=UNET_DIM_MULTS[1])
     m = mpd.models.StaticGaussianDiffusionModel(model=net, variance_schedule='exponential', n_diffusion_steps=100,
@@ -31,4 +34,6 @@ def test_reference_imports_resolve_to_ramp_b200():
             "model.downs.0.3.transformer_blocks.1.attn2.to_k.weight", "model.final_conv.1.bias"} <= keys
     assert m.ddim_num_inference_steps == 8 and m.ddim is True
     for k in [k for k in sys.modules if k == "mpd" or k.startswith("mpd.")]:
+        del sys.modules[k]
+    for k in [k for k in sys.modules if k == "core" or k.startswith("core.")]:
         del sys.modules[k]
