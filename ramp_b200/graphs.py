@@ -72,16 +72,21 @@ class ReplanGraph:
     """Graph of one replan tick of DynamicGaussianDiffusionModel for tick index k (= number of executed states - 1).
 
     Static inputs (update in place, then `replay()`): `x_clean` [H, D] current plan, `history` [k+1, D] executed states,
-    `disc_points` [Pd, 2] + `disc_center` [2] pursuer cloud, and the cost cloud whose last Pd points are the disc.
+    `disc_points` [Pd, 2] + `disc_center` [2] pursuer cloud, the cost cloud whose last Pd points are the disc, and —
+    with `stream_conditioning` — `cloud`, the U-Net's conditioning cloud.
     Outputs (static): `batch` [B, H, D], `sel` [8] (ramp_select_best), `best` [H, D]."""
 
     def __init__(self, model, batch, horizon, k, obstacle_pts, static_points, disc_points, cost_static_points,
-                 collision_threshold=None):
+                 collision_threshold=None, stream_conditioning=False):
+        """stream_conditioning: re-run the scene encoder kernels on `cloud` inside the graph: update
+        the static `cloud` buffer in place before a replay and the tick is conditioned on the new scene."""
         self.model = model
         dev = model.betas.device
         B, H, D = batch, horizon, model.state_dim
         self.k = k
         self.cloud = obstacle_pts.to(dev).float().contiguous()
+        if stream_conditioning:
+            self.cloud = self.cloud.clone()               # a static buffer of its own: the caller writes new clouds into it
         self.x_clean = torch.zeros(H, D, device=dev)
         self.history = torch.zeros(k + 1, D, device=dev)
         self.disc_points = disc_points.to(dev).float().contiguous().clone()
@@ -122,6 +127,8 @@ class ReplanGraph:
                 p.val[0, H - 1] = self.x_clean[-1]
                 if zero_v:
                     p.val[0, 0, 2:] = 0.0
+            if stream_conditioning:
+                model._scene_sig = None                               # encode `cloud` again on this replay
             self._cost_disc.copy_(self.disc_points)
             self.field.dynamic_cloud.repack()
             self.cost_cloud.repack()

@@ -110,3 +110,43 @@ def test_run_inference_protocol(cuda):
         assert torch.allclose(chain[j + 1, 0, :j, :2], chain[j, 0, :j, :2], atol=1e-6)
     assert torch.allclose(chain[-1, 0, -1], torch.tensor([0.8, 0.8, 0.0, 0.0], device=cuda))
     assert 'obstacle_field' not in ctx          # run_inference works on a shallow copy of the context (:650)
+
+
+def test_replan_graph_streams_the_conditioning_cloud(cuda):
+    """ReplanGraph(stream_conditioning=True): after a replay the engine is conditioned on whatever the static `cloud`
+    buffer held at that replay (encoder kernels + scene constants are graph nodes), bit-equal to an eager re-encode."""
+    import numpy as np
+    from ramp_b200.apf_dynamic import generate_box_points, generate_sphere_points
+    from ramp_b200.graphs import ReplanGraph
+    from ramp_b200.testing import SyntheticPursuitDataset, pursuit_cloud_2d
+    m = _model(cuda)
+    ds = SyntheticPursuitDataset()
+    cloud_a = pursuit_cloud_2d(ds).to(cuda)
+    g0 = torch.Generator("cpu").manual_seed(2)
+    cloud_b = (cloud_a.cpu() + 0.05 * torch.randn(cloud_a.shape, generator=g0)).to(cuda)
+    np.random.seed(0)
+    boxes = ds.env.obj_fixed_list[0].fields[0]
+    static_pts = torch.from_numpy(np.vstack([generate_box_points(c, s, 64) for c, s in
+                                             zip(boxes.centers.numpy(), boxes.sizes.numpy())])).float()
+    disc = torch.from_numpy(generate_sphere_points(np.array([-0.35, -0.95]), 0.1, 64)).float()
+    H, k, B = 64, 2, 8
+    s = torch.linspace(0, 1, H)[:, None]
+    plan = torch.cat([-0.8 + 1.6 * s, -0.8 + 1.6 * s, torch.full((H, 2), 0.2)], dim=1).to(cuda)
+    g = ReplanGraph(m, B, H, k, cloud_a, static_pts, disc, static_pts, stream_conditioning=True)
+    g.x_clean.copy_(plan)
+    g.history.copy_(plan[:k + 1])
+    g.disc_center.copy_(torch.tensor([-0.35, -0.95]))
+    x = torch.randn(2 * B, H, 4, generator=torch.Generator("cpu").manual_seed(1)).to(cuda)
+    r2s = m._row_scenes(B, 1, cuda)
+    seen = []
+    for cl in (cloud_a, cloud_b):
+        g.cloud.copy_(cl)
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.isfinite(g.batch).all()
+        seen.append(m.model.energy_grad_rows(x, 10, r2s).clone())            # engine state left by the replay
+    assert not torch.equal(seen[0], seen[1])
+    for cl, got in zip((cloud_a, cloud_b), seen):
+        m._scene_sig = None
+        m._set_scenes(m._groups_and_weights(cl, False)[0])                  # eager re-encode
+        assert torch.equal(m.model.energy_grad_rows(x, 10, r2s), got)
