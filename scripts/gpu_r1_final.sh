@@ -2,7 +2,7 @@
 # Round-1 evidence run: GPU test suite, both bench arms, ncu launch list of the bench command, per-launch DRAM traffic
 # of every GEMM launch of one network call, and full captures of the dominant launches.
 mkdir -p gpurun_out
-O=gpurun_out/r1z
+O=gpurun_out/r1f
 timeout 600 python -m pytest tests -m gpu -q 2>&1 | tail -4 > ${O}_tests.log
 timeout 600 python bench.py > ${O}_bench.json 2> ${O}_bench.err
 timeout 600 python bench.py --impl reference > ${O}_bench_reference.json 2> ${O}_bench_reference.err
