@@ -208,7 +208,7 @@ def run_ours(args):
                          "class_ms": prof_ms,
                          "note": "parity mode issues 3 bf16 MMAs per product (hi*hi+hi*lo+lo*hi): ceiling = peak/3"},
         }
-        if args.cpu_sample > 0:
+        if args.cpu_sample > 0 and world == 1:
             line["cpu_baseline"] = cpu_baseline(sample_B=args.cpu_sample)
         if replan is not None:
             line["replan"] = replan
