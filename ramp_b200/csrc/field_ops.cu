@@ -11,6 +11,8 @@
 // re-derived exactly (direct form) for the winner.
 #include "../../include/ramp_b200.h"
 #include "common.cuh"
+#include <cstdio>
+#include <cstdlib>
 #include <cfloat>
 
 namespace ramp {
@@ -49,12 +51,13 @@ __device__ __forceinline__ float nn_key(const float4 p, float mx, float my, floa
   return fmaf(mx, p.x, k);
 }
 
-template <int DIM, int R>
+// R = waypoints per thread (register blocking), TILE = cloud points per shared-memory buffer (two buffers per CTA)
+template <int DIM, int R, int TILE>
 __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __restrict__ cloud4, int P, int Ppad,
                                                               const float* __restrict__ q, int Q, int qstride, float thr,
                                                               float* __restrict__ out_d, int* __restrict__ out_idx) {
   extern __shared__ __align__(128) unsigned char nn_smem[];
-  float4* tile = reinterpret_cast<float4*>(nn_smem);                       // 2 x NN_TILE
+  float4* tile = reinterpret_cast<float4*>(nn_smem);                       // 2 x TILE
   __shared__ __align__(8) unsigned long long bars[2];
   const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&bars[0]);
   const uint32_t tile0 = (uint32_t)__cvta_generic_to_shared(tile);
@@ -65,13 +68,13 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  const int ntiles = Ppad / NN_TILE;
+  const int ntiles = Ppad / TILE;
   auto issue = [&](int t) {
     const uint32_t bar = bar0 + 8 * (t & 1);
-    const uint32_t dst = tile0 + (t & 1) * NN_TILE * 16;
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(NN_TILE * 16) : "memory");
+    const uint32_t dst = tile0 + (t & 1) * TILE * 16;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(TILE * 16) : "memory");
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(cloud4 + (size_t)t * NN_TILE), "r"(NN_TILE * 16), "r"(bar) : "memory");
+                 ::"r"(dst), "l"(cloud4 + (size_t)t * TILE), "r"(TILE * 16), "r"(bar) : "memory");
   };
   if (tid == 0) issue(0);
 
@@ -91,8 +94,8 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
   for (int t = 0; t < ntiles; ++t) {
     if (tid == 0 && t + 1 < ntiles) issue(t + 1);
     nn_mbar_wait(bar0 + 8 * (t & 1), (t >> 1) & 1);
-    const float4* tp = tile + (t & 1) * NN_TILE;
-    for (int c = 0; c < NN_TILE / NN_CHUNK; ++c) {
+    const float4* tp = tile + (t & 1) * TILE;
+    for (int c = 0; c < TILE / NN_CHUNK; ++c) {
       float cm[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) cm[r] = FLT_MAX;
@@ -103,7 +106,7 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
         for (int r = 0; r < R; ++r)
           cm[r] = min3f(cm[r], nn_key<DIM>(pa, mx[r], my[r], mz[r]), nn_key<DIM>(pb, mx[r], my[r], mz[r]));
       }
-      const int gc = t * (NN_TILE / NN_CHUNK) + c;
+      const int gc = t * (TILE / NN_CHUNK) + c;
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         if (cm[r] < best[r]) { second[r] = best[r]; schunk[r] = bchunk[r]; best[r] = cm[r]; bchunk[r] = gc; }
@@ -354,15 +357,58 @@ __global__ void __launch_bounds__(1024) select_best_kernel(const float* __restri
 
 using namespace ramp;
 
-template <int DIM, int R>
+template <int DIM, int R, int TILE>
 static int nn_launch(const float4* c4, int P, int Ppad, const float* q, int Q, int qstride, float thr, float* od, int* oi,
                      cudaStream_t s) {
   static bool attr = false;
-  const int smem = 2 * NN_TILE * 16;
-  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(nn_query_kernel<DIM, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
+  const int smem = 2 * TILE * 16;
+  if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(nn_query_kernel<DIM, R, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
   const int per = NN_THREADS * R;
-  nn_query_kernel<DIM, R><<<(Q + per - 1) / per, NN_THREADS, smem, s>>>(c4, P, Ppad, q, Q, qstride, thr, od, oi);
+  nn_query_kernel<DIM, R, TILE><<<(Q + per - 1) / per, NN_THREADS, smem, s>>>(c4, P, Ppad, q, Q, qstride, thr, od, oi);
   RAMP_LAUNCH_OK();
+  return 0;
+}
+// dispatch over the instantiated (R, TILE) pairs
+template <int DIM>
+static int nn_dispatch(int R, int TILE, const float4* c4, int P, int Ppad, const float* q, int Q, int qstride, float thr,
+                       float* od, int* oi, cudaStream_t s) {
+#define RAMP_NN_CASE(r) \
+  case r: return TILE == 2048 ? nn_launch<DIM, r, 2048>(c4, P, Ppad, q, Q, qstride, thr, od, oi, s) \
+                              : nn_launch<DIM, r, 1024>(c4, P, Ppad, q, Q, qstride, thr, od, oi, s);
+  switch (R) {
+    RAMP_NN_CASE(1) RAMP_NN_CASE(2) RAMP_NN_CASE(4) RAMP_NN_CASE(6) RAMP_NN_CASE(8) RAMP_NN_CASE(10) RAMP_NN_CASE(12)
+  }
+#undef RAMP_NN_CASE
+  set_error("ramp_nn_query: unsupported register blocking");
+  return -2;
+}
+// The grid is one CTA per 128 R waypoints, each scanning the whole cloud, so an SM works through
+// ceil(CTAs / SMs) * R blocks of 128 waypoints.  The cost of one block depends on R: more waypoints per thread amortise
+// the shared-memory loads of a cloud point over more FFMAs, until register pressure costs occupancy (3-D: three
+// coordinates per waypoint).  Relative costs per block measured on B200 (8192 x 64 waypoints, 1 M points; R = 1, 2
+// extrapolated); the launch takes the R with the smallest ceil(CTAs / SMs) * R * cost[R].
+template <int DIM>
+static int nn_choose(int Q, int* R_out, int* TILE_out) {
+  static const int Rs[7] = {1, 2, 4, 6, 8, 10, 12};
+  static const double cost2[7] = {4.64, 3.17, 2.43, 2.20, 2.19, 1.97, 1.94};
+  static const double cost3[7] = {5.20, 3.55, 2.72, 3.07, 3.00, 3.46, 3.50};
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 148;
+  }
+  *TILE_out = 1024;                                   // 32 KB of buffers per CTA: up to 7 CTAs resident per SM
+  if (const char* v = getenv("RAMP_NN_FORCE")) {      // "R,TILE" - tuning knob
+    int r = 0, t = 0;
+    if (sscanf(v, "%d,%d", &r, &t) == 2) { *R_out = r; *TILE_out = t; return 0; }
+  }
+  double best = 1e300;
+  for (int ri = 0; ri < 7; ++ri) {
+    const long ctas = ((long)Q + NN_THREADS * Rs[ri] - 1) / (NN_THREADS * Rs[ri]);
+    const double t = (double)((ctas + sms - 1) / sms) * Rs[ri] * (DIM == 2 ? cost2[ri] : cost3[ri]);
+    if (t < best) { best = t; *R_out = Rs[ri]; }
+  }
   return 0;
 }
 
@@ -388,19 +434,13 @@ int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int
   const int Ppad = (int)ramp_cloud_packed_points(P);
   const float4* c4 = (const float4*)packed;
   cudaStream_t s = (cudaStream_t)stream;
-  // registers-per-thread blocking: as many waypoints per thread as still leaves >= 2 CTAs per SM
-  const long ctas8 = ((long)Q + NN_THREADS * 8 - 1) / (NN_THREADS * 8);
-  int R = ctas8 >= 296 ? 8 : (ctas8 * 2 >= 296 ? 4 : (ctas8 * 4 >= 296 ? 2 : 1));
+  int R = 1, TILE = 2048;
   if (dim == 2) {
-    if (R == 8) return nn_launch<2, 8>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
-    if (R == 4) return nn_launch<2, 4>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
-    if (R == 2) return nn_launch<2, 2>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
-    return nn_launch<2, 1>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+    if (nn_choose<2>(Q, &R, &TILE)) return -1;
+    return nn_dispatch<2>(R, TILE, c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
   }
-  if (R == 8) return nn_launch<3, 8>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
-  if (R == 4) return nn_launch<3, 4>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
-  if (R == 2) return nn_launch<3, 2>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
-  return nn_launch<3, 1>(c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+  if (nn_choose<3>(Q, &R, &TILE)) return -1;
+  return nn_dispatch<3>(R, TILE, c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
 }
 
 int ramp_apf_static(const float* x, int B, int H, int D, int dim, const float* dist, const int32_t* idx,
