@@ -87,6 +87,27 @@ __device__ __forceinline__ void gn_group_reduce(const GnTile& t, const float (&a
   if (lane == 0) red[g] = s;
   __syncthreads();
 }
+// two quantities in one pass (part holds 2 x 512 slots)
+__device__ __forceinline__ void gn_group_reduce2(const GnTile& t, const float (&a)[2], const float (&b)[2], int L, int C,
+                                                 float* part, float* redA, float* redB) {
+  const int cg = C / 8, seg = cg >= 32 ? 8 : cg / 4, nl = cg >= 32 ? cg / 32 : 1;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    part[threadIdx.x + i * 256] = seg_sum(a[i], seg);
+    part[512 + threadIdx.x + i * 256] = seg_sum(b[i], seg);
+  }
+  __syncthreads();
+  const int g = threadIdx.x >> 5, lane = threadIdx.x & 31, n = L * nl;
+  float s = 0.f, u = 0.f;
+  for (int k = lane; k < n; k += 32) {
+    const int r = k / nl, j = k - r * nl, slot = (r * C + g * cg) / 4 + j * seg;
+    s += part[slot]; u += part[512 + slot];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); u += __shfl_xor_sync(0xffffffffu, u, o); }
+  if (lane == 0) { redA[g] = s; redB[g] = u; }
+  __syncthreads();
+}
 __device__ __forceinline__ void gn_store(float4 y, size_t row, int c, float* out_f32, int ldO, bf16* hi, bf16* lo, int ldS) {
   if (out_f32) *reinterpret_cast<float4*>(out_f32 + row * ldO + c) = y;
   if (hi) {
@@ -105,11 +126,10 @@ __device__ __forceinline__ void gn_stats(const GnTile& t, int L, int C, float ep
 #pragma unroll
   for (int i = 0; i < 2; ++i) a[i] = (t.v[i].x + t.v[i].y) + (t.v[i].z + t.v[i].w);
   gn_group_reduce(t, a, L, C, part, red);
-  if (threadIdx.x < 8) stat[threadIdx.x] = red[threadIdx.x] * inv_m;
-  __syncthreads();
+  if (threadIdx.x < 8) stat[threadIdx.x] = red[threadIdx.x] * inv_m;          // read after the next reduction's barriers
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
-    const float m = stat[t.col[i] / cg];
+    const float m = red[t.col[i] / cg] * inv_m;
     const float dx = t.v[i].x - m, dy = t.v[i].y - m, dz = t.v[i].z - m, dw = t.v[i].w - m;
     a[i] = t.ok[i] ? (dx * dx + dy * dy) + (dz * dz + dw * dw) : 0.f;
   }
@@ -169,7 +189,7 @@ int gn_forward(const GnArgs& a, cudaStream_t s) {
 
 template <int CT>
 __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
-  __shared__ float red[16], stat[16], red2[16], part[512];
+  __shared__ float red[16], stat[16], red2[16], part[1024];
   const size_t row0 = (size_t)blockIdx.x * a.L;
   const int C = CT ? CT : a.C;
   const int cg = C / 8;
@@ -198,8 +218,7 @@ __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
       p2[i] += dyh[i][j] * xh[i][j];
     }
   }
-  gn_group_reduce(t, p1, a.L, C, part, red2);
-  gn_group_reduce(t, p2, a.L, C, part, red2 + 8);
+  gn_group_reduce2(t, p1, p2, a.L, C, part, red2, red2 + 8);
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     if (!t.ok[i]) continue;
