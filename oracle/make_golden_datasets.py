@@ -117,7 +117,11 @@ def snapshot(ds, items=(0, -1)):
         out["items"][i] = ds[i]
     t = ds.fields["traj"][0]
     for norm in (False, True):
-        out["hard_conds"][norm] = ds.get_hard_conditions(t, horizon=None, normalize=norm)
+        try:
+            out["hard_conds"][norm] = ds.get_hard_conditions(t, horizon=None, normalize=norm)
+        except NotImplementedError:                      # ExpDirectoryDataset inherits the abstract method
+            out["hard_conds"] = None
+            break
     g = torch.Generator("cpu").manual_seed(99)
     probe = torch.rand(7, ds.n_support_points, ds.state_dim, generator=g) * 2.4 - 1.2       # leaves [-1, 1]: clip branch
     out["probe"] = probe

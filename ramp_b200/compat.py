@@ -12,7 +12,7 @@ import importlib
 import sys
 import types
 
-from . import apf, apf_dynamic, cost, diffusion, dynamic, metrics, sample_functions, unet
+from . import apf, apf_dynamic, cost, datasets, diffusion, dynamic, metrics, sample_functions, unet
 
 _HOT = {
     "mpd.models": dict(
@@ -51,6 +51,16 @@ _HOT = {
         DynamicGaussianDiffusionModel=dynamic.DynamicGaussianDiffusionModel, make_timesteps=diffusion.make_timesteps),
     # `from core.metrics import Metrics` / `DynamicMetrics` (inference_static.py:16, inference_dynamic.py:17)
     "core.metrics": dict(Metrics=metrics.Metrics, DynamicMetrics=metrics.DynamicMetrics),
+    # formats either side of the loop: `getattr(datasets, dataset_class)` (train_loaders.py:84,118),
+    # `from core.utils import StateGenerator, ContextManager` (inference_static.py:15)
+    "mpd.datasets": dict(TrajectoryDataset=datasets.TrajectoryDataset, ExpDirectoryDataset=datasets.ExpDirectoryDataset,
+                         TrajectoryDataset3d=datasets.TrajectoryDataset3d),
+    "mpd.datasets.normalization": dict(
+        DatasetNormalizer=datasets.DatasetNormalizer, Normalizer=datasets.Normalizer, Identity=datasets.Identity,
+        GaussianNormalizer=datasets.GaussianNormalizer, LimitsNormalizer=datasets.LimitsNormalizer,
+        SafeLimitsNormalizer=datasets.SafeLimitsNormalizer, FixedLimitsNormalizer=datasets.FixedLimitsNormalizer),
+    "core.utils": dict(StateGenerator=datasets.StateGenerator, ContextManager=datasets.ContextManager,
+                       DynamicsGenerator=datasets.DynamicsGenerator),
 }
 
 

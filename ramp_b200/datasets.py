@@ -271,6 +271,11 @@ def _read_3d(d, ta):
                 sphere_radii=torch.tensor(meta["sphere_radii"], **ta))
 
 
+# EnvPredator.py:22-38 — six square pillars on a 3 x 2 grid; the dynamic loop plans around the first four (:510-511)
+_PX, _PY = 0.5575312972068787, 0.5508843064308167
+PREDATOR_ARENA_BOX_CENTERS = [[_PX, -_PY], [_PX, _PY], [-_PX, _PY], [-_PX, -_PY], [0.0, -_PY], [0.0, _PY]]
+PREDATOR_ARENA_BOX_SIDE = 0.26
+
 _LAYOUTS = {
     "static2d": (("trajs-free.pt", "obstacle_points.pt", "box_centers.npy"), _read_static_2d),
     "pursuit2d": (("trajs-free.pt", "obstacle_pointsORG.pt", "obstacle_config.npy"), _read_pursuit_2d),
@@ -369,6 +374,13 @@ class _TrajectoryTree(Dataset):
             pursuer = PursuerField(np.array([pos if pos is not None else [0.0, 0.0]]), np.array([0.05]),
                                    dynamics_fn=self.dynamics_fn, velocity=self.velocity, tensor_args=self.tensor_args)
         spheres = getattr(self, "sphere_centers", None)
+        if env_id.startswith("EnvPredator"):
+            # the pursuit arena is fixed geometry, whatever the entry's obstacle_config says (EnvPredator.py:22-38)
+            ta = self.tensor_args
+            return PlanningScene(env_id + ("Obstacles" if self.use_extra_objects else ""),
+                                 torch.tensor(PREDATOR_ARENA_BOX_CENTERS, **ta),
+                                 torch.full((len(PREDATOR_ARENA_BOX_CENTERS), 2), PREDATOR_ARENA_BOX_SIDE, **ta),
+                                 pursuer=pursuer, dim=2, tensor_args=ta)
         return PlanningScene(env_id + ("Obstacles" if self.use_extra_objects else ""), self.box_centers[0], self.box_sizes[0],
                              None if spheres is None else spheres[0], None if spheres is None else self.sphere_radi[0],
                              pursuer=pursuer, dim=self.scene_dim, tensor_args=self.tensor_args)
@@ -534,7 +546,7 @@ class ContextManager:
 
 class DynamicsGenerator:
     """scripts/inference/core/utils.py:81-137 — the pursuer's motion law.  `dynamics_fn(t, prev_center, robot_position,
-    velocity_input)` -> new centre [1, 2] (float64 numpy, as the reference computes it): a unit vector toward the robot
+    velocity_input)` -> new centre [1, 2] (float64 numpy): a unit vector toward the robot
     weighted `pursuit_strength`, plus `random_strength` · (sin 2πt, cos 2πt), times the per-axis speed, times dt = 0.1,
     clipped to the arena [-1, 1]².  `ramp_b200.pursuit.DevicePursuer` is the same law as a CUDA kernel."""
 
@@ -545,14 +557,16 @@ class DynamicsGenerator:
         velocity = np.array([[velocity_max / np.sqrt(2), velocity_max / np.sqrt(2)]])
 
         def dynamics_fn(t, prev_center, robot_position, velocity_input):
-            c = np.asarray(prev_center[0], dtype=np.float64)
-            to_robot = np.asarray(robot_position[0], dtype=np.float64)[:2] - c
+            # dtypes flow as in the reference's scalar code: the direction to the robot is computed in the inputs' own
+            # precision (float32 when the centres come from float32 tensors), the wobble and the update in float64
+            c = np.asarray(prev_center)[0]
+            to_robot = np.asarray(robot_position)[0][:2] - c
             dist = np.sqrt(to_robot[0] ** 2 + to_robot[1] ** 2)
             if dist > 0:
                 to_robot = to_robot / dist
             wobble = np.array([np.sin(2 * np.pi * t), np.cos(2 * np.pi * t)])
             heading = pursuit_strength * to_robot + random_strength * wobble
-            new = c + heading * np.asarray(velocity_input[0], dtype=np.float64) * DynamicsGenerator.dt
+            new = c + heading * np.asarray(velocity_input)[0] * DynamicsGenerator.dt
             return np.clip(new, -1, 1)[None, :]
 
         return dynamics_fn, velocity

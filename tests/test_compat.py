@@ -24,6 +24,14 @@ def test_reference_imports_resolve_to_ramp_b200():
     from core.metrics import DynamicMetrics, Metrics                                     # inference_static.py:16, inference_dynamic.py:17
     import ramp_b200.metrics
     assert Metrics is ramp_b200.metrics.Metrics and issubclass(DynamicMetrics, Metrics)
+    from core.utils import ContextManager, DynamicsGenerator, StateGenerator            # inference_dynamic.py:16
+    from mpd.datasets.normalization import LimitsNormalizer
+    import mpd.datasets
+    import ramp_b200.datasets as D
+    assert (ContextManager, DynamicsGenerator, StateGenerator) == (D.ContextManager, D.DynamicsGenerator, D.StateGenerator)
+    assert LimitsNormalizer is D.LimitsNormalizer
+    for cls in ("TrajectoryDataset", "ExpDirectoryDataset", "TrajectoryDataset3d"):     # get_dataset's lookup, train_loaders.py:84
+        assert getattr(mpd.datasets, cls) is getattr(D, cls)
     # constructor contract of the scripts (inference_static.py:85-105): kwargs accepted, state-dict keys of the reference
     net = TemporalUnetInference(state_dim=4, n_support_points=64, unet_input_dim=32, dim_mults=UNET_DIM_MULTS[1])
     m = mpd.models.StaticGaussianDiffusionModel(model=net, variance_schedule='exponential', n_diffusion_steps=100,
