@@ -315,7 +315,7 @@ def _cpu_scene_encoder(pts):
 # ---------------------------------------------------------------------------------------------------
 def replan_latency(dev, ticks, warm, batch=1024):
     import numpy as np
-    from ramp_b200.apf_dynamic import generate_box_points, generate_sphere_points
+    from ramp_b200.apf_dynamic import generate_box_points
     from ramp_b200.dynamic import DynamicGaussianDiffusionModel
     from ramp_b200.graphs import ReplanGraph
     from ramp_b200.testing import SyntheticPursuitDataset, pursuit_cloud_2d, synthetic_state_dict
@@ -330,30 +330,27 @@ def replan_latency(dev, ticks, warm, batch=1024):
     boxes = ds.env.obj_fixed_list[0].fields[0]
     static_pts = torch.from_numpy(np.vstack([generate_box_points(c, s, 960) for c, s in
                                              zip(boxes.centers.numpy(), boxes.sizes.numpy())])).float()
-    pursuer = ds.env.obj_extra_list[0].fields[0]
-    disc_host = torch.empty(256, 2).pin_memory()
-    center_host = torch.empty(2).pin_memory()
+    from ramp_b200.pursuit import DevicePursuer
+    # the pursuer lives on the device: its motion law and its 256-point disc are the first node of the tick graph
+    # (SURVEY 8f f4); the interior-point draws are numpy's, uploaded once as a tape
+    pursuer = DevicePursuer(ds.env.obj_extra_list[0].fields[0].centers[0].numpy(), radius=0.1, num_points=256,
+                            tape_ticks=warm + ticks, device=dev)
     sel_host = torch.empty(8).pin_memory()
     k = 3                                               # a tick with three executed states pinned
     s = torch.linspace(0, 1, H)[:, None]
     plan = torch.cat([-0.8 + 1.6 * s, -0.8 + 1.6 * s, torch.full((H, 2), 0.2)], dim=1)
-    g = ReplanGraph(m, batch, H, k, cloud, static_pts, torch.zeros(256, 2), static_pts, stream_conditioning=True)
+    g = ReplanGraph(m, batch, H, k, cloud, static_pts, torch.zeros(256, 2), static_pts, stream_conditioning=True,
+                    pursuer=pursuer)
     cond_host = cloud.cpu().pin_memory()                # conditioning cloud [6, 64, 2], re-encoded inside the graph every tick
     g.x_clean.copy_(plan.to(dev))
     g.history.copy_(plan[:k + 1].to(dev))
     lat_ms, dev_ms = [], []
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for it in range(warm + ticks):
-        pursuer.update_centers(it, plan[k:k + 1, :2])            # host-side pursuer dynamics (environment protocol)
-        c = pursuer.centers[0].numpy()
-        disc_host.copy_(torch.from_numpy(generate_sphere_points(c, 0.1, 256)).float())
-        center_host.copy_(torch.from_numpy(c))
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         e0.record()
         g.cloud.copy_(cond_host, non_blocking=True)
-        g.disc_points.copy_(disc_host, non_blocking=True)
-        g.disc_center.copy_(center_host, non_blocking=True)
         g.replay()
         sel_host.copy_(g.sel, non_blocking=True)
         e1.record()
@@ -372,8 +369,9 @@ def replan_latency(dev, ticks, warm, batch=1024):
     return {"p50_ms": q(lat_ms, 0.5), "p95_ms": q(lat_ms, 0.95), "device_p50_ms": q(dev_ms, 0.5), "ticks": ticks,
             "warmup_ticks": warm, "batch": batch, "ddim_steps": 5, "network_rows_per_step": 2 * batch,
             "apf_cloud_points": 3840 + 256, "cost_cloud_points": 4096, "cuda_graph": True,
-            "h2d_bytes_per_tick": 256 * 2 * 4 + 8 + int(cond_host.numel()) * 4, "d2h_bytes_per_tick": 32,
+            "h2d_bytes_per_tick": int(cond_host.numel()) * 4, "d2h_bytes_per_tick": 32,
             "conditioning": "cloud uploaded and re-encoded (scene encoder kernels) inside the graph every tick",
+            "pursuer": "motion law + 256-point disc computed by ramp_pursuer_tick inside the graph (no host step)",
             "tensor_floor_ms": 1e3 * 3 * flops / (peaks()[0] * 1e12),
             "note": "reference tick shape (5 DDIM steps of 100, CFG rows x2); floor = 3 split-bf16 MMAs per product at the "
                     "measured sustained bf16 peak"}

@@ -178,6 +178,27 @@ size_t ramp_waypoint_variance_workspace_bytes(int n, int H);
 int ramp_waypoint_variance(const float* x, int n, int H, int D, void* workspace, float* out1, void* stream);
 int ramp_vector_stats(const float* v, int n, float* out3, void* stream);
 
+/* ---- caller-side state of the dynamic planner on the device --------------------------------
+ * ramp_pursuer_tick: one launch = MultiSphereFieldDynamics.update_centers (deps/torch_robotics/.../primitives.py:
+ *     100-107) with the pursuit law of DynamicsGenerator.create_pursuit_dynamics (scripts/inference/core/utils.py:
+ *     84-137), followed by generate_sphere_points (mpd/models/diffusion_models/APFhelper_dynamic.py:18-39).
+ *     center [2] fp32 device, in-out (the reference keeps a float32 tensor between ticks); robot [>=2] fp32 device
+ *     (x, y of the state the pursuer chases); time t = t0 + *tick (tick: device int, may be NULL = 0; `advance`
+ *     increments it after use so graph replays walk forward); do_step = 0 only regenerates the points.
+ *     points [n_rim + n_in, 2] fp32 (NULL = motion only): n_rim golden-angle rim points, then n_in interior points
+ *     from row (*tick mod tape_ticks) of tape [tape_ticks, 2*n_in] fp64 = n_in draws of U(0,1) (radius) then n_in
+ *     draws of U(0, 2pi) (angle), i.e. numpy's draws in the reference's order.  center_out [2] (may be NULL or alias
+ *     another buffer) receives the new centre.  The reference's n_rim = int(num_points * 0.9).
+ * ramp_box_points: generate_box_points (APFhelper_dynamic.py:41-68) for n_boxes boxes of float32 centres / sizes
+ *     [n_boxes, 2]: out [n_boxes, n_per, 2]; n_edge [n_boxes] = the reference's randint draw per box; u_edge
+ *     [n_boxes, n_per] (first n_edge[b] used) and u_in [n_boxes, n_per, 2] (first n_per - n_edge[b] pairs) = its
+ *     np.random.rand draws, fp64. */
+int ramp_pursuer_tick(float* center, const float* robot, int* tick, double t0, int do_step, int advance, float vel_x,
+                      float vel_y, double pursuit_strength, double random_strength, double dt, double radius, int n_rim,
+                      int n_in, const double* tape, int tape_ticks, float* points, float* center_out, void* stream);
+int ramp_box_points(const float* centers, const float* sizes, int n_boxes, int n_per, const int* n_edge,
+                    const double* u_edge, const double* u_in, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -626,3 +626,60 @@ def metric_success(x, ci, thr=0.01):
         out["path_length"], out["path_length_std"] = pl.mean().item(), pl.std().item()
         out["waypoint_variance"] = 0.0 if len(free) == 1 else metric_variance_waypoints(free).item()
     return out
+
+
+# --------------------------------------------------------------------------------------
+# caller-side state of the dynamic planner, with numpy's random draws as INPUTS
+# --------------------------------------------------------------------------------------
+def pursuer_step(t, center, robot, velocity, pursuit_strength=0.8, random_strength=0.2, dt=0.1):
+    """MultiSphereFieldDynamics.update_centers (deps/torch_robotics/torch_robotics/environments/primitives.py:100-107) with
+    dynamics_fn of scripts/inference/core/utils.py:92-135: `to_numpy` hands the law float32 arrays; the unit vector to the
+    robot stays float32, the wobble (sin 2πt, cos 2πt) and the position update are float64, the result is stored back as
+    float32.  center / robot / velocity: 2 values each.  Returns the new centre, float32 [2]."""
+    c = np.asarray(center, dtype=np.float32).reshape(-1)[:2]
+    r = np.asarray(robot, dtype=np.float32).reshape(-1)[:2]
+    v = np.asarray(velocity, dtype=np.float32).reshape(-1)[:2]
+    d = r - c
+    dist = np.sqrt(d[0] ** 2 + d[1] ** 2)
+    if dist > 0:
+        d = d / dist
+    wob = np.array([np.sin(2 * np.pi * t), np.cos(2 * np.pi * t)])
+    head = np.float32(pursuit_strength) * d + random_strength * wob
+    new = c + head * v * dt
+    return np.clip(new, -1, 1).astype(np.float32)
+
+
+def disc_points(center, radius, num_points, draws, surface_ratio=0.9):
+    """generate_sphere_points (mpd/models/diffusion_models/APFhelper_dynamic.py:18-39); draws = the n_in U(0,1) radius draws
+    followed by the n_in U(0,2π) angle draws the reference takes from np.random (:28-29).  Returns float64 [num_points, 2]."""
+    n_rim = int(num_points * surface_ratio)
+    n_in = num_points - n_rim
+    th = np.pi * (3 - np.sqrt(5)) * np.arange(n_rim)
+    r = np.full(n_rim, float(radius))
+    if n_in > 0:
+        draws = np.asarray(draws, dtype=np.float64)
+        r = np.concatenate((r, float(radius) * np.sqrt(draws[:n_in])))
+        th = np.concatenate((th, draws[n_in:2 * n_in]))
+    return np.column_stack((r * np.cos(th) + center[0], r * np.sin(th) + center[1]))
+
+
+def box_points(center, size, num_points, n_edge, u_edge, u_in):
+    """generate_box_points (APFhelper_dynamic.py:41-68) for one box with float32 centre / size (what the dynamic loop passes,
+    diffusion_model_dynamic.py:516-517); n_edge = its randint draw (:49), u_edge = rand(n_edge) (:55), u_in = rand(n_in, 2)
+    (:64).  The perimeter is walked over the reference's 8-entry length table [w, w, h, h, w, w, h, h]."""
+    c = np.asarray(center, dtype=np.float32)
+    s = np.asarray(size, dtype=np.float32)
+    w, h = s[0], s[1]
+    left, right, top, bottom = c[0] - w / 2, c[0] + w / 2, c[1] + h / 2, c[1] - h / 2
+    corners = np.array([[left, top], [right, top], [right, bottom], [left, bottom]])
+    lens = np.array([w, h, w, h]).repeat(2)
+    along = np.asarray(u_edge, dtype=np.float64)[:n_edge] * lens.sum()
+    cum = np.cumsum(lens)
+    seg = np.searchsorted(cum, along)
+    frac = (along - np.concatenate(([0], cum[:-1]))[seg]) / lens[seg]
+    a, b = corners[seg % 4], corners[(seg + 1) % 4]
+    edge = a + frac[:, None] * (b - a)
+    inner = np.array(np.asarray(u_in, dtype=np.float64)[:num_points - n_edge], copy=True)
+    inner[:, 0] = inner[:, 0] * w + left
+    inner[:, 1] = inner[:, 1] * h + bottom
+    return np.concatenate([edge, inner], axis=0)

@@ -10,7 +10,8 @@ the captured region allocates through the library (weights, workspace and tensor
   diffusion_model_3d.py:184-218): T steps of (score network over B*(G+1) rows, fused posterior step).
 * `ReplanGraph`    — one stage-II tick of the dynamic planner (diffusion_model_dynamic.py:553-598): q_sample, pins,
   5 DDIM steps with the point-cloud potential field on the last, smoothing, cost terms, best-of-N selection.  The moving
-  pursuer enters through two small static buffers (disc points, centre) refreshed by the host before each replay.
+  pursuer enters through two small static buffers (disc points, centre) refreshed by the host before each replay, or
+  by `pursuit.DevicePursuer` as the first node of the graph.
 """
 import torch
 
@@ -73,11 +74,13 @@ class ReplanGraph:
 
     Static inputs (update in place, then `replay()`): `x_clean` [H, D] current plan, `history` [k+1, D] executed states,
     `disc_points` [Pd, 2] + `disc_center` [2] pursuer cloud, the cost cloud whose last Pd points are the disc, and —
-    with `stream_conditioning` — `cloud`, the U-Net's conditioning cloud.
+    with `stream_conditioning` — `cloud`, the U-Net's conditioning cloud.  With `pursuer` (a `pursuit.DevicePursuer`) the
+    first node of the graph moves the pursuer toward `history[k]` and rewrites `disc_points` / `disc_center` on the
+    device, so a replay needs no host-side environment step at all.
     Outputs (static): `batch` [B, H, D], `sel` [8] (ramp_select_best), `best` [H, D]."""
 
     def __init__(self, model, batch, horizon, k, obstacle_pts, static_points, disc_points, cost_static_points,
-                 collision_threshold=None, stream_conditioning=False):
+                 collision_threshold=None, stream_conditioning=False, pursuer=None):
         """stream_conditioning: re-run the scene encoder kernels on `cloud` inside the graph: update
         the static `cloud` buffer in place before a replay and the tick is conditioned on the new scene."""
         self.model = model
@@ -110,6 +113,9 @@ class ReplanGraph:
         f.distance_threshold = model.distance_threshold_static
         f.distance_threshold_pred = model.distance_threshold_pred_apf
         self.field = f
+        self.pursuer = pursuer
+        if pursuer is not None and pursuer.num_points != Pd:
+            raise ValueError("pursuer.num_points must equal the disc buffer size")
         mask = torch.zeros(H, dtype=torch.uint8)
         mask[:k + 1] = 1
         mask[H - 1] = 1
@@ -129,6 +135,8 @@ class ReplanGraph:
                     p.val[0, 0, 2:] = 0.0
             if stream_conditioning:
                 model._scene_sig = None                               # encode `cloud` again on this replay
+            if pursuer is not None:                                   # update_centers + generate_sphere_points, one launch
+                pursuer.tick(self.history[k], points=self.disc_points, center_out=self.disc_center)
             self._cost_disc.copy_(self.disc_points)
             self.field.dynamic_cloud.repack()
             self.cost_cloud.repack()
@@ -141,7 +149,11 @@ class ReplanGraph:
             self.best[0, 2:] = 0.0                                    # diffusion_model_dynamic.py:609
             return self.best
 
+        saved = None if pursuer is None else (pursuer.center.clone(), pursuer.counter.clone())
         self.graph, _ = _capture(tick)
+        if saved is not None:                                         # the warm-up passes moved the pursuer: put it back
+            pursuer.center.copy_(saved[0])
+            pursuer.counter.copy_(saved[1])
 
     def replay(self):
         self.graph.replay()
