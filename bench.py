@@ -365,16 +365,20 @@ def replan_latency(dev, ticks, warm, batch=1024):
     lat_ms.sort()
     dev_ms.sort()
     q = lambda v, f: v[min(len(v) - 1, int(f * len(v)))]  # noqa: E731
-    flops = 2 * batch * 5 * F_ROW
+    rows = batch if (batch % 2 == 0 and m.collapse_duplicate_rows) else 2 * batch
+    flops = rows * 5 * F_ROW
     return {"p50_ms": q(lat_ms, 0.5), "p95_ms": q(lat_ms, 0.95), "device_p50_ms": q(dev_ms, 0.5), "ticks": ticks,
-            "warmup_ticks": warm, "batch": batch, "ddim_steps": 5, "network_rows_per_step": 2 * batch,
+            "warmup_ticks": warm, "batch": batch, "ddim_steps": 5, "network_rows_per_step": rows,
+            "reference_rows_per_step": 2 * batch,
             "apf_cloud_points": 3840 + 256, "cost_cloud_points": 4096, "cuda_graph": True,
             "h2d_bytes_per_tick": int(cond_host.numel()) * 4, "d2h_bytes_per_tick": 32,
             "conditioning": "cloud uploaded and re-encoded (scene encoder kernels) inside the graph every tick",
             "pursuer": "motion law + 256-point disc computed by ramp_pursuer_tick inside the graph (no host step)",
             "tensor_floor_ms": 1e3 * 3 * flops / (peaks()[0] * 1e12),
-            "note": "reference tick shape (5 DDIM steps of 100, CFG rows x2); floor = 3 split-bf16 MMAs per product at the "
-                    "measured sustained bf16 peak"}
+            "note": "reference tick shape (5 DDIM steps of 100). The reference stacks the batch twice for CFG, but with an "
+                    "even batch its odd-row latent mask makes both halves the same rows (diffusion_model_dynamic.py:132-145, "
+                    "UnetInference.py:192-195): each distinct row is evaluated once, results bit-identical. floor = 3 "
+                    "split-bf16 MMAs per product over the evaluated rows at the measured sustained bf16 peak"}
 
 
 # ---------------------------------------------------------------------------------------------------

@@ -165,6 +165,7 @@ class _DiffusionBase(nn.Module):
         key = (B, G, x.device)
         if key not in self._r2s:
             self._r2s = {key: self._row_scenes(B, G, x.device)}
+        self._eps_strides = (None, 1)                      # row of (b, g) = b*(G+1) + g
         return self.model.energy_grad_rows(x, t, self._r2s[key], x_repeat=G + 1)
 
     def _row_scenes(self, B, G, device):
@@ -183,7 +184,8 @@ class _DiffusionBase(nn.Module):
         eps = self._eps_rows(x, t, G)
         s = self._sched()
         out = torch.empty_like(x) if out is None else out
-        return ops.step(x, eps, G, w, out, 0, pins=pins, sqrt_recip=s['sqrt_recip'][t], sqrt_recipm1=s['sqrt_recipm1'][t],
+        return ops.step(x, eps, G, w, out, 0, pins=pins, eps_bstride=self._eps_strides[0], eps_gstride=self._eps_strides[1],
+                        sqrt_recip=s['sqrt_recip'][t], sqrt_recipm1=s['sqrt_recipm1'][t],
                         coef1=s['coef1'][t], coef2=s['coef2'][t], sigma=s['sigma'][t], noise_scale=noise_scale,
                         noise=noise, predict_epsilon=self.predict_epsilon)
 
@@ -195,7 +197,8 @@ class _DiffusionBase(nn.Module):
         eps = self._eps_rows(x, t, G)
         s = self._sched()
         x0_out = torch.empty_like(x) if x0_out is None else x0_out
-        ops.step(x, eps, G, w, None, 2, sqrt_recip=s['sqrt_recip'][t], sqrt_recipm1=s['sqrt_recipm1'][t], x0_out=x0_out,
+        ops.step(x, eps, G, w, None, 2, eps_bstride=self._eps_strides[0], eps_gstride=self._eps_strides[1],
+                        sqrt_recip=s['sqrt_recip'][t], sqrt_recipm1=s['sqrt_recipm1'][t], x0_out=x0_out,
                  eps_out=eps_out, predict_epsilon=self.predict_epsilon)
         return x0_out
 
@@ -207,7 +210,8 @@ class _DiffusionBase(nn.Module):
         eps = self._eps_rows(x, t, G)
         s = self._sched()
         out = torch.empty_like(x) if out is None else out
-        return ops.step(x, eps, G, w, out, 1, pins=pins, sqrt_recip=s['sqrt_recip'][t], sqrt_recipm1=s['sqrt_recipm1'][t],
+        return ops.step(x, eps, G, w, out, 1, pins=pins, eps_bstride=self._eps_strides[0], eps_gstride=self._eps_strides[1],
+                        sqrt_recip=s['sqrt_recip'][t], sqrt_recipm1=s['sqrt_recipm1'][t],
                         predict_epsilon=self.predict_epsilon, **self._ddim_scalars(t, t_prev))
 
     # ------------------------------------------------------------------ reference helper surface
