@@ -49,7 +49,7 @@ class ObstacleField:
     """APFhelper_dynamic.py:70-105."""
 
     def __init__(self, static_obstacle_centers, static_obstacle_sizes, dynamic_obstacle_fn, points_per_obstacle=32,
-                 distance_threshold=0.1, distance_threshold_pred=0.2, device=None):
+                 distance_threshold=0.1, distance_threshold_pred=0.2, device=None, device_pursuer=None):
         self.static_obstacle_centers = static_obstacle_centers
         self.static_obstacle_sizes = static_obstacle_sizes
         self.dynamic_obstacle_fn = dynamic_obstacle_fn
@@ -57,6 +57,7 @@ class ObstacleField:
         self.distance_threshold = distance_threshold
         self.distance_threshold_pred = distance_threshold_pred
         self.last_update_time = None
+        self.device_pursuer = device_pursuer
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.static_obstacle_points = np.vstack([generate_box_points(c, s, points_per_obstacle)
                                                  for c, s in zip(static_obstacle_centers, static_obstacle_sizes)])
@@ -75,7 +76,21 @@ class ObstacleField:
         self.dynamic_center_dev = torch.as_tensor(self.dynamic_center, dtype=torch.float32).to(self.device)
 
     def update_dynamic(self, t, start_pos, replan_guide=False, best_idx=None):
-        if self.last_update_time != t:
+        if self.last_update_time != t and self.device_pursuer is not None:
+            # pursuit.DevicePursuer: motion law and disc sampling are kernels, the cloud never visits the host
+            p = self.device_pursuer
+            if replan_guide and best_idx is not None:
+                start_pos = start_pos[best_idx].unsqueeze(0)
+            p.update_centers(t, start_pos)
+            pts = p.tick(p.center, step=False)
+            if self.dynamic_cloud is None or self.dynamic_cloud.points is not pts:
+                self.dynamic_cloud = ops.CloudIndex(pts)
+                self.dynamic_cloud.points = pts
+            else:
+                self.dynamic_cloud.repack()
+            self.dynamic_points, self.dynamic_center, self.dynamic_center_dev = None, None, p.center
+            self.last_update_time = t
+        elif self.last_update_time != t:
             center, radius = self.dynamic_obstacle_fn(t, start_pos, replan_guide, best_idx)
             self.set_dynamic_points(generate_sphere_points(center, radius, self.points_per_obstacle), center)
             self.last_update_time = t

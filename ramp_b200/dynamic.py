@@ -18,6 +18,7 @@ from ._lib import RampError
 from .apf_dynamic import ObstacleField, generate_sphere_points
 from .cost import compute_trajectory_costs
 from .diffusion import _DiffusionBase
+from .pursuit import DevicePursuer
 from .sample_functions import ddpm_sample_fn
 
 
@@ -160,7 +161,8 @@ class DynamicGaussianDiffusionModel(_DiffusionBase):
                                                       dynamic_obstacle_fn, self.points_per_obstacle,
                                                       distance_threshold=self.distance_threshold_static,
                                                       distance_threshold_pred=self.distance_threshold_pred_apf,
-                                                      device=device)
+                                                      device=device,
+                                                      device_pursuer=sphere if isinstance(sphere, DevicePursuer) else None)
         return context['obstacle_field']
 
     # ------------------------------------------------------------------ one DDIM step (reference-shaped)

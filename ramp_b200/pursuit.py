@@ -9,7 +9,7 @@ the `centers` / `radii` / `update_centers` protocol of the reference field, so `
 it as `dataset.env.obj_extra_list[0].fields[0]`.
 
 numpy's random draws are inputs: `draw_disc_tape` / `draw_box_tape` take them from `np.random` in the reference's call
-order, so a seeded run reproduces the reference's clouds (`tests/test_pursuit_gpu.py`)."""
+order, so a seeded run reproduces the reference's clouds (`tests/test_pursuit.py`)."""
 import ctypes
 
 import numpy as np
@@ -96,7 +96,9 @@ class DevicePursuer:
     # -- the reference field protocol (primitives.py:90-107) -------------------------------------------------------
     @property
     def centers(self):
-        return self.center.reshape(1, 2)
+        """[1, 2] snapshot (the reference field rebinds `centers` to a new tensor on every update, and the planner keeps the
+        old ones in `chain_obs`, diffusion_model_dynamic.py:612)."""
+        return self.center.reshape(1, 2).clone()
 
     def update_centers(self, t, current_state=None):
         """Move only (no points), at explicit time t, chasing current_state[0, :2] (a device tensor or host values)."""

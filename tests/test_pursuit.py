@@ -212,3 +212,37 @@ def test_replan_graph_with_device_pursuer_matches_host_fed_graph(cuda):
             assert int(g_dev.sel[0]) == int(g_host.sel[0])
     assert int(dp.counter) == 4
     print("ticks compared under identical noise:", compared)
+
+
+@pytest.mark.gpu
+def test_run_inference_with_device_pursuer_in_the_environment(cuda):
+    """The planner's own loop (run_inference) with a DevicePursuer standing in for the environment's moving sphere: same
+    protocol (`centers`, `radii`, `update_centers`), the pursuer cloud is produced on the device each tick."""
+    from ramp_b200.dynamic import DynamicGaussianDiffusionModel
+    from ramp_b200.pursuit import DevicePursuer
+    from ramp_b200.sample_functions import ddpm_sample_fn
+    from ramp_b200.testing import SyntheticPursuitDataset, pursuit_cloud_2d, synthetic_state_dict
+    from ramp_b200.unet import TemporalUnetInference
+    net = TemporalUnetInference(n_support_points=64, state_dim=4, max_rows=64)
+    m = DynamicGaussianDiffusionModel(model=net, n_diffusion_steps=100, predict_epsilon=True)
+    m.load_state_dict(synthetic_state_dict(m, 0))
+    m = m.to(cuda).eval()
+    m.max_iteration = 3
+    ds = SyntheticPursuitDataset(device=cuda)
+    np.random.seed(0)
+    torch.manual_seed(0)
+    start = ds.env.obj_extra_list[0].fields[0].centers[0].cpu().numpy()
+    dp = DevicePursuer(start, radius=0.1, num_points=64, device=cuda)
+    ds.env.obj_extra_list[0].fields[0] = dp
+    cloud = pursuit_cloud_2d(ds).to(cuda)
+    hc = {0: torch.tensor([-0.8, -0.8, 0.0, 0.0], device=cuda), 63: torch.tensor([0.8, 0.8, 0.0, 0.0], device=cuda)}
+    chain, chain_obs, chain_start = m.run_inference({'dataset': ds}, hc, n_samples=6, horizon=64, return_chain=True,
+                                                    traj_normalized=torch.zeros(64, 4, device=cuda), obstacle_pts=cloud,
+                                                    sample_fn=ddpm_sample_fn)
+    assert chain.shape == (4, 1, 64, 4) and len(chain_obs) == 3 and torch.isfinite(chain).all()
+    track = torch.cat([c.cpu() for c in chain_obs])
+    assert track.shape == (3, 2) and not torch.equal(track[0], track[1]) and not torch.equal(track[1], track[2])
+    # each tick moves the pursuer 0.1 * (0.5 / sqrt 2) * |0.8 unit + 0.2 wobble| <= 0.0354
+    steps = (track[1:] - track[:-1]).norm(dim=1)
+    assert (steps > 0.01).all() and (steps <= 0.0354 * 1.01).all()
+    assert int(dp.counter) == 3                                   # one disc cloud per tick, drawn from the tape
