@@ -49,7 +49,7 @@ def main():
         met = M.trajectory_success_and_metrics(final, ci, threshold=0.01)
         cloud_hit = {thr: compute_collision_with_pointcloud(final, cloud, collision_threshold=thr) for thr in (0.02, 0.05)}
         best = compute_trajectory_costs(final, cloud, collision_threshold=0.02)
-        cases.append(dict(seed=seed, cloud_seed=i, cloud=cloud, centres=centres, sizes=sizes, final=final, x1=chain[1].clone(),
+        cases.append(dict(seed=seed, cloud_seed=i, cloud=cloud, centres=centres, sizes=sizes, final=final.clone(), x1=chain[1].clone(),
                           collision_intensity=ci, free=(ci <= 0.01), success=met["success"],
                           n_free=met["n_free_trajectories"], cloud_hit=cloud_hit,
                           best_index=None if best[0] is None else int(best[4]),
