@@ -190,6 +190,7 @@ __global__ void __launch_bounds__(128) attn_fwd_tc(const bf16* __restrict__ qkv_
                                                    int n_problems, bf16* __restrict__ out_hi, bf16* __restrict__ out_lo) {
   using S = TcShape<L>;
   extern __shared__ __align__(128) unsigned char sm_tc[];
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int pl = warp / S::W, wp = warp % S::W;              // problem within the CTA, warp within the problem
   const int prob = blockIdx.x * S::NP + pl;
@@ -259,6 +260,7 @@ __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_
                                                    int n_problems, bf16* __restrict__ dq_hi, bf16* __restrict__ dq_lo) {
   using S = TcShape<L>;
   extern __shared__ __align__(128) unsigned char sm_tc[];
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int pl = warp / S::W, wp = warp % S::W;
   const int prob = blockIdx.x * S::NP + pl;
@@ -321,7 +323,7 @@ static int launch_fwd_tc(const bf16* qh, const bf16* ql, int n_samples, bf16* oh
   const int smem = S::NP * S::FWD_BYTES;
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_fwd_tc<L, LV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
   const int np = n_samples * 4;
-  attn_fwd_tc<L, LV><<<(np + S::NP - 1) / S::NP, 128, smem, s>>>(qh, ql, np, oh, ol);
+  RAMP_CUDA_OK(launch_pdl(4, attn_fwd_tc<L, LV>, dim3((np + S::NP - 1) / S::NP), dim3(128), smem, s, qh, ql, np, oh, ol));
   RAMP_LAUNCH_OK();
   return 0;
 }
@@ -333,7 +335,7 @@ static int launch_bwd_tc(const bf16* qh, const bf16* ql, const bf16* dh, const b
   const int smem = S::NP * S::BWD_BYTES;
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(attn_bwd_tc<L, LV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
   const int np = n_samples * 4;
-  attn_bwd_tc<L, LV><<<(np + S::NP - 1) / S::NP, 128, smem, s>>>(qh, ql, dh, dl, np, oh, ol);
+  RAMP_CUDA_OK(launch_pdl(4, attn_bwd_tc<L, LV>, dim3((np + S::NP - 1) / S::NP), dim3(128), smem, s, qh, ql, dh, dl, np, oh, ol));
   RAMP_LAUNCH_OK();
   return 0;
 }

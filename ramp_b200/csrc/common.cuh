@@ -5,6 +5,8 @@
 #include <cuda.h>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <string>
 
 namespace ramp {
@@ -36,6 +38,32 @@ void count_launch();
   } while (0)
 
 typedef __nv_bfloat16 bf16;
+
+// ---- programmatic dependent launch (RAMP_PDL bit mask: 1 = GEMM, 2 = GroupNorm, 4 = attention) ----------------------
+// A kernel launched with the attribute may start while the previous kernel of the stream is still draining; it must
+// call pdl_wait() before touching anything that kernel wrote (without the attribute pdl_wait() is a no-op).
+#ifndef RAMP_PDL_DEFAULT
+#define RAMP_PDL_DEFAULT 0
+#endif
+inline int pdl_mode() {
+  static const int m = [] { const char* e = getenv("RAMP_PDL"); return e ? atoi(e) : RAMP_PDL_DEFAULT; }();
+  return m;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(int bit, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = (pdl_mode() & bit) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
 
 // Split-precision activation / weight view: value = hi + lo (two bf16 planes, same layout).
 struct Split {

@@ -543,6 +543,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   uint32_t tmem_acc;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_acc) : "r"(tmem_slot));
+  // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) touches no global data and may
+  // run while the previous kernel of the stream drains; from here on its results are needed.  Both instructions are no-ops
+  // when the launch carries no programmatic-serialization attribute.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   if (warp == 0) {
     // ---------------- TMA producer ----------------
@@ -826,7 +831,21 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   const size_t smem = (size_t)stages * stage_bytes + fixed;
   const long tiles = (long)p.m_tiles * p.n_tiles;
   dim3 grid((unsigned)(tiles < g_num_sms ? tiles : g_num_sms));
-#define RAMP_GEMM_LAUNCH(E, C) gemm_tc_kernel<E, C><<<grid, gemm_threads(C), smem, stream>>>(mAhi, mAlo, mBhi, mBlo, p)
+  // RAMP_PDL=1: launch with programmatic stream serialization, so this kernel's prologue overlaps the tail of the previous
+  // kernel in the stream (it blocks at griddepcontrol.wait until that kernel has completed and flushed)
+  const int use_pdl = pdl_mode() & 1;
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute pdl_attr[1];
+  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = pdl_attr; cfg.numAttrs = use_pdl ? 1 : 0;
+#define RAMP_GEMM_LAUNCH(E, C)                                                                       \
+  do {                                                                                               \
+    cfg.blockDim = dim3(gemm_threads(C));                                                            \
+    RAMP_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<E, C>, mAhi, mAlo, mBhi, mBlo, p));         \
+  } while (0)
   switch (d.epi) {
     case EPI_PLAIN: if (cw == 16) RAMP_GEMM_LAUNCH(EPI_PLAIN, 16); else RAMP_GEMM_LAUNCH(EPI_PLAIN, 32); break;
     case EPI_GEGLU_FWD: RAMP_GEMM_LAUNCH(EPI_GEGLU_FWD, 16); break;

@@ -143,6 +143,7 @@ __device__ __forceinline__ void gn_stats(const GnTile& t, int L, int C, float ep
 template <int CT>
 __global__ void __launch_bounds__(256) gn_forward_kernel(GnArgs a) {
   __shared__ float red[16], stat[16], part[512];
+  pdl_wait();
   const size_t row0 = (size_t)blockIdx.x * a.L;
   const int C = CT ? CT : a.C;
   const int cg = C / 8;
@@ -177,11 +178,11 @@ int gn_forward(const GnArgs& a, cudaStream_t s) {
   RAMP_CHECK(a.ldX % 4 == 0 && (!a.add || a.ldAdd % 4 == 0) && (!a.out_f32 || a.ldO % 4 == 0) && (!a.out_hi || a.ldS % 4 == 0),
              "gn: leading dimensions must be multiples of 4");
   switch (a.C) {
-    case 32: gn_forward_kernel<32><<<a.n_samples, 256, 0, s>>>(a); break;
-    case 64: gn_forward_kernel<64><<<a.n_samples, 256, 0, s>>>(a); break;
-    case 128: gn_forward_kernel<128><<<a.n_samples, 256, 0, s>>>(a); break;
-    case 256: gn_forward_kernel<256><<<a.n_samples, 256, 0, s>>>(a); break;
-    default: gn_forward_kernel<0><<<a.n_samples, 256, 0, s>>>(a); break;
+    case 32: RAMP_CUDA_OK(launch_pdl(2, gn_forward_kernel<32>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
+    case 64: RAMP_CUDA_OK(launch_pdl(2, gn_forward_kernel<64>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
+    case 128: RAMP_CUDA_OK(launch_pdl(2, gn_forward_kernel<128>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
+    case 256: RAMP_CUDA_OK(launch_pdl(2, gn_forward_kernel<256>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
+    default: RAMP_CUDA_OK(launch_pdl(2, gn_forward_kernel<0>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
   }
   RAMP_LAUNCH_OK();
   return 0;
@@ -190,6 +191,7 @@ int gn_forward(const GnArgs& a, cudaStream_t s) {
 template <int CT>
 __global__ void __launch_bounds__(256) gn_backward_kernel(GnBwdArgs a) {
   __shared__ float red[16], stat[16], red2[16], part[1024];
+  pdl_wait();
   const size_t row0 = (size_t)blockIdx.x * a.L;
   const int C = CT ? CT : a.C;
   const int cg = C / 8;
@@ -240,11 +242,11 @@ int gn_backward(const GnBwdArgs& a, cudaStream_t s) {
   RAMP_CHECK(a.ldX % 4 == 0 && a.ldDy % 4 == 0 && (!a.add || a.ldAdd % 4 == 0) && (!a.out_f32 || a.ldO % 4 == 0) &&
              (!a.out_hi || a.ldS % 4 == 0), "gn: leading dimensions must be multiples of 4");
   switch (a.C) {
-    case 32: gn_backward_kernel<32><<<a.n_samples, 256, 0, s>>>(a); break;
-    case 64: gn_backward_kernel<64><<<a.n_samples, 256, 0, s>>>(a); break;
-    case 128: gn_backward_kernel<128><<<a.n_samples, 256, 0, s>>>(a); break;
-    case 256: gn_backward_kernel<256><<<a.n_samples, 256, 0, s>>>(a); break;
-    default: gn_backward_kernel<0><<<a.n_samples, 256, 0, s>>>(a); break;
+    case 32: RAMP_CUDA_OK(launch_pdl(2, gn_backward_kernel<32>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
+    case 64: RAMP_CUDA_OK(launch_pdl(2, gn_backward_kernel<64>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
+    case 128: RAMP_CUDA_OK(launch_pdl(2, gn_backward_kernel<128>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
+    case 256: RAMP_CUDA_OK(launch_pdl(2, gn_backward_kernel<256>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
+    default: RAMP_CUDA_OK(launch_pdl(2, gn_backward_kernel<0>, dim3(a.n_samples), dim3(256), 0, s, a)); break;
   }
   RAMP_LAUNCH_OK();
   return 0;
