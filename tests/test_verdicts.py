@@ -9,7 +9,8 @@ The first reverse step amplifies eps 4602x before the clamp, so a
 clamped entries; like tests/test_sampler_gpu.py the strict comparison therefore starts from the reference's state after that
 step (x1) and runs the remaining 24 steps freely: EVERY verdict identical, waypoints within 1e-3 for >= 95 % of the
 trajectories and within 2e-3 for all (see FREE_RUN_CAP).  A verdict is exempt
-only if the reference trajectory itself sits within 2e-3 of the decision boundary (none in this fixture; counted).  The full
+only if the reference's own verdict on its own trajectory flips when the boxes / the distance threshold move by 2e-3
+(counted and bounded; the disagreements found are reported all at once).  The full
 run from x_T is compared as well and its disagreements are bounded."""
 import os
 
@@ -36,34 +37,44 @@ def _noise(seed, k, B=6):
     return torch.randn((B, 64, 4), generator=torch.Generator("cpu").manual_seed(seed + k), dtype=torch.float32)
 
 
-def _box_margin(final, centres, sizes):
-    """Smallest |distance to a box face| over waypoints, per trajectory (how close the box verdict is to flipping)."""
+def _box_robust(final, centres, sizes):
+    """True where the reference's own box verdict does not change when every box grows or shrinks by MARGIN per face."""
     p = final[:, :, None, :2].double()
-    lo, hi = (centres - sizes[:, None] / 2).double(), (centres + sizes[:, None] / 2).double()
-    return torch.minimum((p - lo).abs(), (p - hi).abs()).amin(dim=(1, 2, 3))
+
+    def free(pad):
+        lo, hi = (centres - sizes[:, None] / 2 - pad).double(), (centres + sizes[:, None] / 2 + pad).double()
+        return ~((p >= lo) & (p <= hi)).all(dim=-1).any(dim=-1).any(dim=-1)
+
+    return free(MARGIN) == free(-MARGIN)
 
 
-def _cloud_margin(final, cloud, thr):
+def _cloud_robust(final, cloud, thr):
+    """True where the reference's own point-cloud verdict is the same at thr - MARGIN and thr + MARGIN."""
     d = torch.cdist(final[:, :, :2].double().reshape(-1, 2), cloud.reshape(-1, 2).double()).reshape(final.shape[0], -1)
-    return (d - thr).abs().amin(dim=1)
+    dmin = d.amin(dim=1)
+    return (dmin < thr - MARGIN) == (dmin < thr + MARGIN)
 
 
-def _check_case(case, final, free, hit, best_index, label):
-    """final [6, 64, 4] cpu; free / hit[thr] bool [6]; best_index int or None."""
+def _check_case(case, final, free, hit, best_index, label, problems):
+    """final [6, 64, 4] cpu; free / hit[thr] bool [6]; best_index int or None.  Appends every disagreement to `problems`
+    (so one run reports all of them) and returns the number of borderline exemptions."""
     dev = (final - case["final"]).abs().amax(dim=(1, 2))
     DEVIATIONS.setdefault(label, []).extend(dev.tolist())
-    assert dev.max().item() <= FREE_RUN_CAP, (label, case["seed"], dev.tolist())
+    if dev.max().item() > FREE_RUN_CAP:
+        problems.append((label, case["seed"], "waypoints", dev.tolist()))
     exempt = 0
-    safe = _box_margin(case["final"], case["centres"], case["sizes"]) > MARGIN
+    safe = _box_robust(case["final"], case["centres"], case["sizes"])
     # the intensity verdict counts waypoints (<= 0.01 means none of 64 inside): compare where no waypoint is borderline
-    assert torch.equal(free[safe], case["free"][safe]), (label, case["seed"], "box verdict")
+    if not torch.equal(free[safe], case["free"][safe]):
+        problems.append((label, case["seed"], "box verdict", free.tolist(), case["free"].tolist()))
     exempt += int((~safe).sum())
     for thr in (0.02, 0.05):
-        safe = _cloud_margin(case["final"], case["cloud"], thr) > MARGIN
-        assert torch.equal(hit[thr][safe], case["cloud_hit"][thr][safe]), (label, case["seed"], "cloud verdict", thr)
+        safe = _cloud_robust(case["final"], case["cloud"], thr)
+        if not torch.equal(hit[thr][safe], case["cloud_hit"][thr][safe]):
+            problems.append((label, case["seed"], "cloud verdict", thr, hit[thr].tolist(), case["cloud_hit"][thr].tolist()))
         exempt += int((~safe).sum())
-    if _cloud_margin(case["final"], case["cloud"], 0.02).min() > MARGIN:
-        assert best_index == case["best_index"], (label, case["seed"], "best-of-N", best_index, case["best_index"])
+    if _cloud_robust(case["final"], case["cloud"], 0.02).all() and best_index != case["best_index"]:
+        problems.append((label, case["seed"], "best-of-N", best_index, case["best_index"]))
     return exempt
 
 
@@ -78,6 +89,7 @@ def test_oracle_verdicts_match_reference_on_two_seeds(gold):
     sd, sch = synthetic_state_dict(m, 0), O.make_schedule(25)
     hc = {0: torch.tensor([-0.8, -0.8, 0.0, 0.0]), 63: torch.tensor([0.8, 0.8, 0.0, 0.0])}
     assert sum(int(c["free"].sum()) for c in gold["cases"]) >= 3 and sum(int((~c["free"]).sum()) for c in gold["cases"]) >= 3
+    problems = []
     for case in (gold["cases"][0], gold["cases"][3]):
         lat = O.scene_encoder_2d(sd, case["cloud"][None])
         x = case["x1"].clone()
@@ -88,7 +100,8 @@ def test_oracle_verdicts_match_reference_on_two_seeds(gold):
         free = O.metric_collision_intensity(x, case["centres"], case["sizes"]) <= 0.01
         hit = {thr: O.collision_mask(x, case["cloud"].reshape(-1, 2), thr) for thr in (0.02, 0.05)}
         best = O.trajectory_costs(x, case["cloud"].reshape(-1, 2), 0.02)
-        _check_case(case, x, free, hit, None if best[0] is None else int(best[4]), "oracle")
+        _check_case(case, x, free, hit, None if best[0] is None else int(best[4]), "oracle", problems)
+    assert not problems, problems
     assert max(DEVIATIONS["oracle"]) <= 1e-3
 
 
@@ -123,7 +136,7 @@ def test_product_verdicts_identical_on_the_fixed_seed_set(cuda, gold):
     m = _product(cuda)
     hc = {0: torch.tensor([-0.8, -0.8, 0.0, 0.0], device=cuda), 63: torch.tensor([0.8, 0.8, 0.0, 0.0], device=cuda)}
     pins = ops.Pins.from_hard_conds(m._repeat_hard_conds(hc, 6), 6, 64, 4, cuda)
-    exempt, n = 0, 0
+    exempt, n, problems = 0, 0, []
     for case in gold["cases"]:
         cloud = case["cloud"].to(cuda).unsqueeze(0)
         x = case["x1"].to(cuda).contiguous()
@@ -131,13 +144,16 @@ def test_product_verdicts_identical_on_the_fixed_seed_set(cuda, gold):
             t = 24 - j
             x = m._ddpm_step(x, t, cloud, _noise(case["seed"], 1 + j).to(cuda) if t > 0 else None, 0.5, pins=pins)
         free, met, hit, best = _product_verdicts(x, case, cuda)
-        exempt += _check_case(case, x.cpu(), free, hit, best, "cuda")
-        assert met["success"] == case["success"] and met["n_free_trajectories"] == case["n_free"]
+        exempt += _check_case(case, x.cpu(), free, hit, best, "cuda", problems)
+        if (met["success"], met["n_free_trajectories"]) != (case["success"], case["n_free"]):
+            problems.append(("cuda", case["seed"], "success", met["success"], met["n_free_trajectories"], case["success"], case["n_free"]))
         n += 6
     dev = torch.tensor(DEVIATIONS["cuda"][-n:])
     print("verdicts compared on %d trajectories x 3 tests, %d borderline exemptions; free-run waypoint deviation: max %.2e, "
           "median %.2e, %d of %d within 1e-3" % (n, exempt, dev.max(), dev.median(), int((dev <= 1e-3).sum()), n))
-    assert exempt == 0
+    print("per-trajectory deviations:", ["%.1e" % v for v in dev.tolist()])
+    assert not problems, problems
+    assert exempt == 0                            # no verdict of this fixture is borderline
     assert (dev <= 1e-3).float().mean().item() >= 0.95
 
 
@@ -160,9 +176,9 @@ def test_product_verdicts_full_run_from_xT(cuda, gold):
         final = chain[-1].contiguous()
         free, _, hit, _ = _product_verdicts(final, case, cuda)
         close = (final.cpu() - case["final"]).abs().amax(dim=(1, 2)) <= 1e-3
-        safe = close & (_box_margin(case["final"], case["centres"], case["sizes"]) > MARGIN)
+        safe = close & _box_robust(case["final"], case["centres"], case["sizes"])
         assert torch.equal(free[safe], case["free"][safe]), case["seed"]
-        safe = close & (_cloud_margin(case["final"], case["cloud"], 0.02) > MARGIN)
+        safe = close & _cloud_robust(case["final"], case["cloud"], 0.02)
         assert torch.equal(hit[0.02][safe], case["cloud_hit"][0.02][safe]), case["seed"]
         flipped += int((~close).sum())
         disagree += int((free != case["free"]).sum())
