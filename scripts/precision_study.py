@@ -1,0 +1,119 @@
+"""CPU study: how many operand bits does the score network need for a FREE-RUNNING 24-step sampling to stay within
+north_star's 1e-3 waypoint band?  (The CUDA path measured 4.4e-4 median / 1.04e-3 max on tests/golden/verdicts.pt with two
+bf16 planes per operand = 16 mantissa bits; profiles/r1_verdicts_gpu.log.)
+
+The oracle's network (oracle/ramp_oracle.py) is run with every contraction operand — activations, weights, attention
+operands, and the output gradients entering the input-gradient contractions — rounded to what a given pair of 16-bit planes
+can carry (value = hi + lo), products and sums in fp32 as in the tensor-core path; the dropped lo*lo term (one more factor
+2^-8 .. 2^-11 down) is not modelled.  Schemes:
+
+  fp32        no rounding (the oracle itself: summation-order noise only)
+  bf16+bf16   what csrc/gemm_tc.cu does today: 8 + 8 mantissa bits
+  fp16+bf16   hi plane fp16 (11 bits), residual plane bf16 (8 bits, keeps the range for tiny residuals): 19 bits; tcgen05
+              kind::f16 takes the operand format per MMA, so hi*hi / hi*lo / lo*hi stay three MMAs on the same bytes
+  fp16+fp16s  both planes fp16, residual scaled by 2^11 before rounding (22 bits; needs a second accumulator or a scaled
+              epilogue add, listed for reference)
+
+Test infrastructure only (imports oracle/); run in the build container:  python scripts/precision_study.py [seed_index ...]
+"""
+import os
+import sys
+import time
+
+import torch
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import ramp_oracle as O  # noqa: E402
+from ramp_b200.testing import synthetic_state_dict  # noqa: E402
+
+
+def planes(x, scheme):
+    if scheme == "fp32":
+        return x
+    if scheme == "bf16+bf16":
+        hi = x.bfloat16().float()
+        return hi + (x - hi).bfloat16().float()
+    if scheme == "fp16+bf16":
+        hi = x.half().float()
+        return hi + (x - hi).bfloat16().float()
+    if scheme == "fp16+fp16s":
+        hi = x.half().float()
+        return hi + ((x - hi) * 2048.0).half().float() / 2048.0
+    raise ValueError(scheme)
+
+
+class _RoundGrad(torch.autograd.Function):
+    """Identity whose backward rounds the gradient: the output-gradient operand of the input-gradient contraction."""
+
+    @staticmethod
+    def forward(ctx, y, scheme):
+        ctx.scheme = scheme
+        return y.view_as(y)
+
+    @staticmethod
+    def backward(ctx, g):
+        return planes(g, ctx.scheme), None
+
+
+class rounded_operands:
+    """Patch the contraction entry points the oracle uses (F.linear, F.conv1d, F.conv_transpose1d, torch.matmul)."""
+
+    def __init__(self, scheme):
+        self.scheme = scheme
+
+    def _q(self, t):
+        return t + (planes(t.detach(), self.scheme) - t.detach())       # rounded value, straight-through gradient
+
+    def __enter__(self):
+        self.saved = (F.linear, F.conv1d, F.conv_transpose1d, torch.matmul)
+        lin, c1, ct, mm = self.saved
+        q, s = self._q, self.scheme
+        F.linear = lambda x, w, b=None: _RoundGrad.apply(lin(q(x), q(w), b), s)
+        F.conv1d = lambda x, w, b=None, **kw: _RoundGrad.apply(c1(q(x), q(w), b, **kw), s)
+        F.conv_transpose1d = lambda x, w, b=None, **kw: _RoundGrad.apply(ct(q(x), q(w), b, **kw), s)
+        torch.matmul = lambda a, b: _RoundGrad.apply(mm(q(a), q(b)), s)
+        return self
+
+    def __exit__(self, *a):
+        F.linear, F.conv1d, F.conv_transpose1d, torch.matmul = self.saved
+
+
+def noise(seed, k, B=6):
+    return torch.randn((B, 64, 4), generator=torch.Generator("cpu").manual_seed(seed + k), dtype=torch.float32)
+
+
+def main():
+    torch.set_num_threads(8)
+    gold = torch.load(os.path.join(ROOT, "tests", "golden", "verdicts.pt"), weights_only=False)
+    which = [int(a) for a in sys.argv[1:]] or [3, 1]
+    from ramp_b200.diffusion import StaticGaussianDiffusionModel
+    from ramp_b200.unet import TemporalUnetInference
+    m = StaticGaussianDiffusionModel(model=TemporalUnetInference(n_support_points=64, state_dim=4), n_diffusion_steps=25,
+                                     predict_epsilon=True)
+    sd, sch = synthetic_state_dict(m, 0), O.make_schedule(25)
+    hc = {0: torch.tensor([-0.8, -0.8, 0.0, 0.0]), 63: torch.tensor([0.8, 0.8, 0.0, 0.0])}
+    print("%-11s %-5s %10s %10s %10s   (free run of 24 steps from the reference's x1, vs the reference's final waypoints)"
+          % ("scheme", "seed", "max", "median", "row err"))
+    for ci in which:
+        case = gold["cases"][ci]
+        lat = O.scene_encoder_2d(sd, case["cloud"][None])
+        ref_eps = O.eps_combined(sd, case["x1"], 23, lat, [2.0])
+        for scheme in ("fp32", "bf16+bf16", "fp16+bf16", "fp16+fp16s"):
+            t0 = time.time()
+            with rounded_operands(scheme):
+                row = (O.eps_combined(sd, case["x1"], 23, lat, [2.0]) - ref_eps).abs().max() / ref_eps.abs().max()
+                x = case["x1"].clone()
+                for j in range(1, 25):
+                    t = 24 - j
+                    x = O.ddpm_step(sch, x, t, O.eps_combined(sd, x, t, lat, [2.0]), noise(case["seed"], 1 + j), 0.5)
+                    x = O.inpaint(x, hc)
+            dev = (x - case["final"]).abs().amax(dim=(1, 2))
+            print("%-11s %-5d %10.2e %10.2e %10.2e   %.0f s" % (scheme, case["seed"], dev.max(), dev.median(), row,
+                                                              time.time() - t0), flush=True)
+
+
+if __name__ == "__main__":
+    main()
