@@ -20,6 +20,9 @@ extern "C" {
 
 const char* ramp_last_error(void);
 int ramp_version(void);
+/* layout of the 16-bit operand planes (value = hi + lo) this build reads and writes: 0 = bf16 hi + bf16 lo (default),
+ * 1 = fp16 hi + bf16 residual (experimental build, -DRAMP_HI_FP16=1) */
+int ramp_plane_format(void);
 /* number of CUDA kernels this library has launched in this process */
 unsigned long long ramp_launch_count(void);
 

@@ -24,18 +24,23 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    if os.environ.get("RAMP_B200_LIB"):
+def build(force=False, verbose=False, hi_fp16=False):
+    """hi_fp16: the experimental plane format (fp16 hi + bf16 residual, csrc/common.cuh) as a SECOND library,
+    libramp_b200_hf16.so, selected at run time with RAMP_B200_LIB=<that path>; the default library is untouched."""
+    if os.environ.get("RAMP_B200_LIB") and not hi_fp16:
         return os.environ["RAMP_B200_LIB"]
-    if not force and not needs_build():
+    if not force and not hi_fp16 and not needs_build():
         return OUT
+    target = os.path.join(HERE, "libramp_b200_hf16.so") if hi_fp16 else OUT
+    bdir = os.path.join(HERE, "build", "hf16") if hi_fp16 else os.path.join(HERE, "build")
+    extra = ["-DRAMP_HI_FP16=1"] if hi_fp16 else []
     objs = []
     procs = []
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    os.makedirs(bdir, exist_ok=True)
     for src in sources():
-        obj = os.path.join(HERE, "build", os.path.basename(src)[:-3] + ".o")
+        obj = os.path.join(bdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
-        cmd = [NVCC] + FLAGS + ["-c", src, "-o", obj]
+        cmd = [NVCC] + FLAGS + extra + ["-c", src, "-o", obj]
         if verbose:
             print(" ".join(cmd))
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
@@ -43,12 +48,12 @@ def build(force=False, verbose=False):
         out, _ = p.communicate()
         if p.returncode != 0:
             raise RuntimeError("nvcc failed on %s:\n%s" % (src, out.decode()))
-    cmd = [NVCC, "-shared", "-cudart", "static", "-o", OUT] + objs + ["-ldl", "-lpthread", "-lrt"]
+    cmd = [NVCC, "-shared", "-cudart", "static", "-o", target] + objs + ["-ldl", "-lpthread", "-lrt"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout.decode())
-    return OUT
+    return target
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True))
+    print(build(force="--force" in sys.argv, verbose=True, hi_fp16="--hi-fp16" in sys.argv))

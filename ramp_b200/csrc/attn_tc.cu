@@ -56,6 +56,27 @@ __device__ __forceinline__ void load_tile(uint32_t tile, const bf16* __restrict_
 __device__ __forceinline__ void cp_async_wait_all() {
   asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
+#if RAMP_HI_FP16
+// The planes in HBM are (fp16 hi, bf16 residual); mma.sync wants both operands in one format, so the `n_pairs` loaded
+// [L][64] tile pairs (hi at base + 2 p TILE, lo one TILE further) are rewritten in place as bf16 + bf16 planes of the same
+// values (the swizzle is irrelevant: hi and lo of an element sit at the same offset of their tiles).
+template <int TILE>
+__device__ __forceinline__ void resplit_tiles(uint32_t base, int n_pairs, int t, int nth) {
+  for (int p = 0; p < n_pairs; ++p) {
+    const uint32_t hi = base + 2 * p * TILE, lo = hi + TILE;
+    for (int w = t; w < TILE / 4; w += nth) {
+      uint32_t h, l;
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(h) : "r"(hi + 4 * w));
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(l) : "r"(lo + 4 * w));
+      float v0, v1;
+      join2_planes(h, l, v0, v1);
+      split2_bb(v0, v1, h, l);
+      asm volatile("st.shared.b32 [%0], %1;" ::"r"(hi + 4 * w), "r"(h) : "memory");
+      asm volatile("st.shared.b32 [%0], %1;" ::"r"(lo + 4 * w), "r"(l) : "memory");
+    }
+  }
+}
+#endif
 
 // A fragments (16 rows m0.., 16 k-columns starting at chunk kc) of a row-major tile
 template <int NCH>
@@ -137,10 +158,10 @@ __device__ __forceinline__ void softmax_frag(float (&s)[L / 8][4]) {
 }
 // accumulator fragments of two adjacent n-tiles -> hi / lo A fragments of the 16-wide k-step they cover
 __device__ __forceinline__ void acc_to_a(const float (&c0)[4], const float (&c1)[4], uint32_t (&ah)[4], uint32_t (&al)[4]) {
-  split2_bf16(c0[0], c0[1], ah[0], al[0]);
-  split2_bf16(c0[2], c0[3], ah[1], al[1]);
-  split2_bf16(c1[0], c1[1], ah[2], al[2]);
-  split2_bf16(c1[2], c1[3], ah[3], al[3]);
+  split2_bb(c0[0], c0[1], ah[0], al[0]);        // operands of mma.sync bf16: always two bf16 planes
+  split2_bb(c0[2], c0[3], ah[1], al[1]);
+  split2_bb(c1[0], c1[1], ah[2], al[2]);
+  split2_bb(c1[2], c1[3], ah[3], al[3]);
 }
 // out[16 x 64] = M[16 x L] (register fragments) . X[L x 64]  (X stored [k][n]: V for O = P V, K for dQ = dS K)
 template <int L>
@@ -207,6 +228,10 @@ __global__ void __launch_bounds__(128) attn_fwd_tc(const bf16* __restrict__ qkv_
   }
   cp_async_wait_all();
   __syncthreads();
+#if RAMP_HI_FP16
+  if (prob < n_problems) resplit_tiles<S::TILE>(base, 3, wp * 32 + lane, S::W * 32);
+  __syncthreads();
+#endif
   if (prob >= n_problems) return;
   const int m0 = 16 * wp;
   float s[L / 8][4];
@@ -224,8 +249,8 @@ __device__ __forceinline__ void park_frag(const float (&p)[L / 8][4], uint32_t T
 #pragma unroll
   for (int nt = 0; nt < L / 8; ++nt) {
     uint32_t h0, l0, h1, l1;
-    split2_bf16(p[nt][0], p[nt][1], h0, l0);
-    split2_bf16(p[nt][2], p[nt][3], h1, l1);
+    split2_bb(p[nt][0], p[nt][1], h0, l0);
+    split2_bb(p[nt][2], p[nt][3], h1, l1);
     const uint32_t a = tile_off<L / 8>(m0 + g, nt) + 4 * t, b = tile_off<L / 8>(m0 + g + 8, nt) + 4 * t;
     asm volatile("st.shared.b32 [%0], %1;" ::"r"(Th + a), "r"(h0));
     asm volatile("st.shared.b32 [%0], %1;" ::"r"(Tl + a), "r"(l0));
@@ -280,6 +305,10 @@ __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_
   }
   cp_async_wait_all();
   __syncthreads();
+#if RAMP_HI_FP16
+  if (live) resplit_tiles<S::TILE>(base, 4, wp * 32 + lane, S::W * 32);
+  __syncthreads();
+#endif
   const int m0 = 16 * wp;
   const size_t row0 = (size_t)n * LV + m0;
   const bool half2 = m0 + 8 < LV;

@@ -577,8 +577,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   } else if (warp == 1) {
     // ---------------- MMA issuer ----------------
     if (lane == 0) {
-      // instruction descriptor: D=f32, A=B=bf16, both K-major, N = BN, M = 128
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      // instruction descriptor: D = f32 (bit 4), A format bits [7,10), B format bits [10,13) (0 = f16, 1 = bf16), both
+      // K-major, N = BN, M = 128.  idesc_ab: a = format of the A plane, b = format of the B plane of that product.
+      const uint32_t idesc0 = (1u << 4) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+#if RAMP_HI_FP16
+      const uint32_t idesc_lh = idesc0 | (1u << 7), idesc_hl = idesc0 | (1u << 10), idesc_hh = idesc0;   // hi planes: fp16
+#else
+      const uint32_t idesc_lh = idesc0 | (1u << 7) | (1u << 10), idesc_hl = idesc_lh, idesc_hh = idesc_lh;
+#endif
       int it = 0, lt = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
         const int buf = lt & 1;
@@ -600,11 +606,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
             const uint32_t ko = k * 32;   // 16 bf16 = 32 B inside the 128 B swizzle row
             const uint32_t first = (i == 0 && k == 0) ? 0u : 1u;
             if (p.nplanes == 2) {
-              umma_bf16(dacc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc, first);
-              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc, 1u);
-              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, 1u);
+              umma_bf16(dacc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc_lh, first);
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc_hl, 1u);
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, 1u);
             } else {
-              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, first);
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, first);
             }
           }
           umma_commit(empty0 + 8 * s);           // frees the smem stage when these MMAs retire

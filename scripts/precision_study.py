@@ -11,6 +11,8 @@ can carry (value = hi + lo), products and sums in fp32 as in the tensor-core pat
   bf16+bf16   what csrc/gemm_tc.cu does today: 8 + 8 mantissa bits
   fp16+bf16   hi plane fp16 (11 bits), residual plane bf16 (8 bits, keeps the range for tiny residuals): 19 bits; tcgen05
               kind::f16 takes the operand format per MMA, so hi*hi / hi*lo / lo*hi stay three MMAs on the same bytes
+  fp16+bf16/attn-bf16   as fp16+bf16 for every Linear / conv, but the attention products (QK^T, PV and their gradients)
+              keep bf16 + bf16 operands (the mma.sync attention kernels re-split what they load)
   fp16+fp16s  both planes fp16, residual scaled by 2^11 before rounding (22 bits; needs a second accumulator or a scaled
               epilogue add, listed for reference)
 
@@ -62,7 +64,9 @@ class rounded_operands:
     """Patch the contraction entry points the oracle uses (F.linear, F.conv1d, F.conv_transpose1d, torch.matmul)."""
 
     def __init__(self, scheme):
-        self.scheme = scheme
+        self.scheme, self.mm_scheme = scheme, scheme
+        if scheme == "fp16+bf16/attn-bf16":          # GEMM operands fp16 + bf16, attention products re-split to bf16 + bf16
+            self.scheme, self.mm_scheme = "fp16+bf16", "bf16+bf16"
 
     def _q(self, t):
         return t + (planes(t.detach(), self.scheme) - t.detach())       # rounded value, straight-through gradient
@@ -74,11 +78,16 @@ class rounded_operands:
         F.linear = lambda x, w, b=None: _RoundGrad.apply(lin(q(x), q(w), b), s)
         F.conv1d = lambda x, w, b=None, **kw: _RoundGrad.apply(c1(q(x), q(w), b, **kw), s)
         F.conv_transpose1d = lambda x, w, b=None, **kw: _RoundGrad.apply(ct(q(x), q(w), b, **kw), s)
-        torch.matmul = lambda a, b: _RoundGrad.apply(mm(q(a), q(b)), s)
+        ms = self.mm_scheme
+        qm = lambda t: t + (planes(t.detach(), ms) - t.detach())  # noqa: E731
+        torch.matmul = lambda a, b: _RoundGrad.apply(mm(qm(a), qm(b)), ms)
         return self
 
     def __exit__(self, *a):
         F.linear, F.conv1d, F.conv_transpose1d, torch.matmul = self.saved
+
+
+SCHEMES = ("fp32", "bf16+bf16", "fp16+bf16", "fp16+bf16/attn-bf16", "fp16+fp16s")
 
 
 def noise(seed, k, B=6):
@@ -88,6 +97,11 @@ def noise(seed, k, B=6):
 def main():
     torch.set_num_threads(8)
     gold = torch.load(os.path.join(ROOT, "tests", "golden", "verdicts.pt"), weights_only=False)
+    global SCHEMES
+    if "--only" in sys.argv:
+        i = sys.argv.index("--only")
+        SCHEMES = tuple(sys.argv[i + 1].split(","))
+        del sys.argv[i:i + 2]
     which = [int(a) for a in sys.argv[1:]] or [3, 1]
     from ramp_b200.diffusion import StaticGaussianDiffusionModel
     from ramp_b200.unet import TemporalUnetInference
@@ -101,7 +115,7 @@ def main():
         case = gold["cases"][ci]
         lat = O.scene_encoder_2d(sd, case["cloud"][None])
         ref_eps = O.eps_combined(sd, case["x1"], 23, lat, [2.0])
-        for scheme in ("fp32", "bf16+bf16", "fp16+bf16", "fp16+fp16s"):
+        for scheme in SCHEMES:
             t0 = time.time()
             with rounded_operands(scheme):
                 row = (O.eps_combined(sd, case["x1"], 23, lat, [2.0]) - ref_eps).abs().max() / ref_eps.abs().max()
