@@ -20,15 +20,15 @@ extern "C" {
 
 const char* ramp_last_error(void);
 int ramp_version(void);
-/* layout of the 16-bit operand planes (value = hi + lo) this build reads and writes: 0 = bf16 hi + bf16 lo (default),
- * 1 = fp16 hi + bf16 residual (experimental build, -DRAMP_HI_FP16=1) */
+/* layout of the 16-bit operand planes (value = hi + lo) this build reads and writes: 2 = fp16 hi + fp16 residual (default),
+ * 0 = bf16 hi + bf16 lo (-DRAMP_PLANES_FP16=0, `python -m ramp_b200.build --planes-bf16`) */
 int ramp_plane_format(void);
 /* number of CUDA kernels this library has launched in this process */
 unsigned long long ramp_launch_count(void);
 
 /* ---- low-level dense contraction (building block of the score network; exposed for tests) ----
  * D[(n,l), :] = sum_t A[n, par_t + a_pstride*(l + joff_t), 0:K] . W[wtap_t, :, 0:K]^T (+bias +bias_tab[row2scene[n]] +residual)
- * A / W are bf16 hi/lo planes (value = hi + lo); precision 3 = hi*hi + hi*lo + lo*hi, 1 = hi*hi.
+ * A / W are 16-bit hi/lo planes (value = hi + lo, format = ramp_plane_format()); precision 3 = hi*hi + hi*lo + lo*hi, 1 = hi*hi.
  * taps_host: ntaps triples (par, joff, wtap).  Output row of (n,l) = n*o_L + l*o_stride + o_off.
  * Replaces torch F.linear / F.conv1d / F.conv_transpose1d calls of mpd/models/layers/layers.py:262-297
  * and mpd/models/layers/layers_attention_mini.py:41,58-62,92-99 and their autograd input-gradients. */
@@ -83,6 +83,8 @@ int ramp_unet_profile_dump(void* handle, const char* path);
  *     x0 = clamp(sqrt_recip*x - sqrt_recipm1*eps, +-1); out = coef1*x0 + coef2*x + sigma*noise*noise_scale
  * mode 1 (DDIM eta=0, diffusion_model_static.py:259-333): out = sa_prev*x0 + sdir*((x - sa_t*x0)/sb_t)
  * mode 2: only x0_out / eps_out are written (the APF runs between the two halves of a DDIM step).
+ * mode 3: out = x + sigma*noise*noise_scale (+ inpainting) only: the second half of a DDPM step whose posterior mean
+ *         was pushed by the potential field first (diffusion_model_static.py:172-181); eps is not read.
  * Inpainting (sample_functions.py:5-10): waypoint h of every trajectory is overwritten by
  * pin_val[b*pin_bstride + h*D ...] when pin_mask[h] != 0.  out may alias x. */
 typedef struct ramp_step_args {
@@ -115,6 +117,9 @@ int ramp_smooth_segment(float* x, int B, int H, int D, int start, int n, float d
  * ramp_nn_query  : cKDTree.query(k=1, distance_upper_bound) (APFhelper.py:17-35): for q[i*qstride + 0..dim-1],
  *                  out_dist = distance (inf if >= upper_bound), out_idx = index (P if none). */
 size_t ramp_cloud_packed_points(int P);
+/* FP32 FMA micro-benchmark (measurement aid): fills every SM with independent FFMA chains on `stream`, waits,
+ * and writes the achieved TFLOP/s (2 flops per FFMA) to *tflops_host: the denominator of the nearest-point kernel's roofline. */
+int ramp_fp32_fma_probe(float* tflops_host, void* stream);
 int ramp_cloud_pack(const float* cloud, int P, int dim, void* packed, void* stream);
 int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int qstride, float upper_bound,
                   float* out_dist, int32_t* out_idx, void* stream);

@@ -326,11 +326,15 @@ def x0_from_eps(sch, x, t, eps):
     return x0.clamp(-1.0, 1.0)
 
 
-def ddpm_step(sch, x, t, eps, noise, noise_scale=1.0):
-    """ddpm_sample_fn (sample_functions.py:19-48) after eps is known; t<0 is treated as 0."""
+def ddpm_step(sch, x, t, eps, noise, noise_scale=1.0, mean_fn=None):
+    """ddpm_sample_fn (sample_functions.py:19-48) after eps is known; t<0 is treated as 0.
+    mean_fn: applied to the posterior mean before the noise (the APF branch of p_mean_variance,
+    diffusion_model_static.py:172-181)."""
     t = max(int(t), 0)
     x0 = x0_from_eps(sch, x, t, eps)
     mean = sch["posterior_mean_coef1"][t] * x0 + sch["posterior_mean_coef2"][t] * x
+    if mean_fn is not None:
+        mean = mean_fn(mean)
     std = torch.exp(0.5 * sch["posterior_log_variance_clipped"][t])
     if t == 0:
         noise = torch.zeros_like(noise)
@@ -489,15 +493,22 @@ def smooth_segment(s1, s2, num_steps, dt=0.1, max_vel=0.8):
 
 
 def sample_ddpm(sd, sch, T, scene_latents, weights, hard_conds, noise, noise_scale=0.5,
-                extra_steps=0, prefix="model."):
-    """p_sample_loop + ddpm_sample_fn (diffusion_model_static.py:231-256, _3d.py:184-218)."""
+                extra_steps=0, prefix="model.", apf_cloud=None, apf_after=20, apf_thr=0.07, apf_strength=0.1,
+                apf_window=5):
+    """p_sample_loop + ddpm_sample_fn (diffusion_model_static.py:231-256, _3d.py:184-218).
+    apf_cloud [P, 2]: the static model's `use_apf` DDPM branch — for forward_t > 20 the posterior mean goes through
+    `avoidance` (threshold 0.07, strength 0.1, window 5) before the noise is added (diffusion_model_static.py:172-181;
+    CFG path only, p_mean_variance_compose has no such branch)."""
     x = inpaint(noise[0].clone(), hard_conds)
     chain = [x.clone()]
     k = 1
-    for i in reversed(range(-extra_steps, T)):
+    for fwd, i in enumerate(reversed(range(-extra_steps, T))):
         t = max(i, 0)
         eps = eps_combined(sd, x, t, scene_latents, weights, prefix)
-        x = ddpm_step(sch, x, t, eps, noise[k], noise_scale)
+        push = None
+        if apf_cloud is not None and fwd > apf_after:
+            push = lambda m: apf_static(m, apf_cloud, apf_thr, apf_strength, apf_window)  # noqa: E731
+        x = ddpm_step(sch, x, t, eps, noise[k], noise_scale, mean_fn=push)
         k += 1
         x = inpaint(x, hard_conds)
         chain.append(x.clone())

@@ -19,7 +19,16 @@ import types
 import torch
 
 _TORCH_RANDN = torch.randn  # bound before any patching
-REF_ROOT = os.environ.get("RAMP_REFERENCE_ROOT", "/root/reference")
+
+
+def _default_root():
+    """/root/reference in the build container; oracle/_ref (oracle/build_ref.py's untracked copy) on the GPU box."""
+    if os.path.isdir("/root/reference/mpd"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REF_ROOT = os.environ.get("RAMP_REFERENCE_ROOT") or _default_root()
 
 
 def reference_available():
@@ -54,8 +63,9 @@ def import_reference():
         if not reference_available():
             raise RuntimeError("reference tree not present at %s" % REF_ROOT)
         _stub_matplotlib()
-        if REF_ROOT not in sys.path:
-            sys.path.insert(0, REF_ROOT)
+        for pth in (os.path.join(REF_ROOT, "deps", "torch_robotics"), REF_ROOT):
+            if pth not in sys.path:
+                sys.path.insert(0, pth)
         with contextlib.redirect_stdout(open(os.devnull, "w")):
             import mpd.models as m  # noqa
         _REF = m

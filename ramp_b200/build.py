@@ -24,16 +24,17 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False, hi_fp16=False):
-    """hi_fp16: the experimental plane format (fp16 hi + bf16 residual, csrc/common.cuh) as a SECOND library,
-    libramp_b200_hf16.so, selected at run time with RAMP_B200_LIB=<that path>; the default library is untouched."""
-    if os.environ.get("RAMP_B200_LIB") and not hi_fp16:
+def build(force=False, verbose=False, planes_bf16=False):
+    """planes_bf16: round 1's operand-plane format (bf16 + bf16, csrc/common.cuh) as a SECOND library,
+    libramp_b200_bf16.so, selected at run time with RAMP_B200_LIB=<that path> for A/B runs; the default library
+    (fp16 + fp16 planes) is untouched."""
+    if os.environ.get("RAMP_B200_LIB") and not planes_bf16:
         return os.environ["RAMP_B200_LIB"]
-    if not force and not hi_fp16 and not needs_build():
+    if not force and not planes_bf16 and not needs_build():
         return OUT
-    target = os.path.join(HERE, "libramp_b200_hf16.so") if hi_fp16 else OUT
-    bdir = os.path.join(HERE, "build", "hf16") if hi_fp16 else os.path.join(HERE, "build")
-    extra = ["-DRAMP_HI_FP16=1"] if hi_fp16 else []
+    target = os.path.join(HERE, "libramp_b200_bf16.so") if planes_bf16 else OUT
+    bdir = os.path.join(HERE, "build", "bf16") if planes_bf16 else os.path.join(HERE, "build")
+    extra = ["-DRAMP_PLANES_FP16=0"] if planes_bf16 else []
     objs = []
     procs = []
     os.makedirs(bdir, exist_ok=True)
@@ -56,4 +57,4 @@ def build(force=False, verbose=False, hi_fp16=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True, hi_fp16="--hi-fp16" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose=True, planes_bf16="--planes-bf16" in sys.argv))

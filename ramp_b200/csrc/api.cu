@@ -26,7 +26,7 @@ extern "C" {
 
 const char* ramp_last_error(void) { return g_err.c_str(); }
 int ramp_version(void) { return 100; }
-int ramp_plane_format(void) { return RAMP_HI_FP16 ? 1 : 0; }
+int ramp_plane_format(void) { return RAMP_PLANES_FP16 ? 2 : 0; }
 unsigned long long ramp_launch_count(void) { return g_launches; }
 
 int ramp_split_bf16(const float* x, size_t n, void* hi, void* lo, void* stream) {

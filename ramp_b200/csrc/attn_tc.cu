@@ -1,7 +1,7 @@
 // Tensor-core self-attention core (layers_attention_mini.py:100-126) for L = 64 / 32 / 16 / 8 tokens (8 runs zero-padded to 16 with masked keys), 4 heads x 64, and its
-// input gradient (autograd at UnetInference.py:23-27), on mma.sync.m16n8k16 bf16 with split-precision operands:
-// every product A.B is issued as A_lo.B_hi + A_hi.B_lo + A_hi.B_hi into one fp32 accumulator (error ~2^-17), the
-// same scheme as the tcgen05 GEMM.  tcgen05 does not fit here: a (sample, head) problem is a 64x64x64 batch item and
+// input gradient (autograd at UnetInference.py:23-27), on mma.sync.m16n8k16 (f16 or bf16, the plane format of
+// common.cuh) with split-precision operands: every product A.B is issued as A_lo.B_hi + A_hi.B_lo + A_hi.B_hi into one
+// fp32 accumulator, the same scheme as the tcgen05 GEMM.  tcgen05 does not fit here: a (sample, head) problem is a 64x64x64 batch item and
 // the softmax sits between the two products, so the FlashAttention-2 register pipeline is used instead —
 //   S = Q K^T (ldmatrix operands) -> softmax on the accumulator fragments -> P re-packed in registers as the A
 //   operand of O = P V (V through ldmatrix.trans).
@@ -23,7 +23,11 @@ __device__ __forceinline__ void ldsm4t(uint32_t addr, uint32_t (&r)[4]) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
 __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+#if RAMP_PLANES_FP16
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+#else
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+#endif
                : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
@@ -56,28 +60,6 @@ __device__ __forceinline__ void load_tile(uint32_t tile, const bf16* __restrict_
 __device__ __forceinline__ void cp_async_wait_all() {
   asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
-#if RAMP_HI_FP16
-// The planes in HBM are (fp16 hi, bf16 residual); mma.sync wants both operands in one format, so the `n_pairs` loaded
-// [L][64] tile pairs (hi at base + 2 p TILE, lo one TILE further) are rewritten in place as bf16 + bf16 planes of the same
-// values (the swizzle is irrelevant: hi and lo of an element sit at the same offset of their tiles).
-template <int TILE>
-__device__ __forceinline__ void resplit_tiles(uint32_t base, int n_pairs, int t, int nth) {
-  for (int p = 0; p < n_pairs; ++p) {
-    const uint32_t hi = base + 2 * p * TILE, lo = hi + TILE;
-    for (int w = t; w < TILE / 4; w += nth) {
-      uint32_t h, l;
-      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(h) : "r"(hi + 4 * w));
-      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(l) : "r"(lo + 4 * w));
-      float v0, v1;
-      join2_planes(h, l, v0, v1);
-      split2_bb(v0, v1, h, l);
-      asm volatile("st.shared.b32 [%0], %1;" ::"r"(hi + 4 * w), "r"(h) : "memory");
-      asm volatile("st.shared.b32 [%0], %1;" ::"r"(lo + 4 * w), "r"(l) : "memory");
-    }
-  }
-}
-#endif
-
 // A fragments (16 rows m0.., 16 k-columns starting at chunk kc) of a row-major tile
 template <int NCH>
 __device__ __forceinline__ void a_frag(uint32_t tile, int m0, int kc, int lane, uint32_t (&r)[4]) {
@@ -158,10 +140,10 @@ __device__ __forceinline__ void softmax_frag(float (&s)[L / 8][4]) {
 }
 // accumulator fragments of two adjacent n-tiles -> hi / lo A fragments of the 16-wide k-step they cover
 __device__ __forceinline__ void acc_to_a(const float (&c0)[4], const float (&c1)[4], uint32_t (&ah)[4], uint32_t (&al)[4]) {
-  split2_bb(c0[0], c0[1], ah[0], al[0]);        // operands of mma.sync bf16: always two bf16 planes
-  split2_bb(c0[2], c0[3], ah[1], al[1]);
-  split2_bb(c1[0], c1[1], ah[2], al[2]);
-  split2_bb(c1[2], c1[3], ah[3], al[3]);
+  split2_bf16(c0[0], c0[1], ah[0], al[0]);        // register operands use the plane format too
+  split2_bf16(c0[2], c0[3], ah[1], al[1]);
+  split2_bf16(c1[0], c1[1], ah[2], al[2]);
+  split2_bf16(c1[2], c1[3], ah[3], al[3]);
 }
 // out[16 x 64] = M[16 x L] (register fragments) . X[L x 64]  (X stored [k][n]: V for O = P V, K for dQ = dS K)
 template <int L>
@@ -228,10 +210,6 @@ __global__ void __launch_bounds__(128) attn_fwd_tc(const bf16* __restrict__ qkv_
   }
   cp_async_wait_all();
   __syncthreads();
-#if RAMP_HI_FP16
-  if (prob < n_problems) resplit_tiles<S::TILE>(base, 3, wp * 32 + lane, S::W * 32);
-  __syncthreads();
-#endif
   if (prob >= n_problems) return;
   const int m0 = 16 * wp;
   float s[L / 8][4];
@@ -249,8 +227,8 @@ __device__ __forceinline__ void park_frag(const float (&p)[L / 8][4], uint32_t T
 #pragma unroll
   for (int nt = 0; nt < L / 8; ++nt) {
     uint32_t h0, l0, h1, l1;
-    split2_bb(p[nt][0], p[nt][1], h0, l0);
-    split2_bb(p[nt][2], p[nt][3], h1, l1);
+    split2_bf16(p[nt][0], p[nt][1], h0, l0);
+    split2_bf16(p[nt][2], p[nt][3], h1, l1);
     const uint32_t a = tile_off<L / 8>(m0 + g, nt) + 4 * t, b = tile_off<L / 8>(m0 + g + 8, nt) + 4 * t;
     asm volatile("st.shared.b32 [%0], %1;" ::"r"(Th + a), "r"(h0));
     asm volatile("st.shared.b32 [%0], %1;" ::"r"(Tl + a), "r"(l0));
@@ -305,10 +283,6 @@ __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_
   }
   cp_async_wait_all();
   __syncthreads();
-#if RAMP_HI_FP16
-  if (live) resplit_tiles<S::TILE>(base, 4, wp * 32 + lane, S::W * 32);
-  __syncthreads();
-#endif
   const int m0 = 16 * wp;
   const size_t row0 = (size_t)n * LV + m0;
   const bool half2 = m0 + 8 < LV;

@@ -73,51 +73,44 @@ struct Split {
 };
 
 // ---- hi/lo split ------------------------------------------------------------------------------
-// split_bb / split2_bb: two bf16 planes (8 + 8 mantissa bits) — the operands of the mma.sync bf16 attention products.
-__device__ __forceinline__ void split_bb(float v, bf16& hi, bf16& lo) {
+// Every GEMM / attention operand is stored as two 16-bit planes, value = hi + lo.  RAMP_PLANES_FP16 picks the format:
+//   1 (default): fp16 + fp16.  hi = fp16(v) (11 bits, clamped to the fp16 range), lo = fp16(v - hi): 22 bits for |v| >= 2^-3,
+//      an absolute error <= 3e-8 (half an fp16 subnormal step) below that.  The backward sweep is loss-scaled by
+//      RAMP_GRAD_SCALE (a power of two: exact) so that gradients sit in the well-resolved range too.  CPU study
+//      (scripts/precision_study.py, profiles/r2_precision_study_cpu.txt): free-run deviation 4-6e-4 -> 4-7e-5 (= fp32 noise).
+//   0: bf16 + bf16 (8 + 8 bits, round 1's format), built as a second library by `python -m ramp_b200.build --planes-bf16`.
+// A mixed pair (fp16 hi, bf16 residual) is NOT an option: tcgen05.mma kind::f16 with A = f16, B = bf16 raises
+// "illegal instruction" on B200 (measured, round 2) — both operands of a product must share one format.
+#ifndef RAMP_PLANES_FP16
+#define RAMP_PLANES_FP16 1
+#endif
+#if RAMP_PLANES_FP16
+#define RAMP_GRAD_SCALE 256.0f
+__device__ __forceinline__ void split_bf16(float v, bf16& hi, bf16& lo) {
+  const __half h = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+  hi = __ushort_as_bfloat16(__half_as_ushort(h));                    // fp16 bits in a 16-bit plane element
+  lo = __ushort_as_bfloat16(__half_as_ushort(__float2half_rn(v - __half2float(h))));
+}
+// two values at once: packed f16x2 planes (element 0 in the low half)
+__device__ __forceinline__ void split2_bf16(float v0, float v1, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(v1), "f"(v0));      // saturates at +-65504 (one F2FP)
+  float h0, h1;
+  asm("{.reg .b16 a, b; mov.b32 {a, b}, %2; cvt.f32.f16 %0, a; cvt.f32.f16 %1, b;}" : "=f"(h0), "=f"(h1) : "r"(hi));
+  const float r0 = v0 - h0, r1 = v1 - h1;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(r1), "f"(r0));
+}
+#else
+#define RAMP_GRAD_SCALE 1.0f
+__device__ __forceinline__ void split_bf16(float v, bf16& hi, bf16& lo) {
   hi = __float2bfloat16_rn(v);
   lo = __float2bfloat16_rn(v - __bfloat162float(hi));
 }
 // two values at once: packed bf16x2 planes (element 0 in the low half), 6 instructions per pair
-__device__ __forceinline__ void split2_bb(float v0, float v1, uint32_t& hi, uint32_t& lo) {
+__device__ __forceinline__ void split2_bf16(float v0, float v1, uint32_t& hi, uint32_t& lo) {
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(v1), "f"(v0));
   const float r0 = v0 - __uint_as_float(hi << 16), r1 = v1 - __uint_as_float(hi & 0xffff0000u);
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(r1), "f"(r0));
 }
-
-// split_bf16 / split2_bf16: the planes every kernel WRITES to HBM for the next contraction.
-// RAMP_HI_FP16 = 0 (default): bf16 + bf16.
-// RAMP_HI_FP16 = 1 (experimental build, `python -m ramp_b200.build --hi-fp16`): the hi plane holds fp16 bits (11 mantissa
-//   bits; clamped to the fp16 range, the bf16 residual plane carries whatever is left), 19 bits in all.  tcgen05 kind::f16
-//   takes the A / B formats per MMA (gemm_tc.cu); the mma.sync attention kernels re-split what they load (attn_tc.cu).
-//   CPU study: scripts/precision_study.py (free-run deviation 4-6e-4 -> 6-9e-5).  Not validated on a GPU yet.
-#ifndef RAMP_HI_FP16
-#define RAMP_HI_FP16 0
-#endif
-#if RAMP_HI_FP16
-__device__ __forceinline__ void split_bf16(float v, bf16& hi, bf16& lo) {
-  const __half h = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
-  hi = __ushort_as_bfloat16(__half_as_ushort(h));                    // fp16 bits in a 16-bit plane element
-  lo = __float2bfloat16_rn(v - __half2float(h));
-}
-__device__ __forceinline__ void split2_bf16(float v0, float v1, uint32_t& hi, uint32_t& lo) {
-  const float c0 = fminf(fmaxf(v0, -65504.f), 65504.f), c1 = fminf(fmaxf(v1, -65504.f), 65504.f);
-  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(c1), "f"(c0));
-  float h0, h1;
-  asm("{.reg .b16 a, b; mov.b32 {a, b}, %2; cvt.f32.f16 %0, a; cvt.f32.f16 %1, b;}" : "=f"(h0), "=f"(h1) : "r"(hi));
-  const float r0 = v0 - h0, r1 = v1 - h1;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(r1), "f"(r0));
-}
-// packed (fp16x2 hi, bf16x2 lo) words -> the two fp32 values they stand for
-__device__ __forceinline__ void join2_planes(uint32_t hi, uint32_t lo, float& v0, float& v1) {
-  float h0, h1;
-  asm("{.reg .b16 a, b; mov.b32 {a, b}, %2; cvt.f32.f16 %0, a; cvt.f32.f16 %1, b;}" : "=f"(h0), "=f"(h1) : "r"(hi));
-  v0 = h0 + __uint_as_float(lo << 16);
-  v1 = h1 + __uint_as_float(lo & 0xffff0000u);
-}
-#else
-__device__ __forceinline__ void split_bf16(float v, bf16& hi, bf16& lo) { split_bb(v, hi, lo); }
-__device__ __forceinline__ void split2_bf16(float v0, float v1, uint32_t& hi, uint32_t& lo) { split2_bb(v0, v1, hi, lo); }
 #endif
 
 __device__ __forceinline__ float warp_sum(float v) {

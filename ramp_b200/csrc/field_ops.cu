@@ -7,8 +7,9 @@
 // over the cloud per waypoint: FP32-pipe bound.  Cloud tiles are staged in shared memory by TMA bulk
 // copies (double buffered, mbarrier completion); each thread keeps R waypoints in registers and
 // evaluates |p|^2 - 2 q.p with d FFMA per pair plus one 3-input min per two pairs; the argmin is
-// recovered by re-scanning only the winning 64-point chunk, and the returned distance is
-// re-derived exactly (direct form) for the winner.
+// recovered by re-scanning, in the direct form (q - p)^2, every 64-point chunk whose minimum key is within the key's
+// rounding bound of the best one (normally one or two chunks; the whole cloud by the warp when three or more tie), so
+// the index is the fp32-exact nearest point with the lowest index on ties, and the distance is re-derived exactly.
 #include "../../include/ramp_b200.h"
 #include "common.cuh"
 #include <cstdio>
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
   };
   if (tid == 0) issue(0);
 
-  float mx[R], my[R], mz[R], best[R], second[R];
+  float mx[R], my[R], mz[R], best[R], second[R], third[R];
   int bchunk[R], schunk[R];
 #pragma unroll
   for (int r = 0; r < R; ++r) {
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
       my[r] = -2.f * q[(size_t)qi * qstride + 1];
       if (DIM == 3) mz[r] = -2.f * q[(size_t)qi * qstride + 2];
     }
-    best[r] = second[r] = FLT_MAX; bchunk[r] = schunk[r] = 0;
+    best[r] = second[r] = third[r] = FLT_MAX; bchunk[r] = schunk[r] = 0;
   }
   for (int t = 0; t < ntiles; ++t) {
     if (tid == 0 && t + 1 < ntiles) issue(t + 1);
@@ -108,43 +109,76 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
       }
       const int gc = t * (TILE / NN_CHUNK) + c;
 #pragma unroll
-      for (int r = 0; r < R; ++r) {
-        if (cm[r] < best[r]) { second[r] = best[r]; schunk[r] = bchunk[r]; best[r] = cm[r]; bchunk[r] = gc; }
-        else if (cm[r] < second[r]) { second[r] = cm[r]; schunk[r] = gc; }
+      for (int r = 0; r < R; ++r) {   // the two smallest chunk minima with their chunks, and the value of the third
+        if (cm[r] < best[r]) { third[r] = second[r]; second[r] = best[r]; schunk[r] = bchunk[r]; best[r] = cm[r]; bchunk[r] = gc; }
+        else if (cm[r] < second[r]) { third[r] = second[r]; second[r] = cm[r]; schunk[r] = gc; }
+        else third[r] = fminf(third[r], cm[r]);
       }
     }
     __syncthreads();
   }
-  // Exact decision: the scan key |p|^2 - 2 q.p carries cancellation error ~2^-22 (|q|^2 + |p|^2); the winning
-  // chunk (and the runner-up chunk when its key is within that bound) is re-scanned with the direct form
-  // (q - p)^2, lowest index winning ties, so the result is the fp32-exact nearest point.
+  // Exact decision.  The scan key k = |p|^2 - 2 q.p is three roundings of |p|^2 (pack) and two fused multiply-adds away
+  // from d^2 - |q|^2: |error| <= 2^-24 (4 |p|^2 + 2 |q| |p| + |k|), with |p| <= |q| + d.  Every chunk whose minimum key lies
+  // within twice that bound (+ margin) of the best key may hold the true nearest point and is re-scanned with the direct
+  // form (q - p)^2, lowest index winning ties: the winning chunk, the runner-up chunk, and - when a THIRD chunk is that
+  // close too (dense clouds: the 1 M-point sweep has a mean nearest d^2 of 1e-6, the size of the bound itself) - the whole
+  // cloud, by the warp together (the lanes stride over the points, then an argmin reduction).
+  const int lane = tid & 31;
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const int qi = (blockIdx.x * R + r) * NN_THREADS + tid;
-    if (qi >= Q) continue;
-    const float qx = q[(size_t)qi * qstride], qy = q[(size_t)qi * qstride + 1];
-    const float qz = DIM == 3 ? q[(size_t)qi * qstride + 2] : 0.f;
+    const bool live = qi < Q;
+    const size_t qo = (size_t)(live ? qi : 0) * qstride;
+    const float qx = q[qo], qy = q[qo + 1];
+    const float qz = DIM == 3 ? q[qo + 2] : 0.f;
     const float q2 = qx * qx + qy * qy + qz * qz;
-    const float tol = 1.2e-6f * (q2 + fabsf(best[r] + q2)) + 1e-30f;
+    const float qn = sqrtf(q2), pn = qn + sqrtf(fmaxf(best[r] + q2, 0.f));
+    const float tol = 1.5e-7f * (4.f * pn * pn + 2.f * qn * pn + fabsf(best[r])) + 1e-30f;    // 2.5 x 2^-24 x (...)
     float bd2 = FLT_MAX; int gi = P;
-    const int ncand = (second[r] <= best[r] + tol && schunk[r] != bchunk[r]) ? 2 : 1;
-    for (int cnd = 0; cnd < ncand; ++cnd) {
-      const int ch = cnd == 0 ? bchunk[r] : schunk[r];
-      const float4* cp = cloud4 + (size_t)ch * NN_CHUNK;
-      for (int j = 0; j < NN_CHUNK; ++j) {
-        const float4 p = cp[j];
-        if (p.w == FLT_MAX) continue;               // padding
-        const float dx = qx - p.x, dy = qy - p.y;
-        float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-        if (DIM == 3) { const float dz = qz - p.z; d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
-        const int g = ch * NN_CHUNK + j;
-        if (d2 < bd2 || (d2 == bd2 && g < gi)) { bd2 = d2; gi = g; }
+    const bool crowded = live && third[r] <= best[r] + tol;
+    const unsigned need = __ballot_sync(0xffffffffu, crowded);
+    if (live && !crowded) {
+      const int ncand = (second[r] <= best[r] + tol && schunk[r] != bchunk[r]) ? 2 : 1;
+      for (int cnd = 0; cnd < ncand; ++cnd) {
+        const int ch = cnd == 0 ? bchunk[r] : schunk[r];
+        const float4* cp = cloud4 + (size_t)ch * NN_CHUNK;
+        for (int j = 0; j < NN_CHUNK; ++j) {
+          const float4 p = cp[j];
+          if (p.w == FLT_MAX) continue;               // padding
+          const float dx = qx - p.x, dy = qy - p.y;
+          float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+          if (DIM == 3) { const float dz = qz - p.z; d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
+          const int g = ch * NN_CHUNK + j;
+          if (d2 < bd2 || (d2 == bd2 && g < gi)) { bd2 = d2; gi = g; }
+        }
       }
     }
-    const float d = sqrtf(bd2);
-    const bool hit = gi < P && d < thr;
-    out_d[qi] = hit ? d : INFINITY;
-    out_idx[qi] = hit ? gi : P;
+    for (unsigned m = need; m; m &= m - 1) {         // warp-uniform loop: one crowded query at a time
+      const int src = __ffs(m) - 1;
+      const float sx = __shfl_sync(0xffffffffu, qx, src), sy = __shfl_sync(0xffffffffu, qy, src);
+      const float sz = __shfl_sync(0xffffffffu, qz, src);
+      float wd = FLT_MAX; int wi = P;
+      for (int g = lane; g < P; g += 32) {            // ascending g per lane: strict < keeps the lowest index
+        const float4 p = cloud4[g];
+        const float dx = sx - p.x, dy = sy - p.y;
+        float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+        if (DIM == 3) { const float dz = sz - p.z; d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
+        if (d2 < wd) { wd = d2; wi = g; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float od = __shfl_xor_sync(0xffffffffu, wd, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, wi, o);
+        if (od < wd || (od == wd && oi < wi)) { wd = od; wi = oi; }
+      }
+      if (lane == src) { bd2 = wd; gi = wi; }
+    }
+    if (live) {
+      const float d = sqrtf(bd2);
+      const bool hit = gi < P && d < thr;
+      out_d[qi] = hit ? d : INFINITY;
+      out_idx[qi] = hit ? gi : P;
+    }
   }
 }
 
@@ -353,6 +387,21 @@ __global__ void __launch_bounds__(1024) select_best_kernel(const float* __restri
   }
 }
 
+// FP32 FMA micro-benchmark: 8 independent FFMA chains per thread, 256-thread CTAs, 8 CTAs per SM.
+__global__ void __launch_bounds__(256) fma_probe_kernel(float* __restrict__ sink, int iters, float b, float c) {
+  float a[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a[j] = (float)(threadIdx.x + j) * 1e-3f;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = fmaf(a[j], b, c);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s += a[j];
+  if (s == 123456.789f) sink[0] = s;      // keeps the chains alive
+}
+
 }  // namespace ramp
 
 using namespace ramp;
@@ -413,6 +462,33 @@ static int nn_choose(int Q, int* R_out, int* TILE_out) {
 }
 
 extern "C" {
+
+int ramp_fp32_fma_probe(float* tflops_host, void* stream) {
+  RAMP_CHECK(tflops_host, "ramp_fp32_fma_probe: null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  int dev = 0, sms = 148;
+  RAMP_CUDA_OK(cudaGetDevice(&dev));
+  RAMP_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  static float* sink = nullptr;
+  if (!sink) RAMP_CUDA_OK(cudaMalloc(&sink, 256));
+  cudaEvent_t e0, e1;
+  RAMP_CUDA_OK(cudaEventCreate(&e0));
+  RAMP_CUDA_OK(cudaEventCreate(&e1));
+  const int iters = 1 << 18, ctas = sms * 8;
+  fma_probe_kernel<<<ctas, 256, 0, s>>>(sink, 1 << 10, 0.999f, 1e-3f);          // warm-up
+  RAMP_LAUNCH_OK();
+  RAMP_CUDA_OK(cudaEventRecord(e0, s));
+  fma_probe_kernel<<<ctas, 256, 0, s>>>(sink, iters, 0.999f, 1e-3f);
+  RAMP_LAUNCH_OK();
+  RAMP_CUDA_OK(cudaEventRecord(e1, s));
+  RAMP_CUDA_OK(cudaEventSynchronize(e1));
+  float ms = 0.f;
+  RAMP_CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *tflops_host = (float)((double)ctas * 256.0 * iters * 8.0 * 2.0 / (ms * 1e-3) / 1e12);
+  return 0;
+}
 
 size_t ramp_cloud_packed_points(int P) { return (size_t)((P + NN_TILE - 1) / NN_TILE) * NN_TILE; }
 

@@ -6,9 +6,9 @@
 // * A rows are (sample, position) pairs of a channels-last activation; the tile for one tap is a 4-D
 //   TMA box (64 channels, 1 parity, L_out positions, 128/L_out samples) whose position coordinate is
 //   shifted by the tap, so conv padding is TMA out-of-bounds zero fill (no im2col, no halo code).
-// * Operands are bf16 hi/lo planes (value = hi + lo).  precision==3 issues hi*hi + hi*lo + lo*hi
-//   into the same fp32 TMEM accumulator (fp32-equivalent products, error ~2^-17); precision==1 issues
-//   hi*hi only.
+// * Operands are 16-bit hi/lo planes (value = hi + lo; fp16 + fp16 by default, bf16 + bf16 with
+//   -DRAMP_PLANES_FP16=0, see common.cuh).  precision==3 issues hi*hi + hi*lo + lo*hi into the same fp32 TMEM
+//   accumulator (fp32-equivalent products); precision==1 issues hi*hi only.
 // * Persistent: one CTA per SM walks tiles (n fastest, so co-running CTAs share A tiles in L2).  The
 //   accumulator is double buffered in TMEM (2 x BN columns), so the epilogue of tile i overlaps the
 //   MMAs of tile i+1; the TMA producer runs ahead across tile boundaries through the smem ring.
@@ -578,12 +578,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
     // ---------------- MMA issuer ----------------
     if (lane == 0) {
       // instruction descriptor: D = f32 (bit 4), A format bits [7,10), B format bits [10,13) (0 = f16, 1 = bf16), both
-      // K-major, N = BN, M = 128.  idesc_ab: a = format of the A plane, b = format of the B plane of that product.
+      // K-major, N = BN, M = 128.  A and B of one MMA must share a format (a mixed f16 x bf16 descriptor is an illegal
+      // instruction on B200).
       const uint32_t idesc0 = (1u << 4) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-#if RAMP_HI_FP16
-      const uint32_t idesc_lh = idesc0 | (1u << 7), idesc_hl = idesc0 | (1u << 10), idesc_hh = idesc0;   // hi planes: fp16
+#if RAMP_PLANES_FP16
+      const uint32_t idesc_lh = idesc0, idesc_hl = idesc0, idesc_hh = idesc0;                 // all planes fp16
 #else
-      const uint32_t idesc_lh = idesc0 | (1u << 7) | (1u << 10), idesc_hl = idesc_lh, idesc_hh = idesc_lh;
+      const uint32_t idesc_lh = idesc0 | (1u << 7) | (1u << 10), idesc_hl = idesc_lh, idesc_hh = idesc_lh;   // all bf16
 #endif
       int it = 0, lt = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {

@@ -31,7 +31,7 @@ struct StepArgs {
   float* out;            // x_{t-1} (may alias x)
   float* x0_out;         // optional clamped x0
   float* eps_out;        // optional combined eps
-  int mode;              // 0 = DDPM step, 1 = DDIM step, 2 = x0 only
+  int mode;              // 0 = DDPM step, 1 = DDIM step, 2 = x0 only, 3 = x + sigma * noise * noise_scale only
   int predict_epsilon;
 };
 
@@ -56,6 +56,13 @@ __global__ void __launch_bounds__(256) step_kernel(StepArgs a) {
     const size_t inner = i - (size_t)b * hd;
     const int h = (int)(inner / a.D);
     const float x = a.x[i];
+    if (a.mode == 3) {   // noise half of a DDPM step whose mean went through the APF first (diffusion_model_static.py:172-181)
+      float r = x;
+      if (a.noise) r = __fadd_rn(r, __fmul_rn(__fmul_rn(a.sigma, a.noise[i]), a.noise_scale));
+      if (a.pin_mask && a.pin_mask[h]) r = a.pin_val[(size_t)b * a.pin_bstride + inner];
+      a.out[i] = r;
+      continue;
+    }
     const float e = combine_eps(a, b, inner);
     float x0 = a.predict_epsilon ? __fsub_rn(__fmul_rn(a.sqrt_recip, x), __fmul_rn(a.sqrt_recipm1, e)) : e;
     x0 = fminf(fmaxf(x0, -1.f), 1.f);
@@ -155,9 +162,9 @@ using namespace ramp;
 extern "C" {
 
 int ramp_step(const ramp_step_args* u, void* stream) {
-  RAMP_CHECK(u && u->x && u->eps && (u->out || u->mode == 2), "ramp_step: null argument");
-  RAMP_CHECK(u->G >= 1 && u->G <= 8, "ramp_step: 1..8 conditional groups");
-  RAMP_CHECK(u->mode >= 0 && u->mode <= 2, "ramp_step: mode must be 0 (ddpm), 1 (ddim) or 2 (x0 only)");
+  RAMP_CHECK(u && u->x && (u->eps || u->mode == 3) && (u->out || u->mode == 2), "ramp_step: null argument");
+  RAMP_CHECK(u->mode == 3 || (u->G >= 1 && u->G <= 8), "ramp_step: 1..8 conditional groups");
+  RAMP_CHECK(u->mode >= 0 && u->mode <= 3, "ramp_step: mode must be 0 (ddpm), 1 (ddim), 2 (x0 only) or 3 (noise only)");
   StepArgs a{};
   a.x = u->x; a.eps = u->eps; a.eps_bstride = u->eps_bstride; a.eps_gstride = u->eps_gstride;
   a.B = u->B; a.H = u->H; a.D = u->D; a.G = u->G;

@@ -41,14 +41,14 @@ const float* UnetEngine::P(const std::string& name, size_t numel) {
 
 // dst[t][noff + n][koff + k] = src[t*st + n*sn + k*sk]
 __global__ void pack_weight_kernel(const float* __restrict__ src, bf16* hi, bf16* lo, int T, int Nd, int Kd, int Ns,
-                                   int Ks, long st, long sn, long sk, int noff, int koff) {
+                                   int Ks, long st, long sn, long sk, int noff, int koff, float scale) {
   const long total = (long)T * Ns * Ks;
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int k = (int)(i % Ks);
     const int n = (int)((i / Ks) % Ns);
     const int t = (int)(i / ((long)Ks * Ns));
     bf16 h, l;
-    split_bf16(src[t * st + n * sn + k * sk], h, l);
+    split_bf16(src[t * st + n * sn + k * sk] * scale, h, l);
     const size_t o = ((size_t)t * Nd + noff + n) * Kd + koff + k;
     hi[o] = h;
     lo[o] = l;
@@ -56,7 +56,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ src, bf16* hi, bf16
 }
 
 int UnetEngine::pack(PackedW& w, const std::string& name, int T, int Nd, int Kd, int Ns, int Ks, long st, long sn,
-                     long sk, int noff, int koff, bool alloc, long src_off, size_t full_numel) {
+                     long sk, int noff, int koff, bool alloc, long src_off, size_t full_numel, float scale) {
   if (alloc) {
     const size_t n = (size_t)T * Nd * Kd;
     w.hi = (bf16*)dev_alloc(n * 2);
@@ -70,7 +70,7 @@ int UnetEngine::pack(PackedW& w, const std::string& name, int T, int Nd, int Kd,
   const long total = (long)T * Ns * Ks;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 1184) blocks = 1184;
-  pack_weight_kernel<<<blocks, 256>>>(src, w.hi, w.lo, T, Nd, Kd, Ns, Ks, st, sn, sk, noff, koff);
+  pack_weight_kernel<<<blocks, 256>>>(src, w.hi, w.lo, T, Nd, Kd, Ns, Ks, st, sn, sk, noff, koff, scale);
   RAMP_LAUNCH_OK();
   return 0;
 }
@@ -78,18 +78,19 @@ int UnetEngine::pack(PackedW& w, const std::string& name, int T, int Nd, int Kd,
 static inline int pad16(int c) { return (c + 15) / 16 * 16; }
 
 // Conv1d weight [cout, cin, kw]  (transposed: ConvTranspose1d weight [cin, cout, kw]); Linear = kw 1.
-int UnetEngine::load_conv(ConvW& c, const std::string& prefix, int cin, int cout, int kw, bool transposed) {
+// bscale multiplies the input-gradient packing only (the loss scale of the backward sweep enters through final_conv.1).
+int UnetEngine::load_conv(ConvW& c, const std::string& prefix, int cin, int cout, int kw, bool transposed, float bscale) {
   c.cin = cin; c.cout = cout; c.kw = kw;
   const int cinp = pad16(cin), coutp = pad16(cout);
   int rc;
   if (!transposed) {
     rc = pack(c.f, prefix + "weight", kw, coutp, cinp, cout, cin, 1, (long)cin * kw, kw);
     if (rc) return rc;
-    rc = pack(c.b, prefix + "weight", kw, cinp, coutp, cin, cout, 1, kw, (long)cin * kw);
+    rc = pack(c.b, prefix + "weight", kw, cinp, coutp, cin, cout, 1, kw, (long)cin * kw, 0, 0, true, 0, 0, bscale);
   } else {
     rc = pack(c.f, prefix + "weight", kw, coutp, cinp, cout, cin, 1, kw, (long)cout * kw);
     if (rc) return rc;
-    rc = pack(c.b, prefix + "weight", kw, cinp, coutp, cin, cout, 1, (long)cout * kw, kw);
+    rc = pack(c.b, prefix + "weight", kw, cinp, coutp, cin, cout, 1, (long)cout * kw, kw, 0, 0, true, 0, 0, bscale);
   }
   if (rc) return rc;
   c.f.K = cinp; c.b.K = coutp;
@@ -221,7 +222,9 @@ int UnetEngine::finalize(cudaStream_t s) {
     if (!rc) rc = load_conv(up_conv_[j], p + "4.conv.", cout, cout, 4, true);
   }
   if (!rc) rc = load_conv(final_c5_, "final_conv.0.block.0.", 32, 32, 5);
-  if (!rc) rc = load_conv(final_c1_, "final_conv.1.", 32, D, 1);
+  // the backward sweep starts at final_conv.1's input gradient: scaling that packing by RAMP_GRAD_SCALE (a power of two)
+  // scales every gradient of the sweep exactly; run() divides it out when it extracts eps
+  if (!rc) rc = load_conv(final_c1_, "final_conv.1.", 32, D, 1, false, RAMP_GRAD_SCALE);
   if (rc) return rc;
   final_g_ = P("final_conv.0.block.2.weight", 32); final_b_ = P("final_conv.0.block.2.bias", 32);
 

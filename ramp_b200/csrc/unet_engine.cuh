@@ -89,8 +89,8 @@ class UnetEngine {
   // helpers
   const float* P(const std::string& name, size_t numel);
   int pack(PackedW& w, const std::string& name, int T, int Nd, int Kd, int Ns, int Ks, long st, long sn, long sk,
-           int noff = 0, int koff = 0, bool alloc = true, long src_off = 0, size_t full_numel = 0);
-  int load_conv(ConvW& c, const std::string& prefix, int cin, int cout, int kw, bool transposed = false);
+           int noff = 0, int koff = 0, bool alloc = true, long src_off = 0, size_t full_numel = 0, float scale = 1.f);
+  int load_conv(ConvW& c, const std::string& prefix, int cin, int cout, int kw, bool transposed = false, float bscale = 1.f);
   int load_res(ResW& r, const std::string& prefix, int cin, int cout, int cin_true);
   int load_st(STW& st, const std::string& prefix, int C);
   void* dev_alloc(size_t bytes);

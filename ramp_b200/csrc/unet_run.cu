@@ -18,11 +18,11 @@ static const GemmTap TAP_UP_F_EVEN[2] = {{0, 0, 1}, {0, -1, 3}};
 static const GemmTap TAP_UP_F_ODD[2] = {{0, 1, 0}, {0, 0, 2}};
 static const GemmTap TAP_UP_B[4] = {{1, -1, 0}, {0, 0, 1}, {1, 0, 2}, {0, 1, 3}};
 
-__global__ void extract_kernel(const float* __restrict__ src, int n_rows, int H, int D, float* __restrict__ dst) {
+__global__ void extract_kernel(const float* __restrict__ src, int n_rows, int H, int D, float* __restrict__ dst, float scale) {
   const size_t total = (size_t)n_rows * H * D;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const size_t row = i / D;
-    dst[i] = src[row * 16 + (i - row * D)];
+    dst[i] = src[row * 16 + (i - row * D)] * scale;
   }
 }
 
@@ -385,12 +385,13 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
   }
   const int eb = (int)((((size_t)n_rows * H * D + 255) / 256) > 1184 ? 1184 : (((size_t)n_rows * H * D + 255) / 256));
   if (!dry_ && f_out) {
-    extract_kernel<<<eb, 256, 0, s>>>(fo, n_rows, H, D, f_out);
+    extract_kernel<<<eb, 256, 0, s>>>(fo, n_rows, H, D, f_out, 1.f);
     RAMP_LAUNCH_OK();
   }
   if (!dry_ && !eps_out) return 0;
 
   // ------------------------------- backward: d(0.5*sum f^2)/dx, seed = f -------------------------------
+  // (every gradient below carries the factor RAMP_GRAD_SCALE that final_c1_.b was packed with)
   float* dh = allocf(M * 32);
   {
     Act fa; fa.hi = fos.hi; fa.lo = fos.lo; fa.lds = 16;
@@ -457,7 +458,7 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
       dy = Act(); dy.C = Cp; dy.f = f; dy.ldf = Cp; dy.hi = sp.hi; dy.lo = sp.lo; dy.lds = Cp;
       L *= 2;
     } else if (!dry_) {
-      extract_kernel<<<eb, 256, 0, s>>>(d0.f, n_rows, H, D, eps_out);
+      extract_kernel<<<eb, 256, 0, s>>>(d0.f, n_rows, H, D, eps_out, 1.f / RAMP_GRAD_SCALE);   // undo the loss scale
       RAMP_LAUNCH_OK();
     }
   }

@@ -176,7 +176,7 @@ class _DiffusionBase(nn.Module):
         raise NotImplementedError
 
     # ------------------------------------------------------------------ one reverse step
-    def _ddpm_step(self, x, t, obstacle_pts, noise, noise_scale, compose=False, pins=None, out=None):
+    def _ddpm_step(self, x, t, obstacle_pts, noise, noise_scale, compose=False, pins=None, out=None, forward_t=None):
         groups, w = self._groups_and_weights(obstacle_pts, compose)
         self._ensure_engine(x.shape[1], x.shape[0] * (groups.shape[0] + 1))
         G = self._set_scenes(groups)
@@ -299,6 +299,28 @@ class StaticGaussianDiffusionModel(_DiffusionBase):
         w = list(self.compose_weights) + [self.compose_weights[-1]] * max(0, G - len(self.compose_weights))
         return g, w[:G]
 
+    # DDPM step with the potential field on the posterior mean --------------------------------------
+    ddpm_apf_threshold, ddpm_apf_strength, ddpm_apf_window, ddpm_apf_after = 0.07, 0.1, 5, 20    # :172-176
+
+    def _ddpm_apf_active(self, compose, forward_t):
+        """:172 — only the non-compose p_mean_variance has the branch (p_mean_variance_compose, :188-229, does not)."""
+        return self.APF and not compose and forward_t is not None and forward_t > self.ddpm_apf_after
+
+    def _ddpm_step(self, x, t, obstacle_pts, noise, noise_scale, compose=False, pins=None, out=None, forward_t=None):
+        """One DDPM step.  With `use_apf` and DDPM sampling the reference pushes the posterior MEAN through `avoidance`
+        (threshold 0.07, strength 0.1, window 5) for forward_t > 20, then adds the noise (:172-181, sample_functions.py:32-48);
+        here: fused step without noise -> nearest point -> windowed push -> noise + inpainting (ramp_step mode 3)."""
+        if not self._ddpm_apf_active(compose, forward_t):
+            return super()._ddpm_step(x, t, obstacle_pts, noise, noise_scale, compose=compose, pins=pins, out=out)
+        mean = super()._ddpm_step(x, t, obstacle_pts, None, noise_scale, compose=compose, pins=None)
+        cloud = self._clouds.get(obstacle_pts)
+        dist, idx = cloud.query(mean, self.ddpm_apf_threshold)
+        pushed = ops.apf_static(mean, cloud, dist, idx, self.ddpm_apf_threshold, self.ddpm_apf_strength,
+                                self.ddpm_apf_window)
+        out = torch.empty_like(x) if out is None else out
+        s = self._sched()
+        return ops.step(pushed, None, 1, [0.0], out, 3, pins=pins, sigma=s['sigma'][t], noise_scale=noise_scale, noise=noise)
+
     # reference-shaped entry points ------------------------------------------------------------
     def p_mean_variance(self, x, hard_conds, context, t, traj_normalized=None, obstacle_pts=None, forward_t=None,
                         compose=False):
@@ -309,6 +331,11 @@ class StaticGaussianDiffusionModel(_DiffusionBase):
         mean, var, logvar = self.q_posterior(x_start=x0, x_t=x, t=t)
         if self.ddim:
             return mean, var, logvar, x0, eps
+        if self._ddpm_apf_active(compose, forward_t):                      # :172-181
+            cloud = self._clouds.get(obstacle_pts)
+            dist, idx = cloud.query(mean.contiguous(), self.ddpm_apf_threshold)
+            mean = ops.apf_static(mean.contiguous(), cloud, dist, idx, self.ddpm_apf_threshold, self.ddpm_apf_strength,
+                                  self.ddpm_apf_window)
         return mean, var, logvar
 
     def p_mean_variance_compose(self, x, hard_conds, context, t, traj_normalized=None, obstacle_pts=None,
@@ -337,7 +364,7 @@ class StaticGaussianDiffusionModel(_DiffusionBase):
                 noise = torch.randn_like(x)
                 ns = 1.0 if noise_fn is None else float(noise_fn(i))
                 self._ddpm_step(x, ti, obstacle_pts, noise if ti > 0 else None, ns, compose=self.compose, pins=pins,
-                                out=chain[k + 1])
+                                out=chain[k + 1], forward_t=k)
             else:   # foreign sample_fn: keep the reference protocol
                 t = make_timesteps(B, i, device)
                 xn, _ = sample_fn(self, x, hard_conds, context, t, traj_normalized=traj_normalized,
@@ -349,8 +376,17 @@ class StaticGaussianDiffusionModel(_DiffusionBase):
             return x, chain.transpose(0, 1)
         return x
 
+    def set_apf_cloud(self, points):
+        """Extension (no reference counterpart): use `points` ([P, d] tensor or an `ops.CloudIndex`) as the potential
+        field's cloud instead of the conditioning cloud.  The reference derives the APF cloud from `obstacle_pts`
+        (:304-311), which the scene encoder hard-wires to 6 x 64 points (obstacle_encoder.py:95); BASELINE's dense clouds
+        (4 k ... 1 M points) can only enter this way.  `None` restores the reference behaviour."""
+        self._apf_override = None if points is None else (points if isinstance(points, ops.CloudIndex) else ops.CloudIndex(points))
+
     def _apf_cloud(self, obstacle_pts):
         """:304-311 — compose uses the first six obstacles of set 0 and the first four of set 1."""
+        if getattr(self, '_apf_override', None) is not None:
+            return self._apf_override
         if self.compose:
             key = (obstacle_pts.data_ptr(), tuple(obstacle_pts.shape), obstacle_pts._version)
             if getattr(self, '_apf_key', None) != key:

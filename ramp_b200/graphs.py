@@ -19,6 +19,28 @@ from . import ops
 from ._lib import RampError
 
 
+class _EngineGuard:
+    """A captured graph holds raw pointers into the score network's workspace arena, packed weights and scene constants.
+    Rebuilding the engine (a larger batch, `prepare()`, `load_state_dict()`, `.to()`, `release_engine()`) frees them, so
+    every replay first checks that the engine it was captured against is still the live one and raises otherwise; the
+    scene constants are re-established before the replay if an eager call conditioned the engine on another cloud."""
+
+    def _bind(self, model):
+        unet = model.model
+        self._unet = unet
+        self._engine_id = (unet._engine.value if unet._engine is not None else None, unet._engine_key)
+        # tensors the captured kernels read that were allocated OUTSIDE the capture (regular allocator pool): keep them alive
+        self._keep = [list(model._r2s.values()), getattr(model, "_groups_cache", None)]
+
+    def _check_engine(self):
+        unet = self._unet
+        now = (unet._engine.value if unet._engine is not None else None, unet._engine_key)
+        if now != self._engine_id:
+            raise RampError("this CUDA graph was captured against a score-network engine that has since been rebuilt or "
+                            "released (batch grew, prepare() / load_state_dict() / .to() / release_engine()): its workspace "
+                            "pointers are stale — capture a new graph")
+
+
 def _capture(fn, warmup=2):
     """Warm up on a side stream (lazy initialisation, autotuned launch attributes, scene cache), then capture."""
     s = torch.cuda.Stream()
@@ -34,7 +56,7 @@ def _capture(fn, warmup=2):
     return g, out
 
 
-class DdpmLoopGraph:
+class DdpmLoopGraph(_EngineGuard):
     """Graph of one complete DDPM sampling (x_T draw, T reverse steps, inpainting) for a fixed batch."""
 
     def __init__(self, model, batch, horizon, hard_conds, obstacle_pts, noise_scale=0.5, extra_steps=0):
@@ -58,18 +80,23 @@ class DdpmLoopGraph:
             for k, t in enumerate(steps):
                 noise = torch.randn((B, H, D), device=dev)
                 model._ddpm_step(self.chain[k], t, self.cloud, noise if t > 0 else None, noise_scale,
-                                 compose=model.compose, pins=self.pins, out=self.chain[k + 1])
+                                 compose=model.compose, pins=self.pins, out=self.chain[k + 1], forward_t=k)
             return self.chain
 
         self.graph, _ = _capture(loop)
+        self._bind(model)
 
     def replay(self):
-        """Runs the captured loop on the current stream; returns the chain [T+1, B, H, D] (static buffer)."""
+        """Runs the captured loop on the current stream; returns the chain [T+1, B, H, D] (static buffer).
+        Raises RampError if the engine was rebuilt since the capture; re-encodes the graph's own cloud first if an
+        eager call conditioned the engine on a different one in between."""
+        self._check_engine()
+        self.model._set_scenes(self.model._groups_and_weights(self.cloud, self.model.compose)[0])
         self.graph.replay()
         return self.chain
 
 
-class ReplanGraph:
+class ReplanGraph(_EngineGuard):
     """Graph of one replan tick of DynamicGaussianDiffusionModel for tick index k (= number of executed states - 1).
 
     Static inputs (update in place, then `replay()`): `x_clean` [H, D] current plan, `history` [k+1, D] executed states,
@@ -77,7 +104,11 @@ class ReplanGraph:
     with `stream_conditioning` — `cloud`, the U-Net's conditioning cloud.  With `pursuer` (a `pursuit.DevicePursuer`) the
     first node of the graph moves the pursuer toward `history[k]` and rewrites `disc_points` / `disc_center` on the
     device, so a replay needs no host-side environment step at all.
-    Outputs (static): `batch` [B, H, D], `sel` [8] (ramp_select_best), `best` [H, D]."""
+    Outputs (static): `batch` [B, H, D], `sel` [8] (ramp_select_best), `best` [H, D].
+    As in the eager tick (dynamic.py, diffusion_model_dynamic.py:592-596) the pursuer disc joins the cost cloud only while
+    the current state `history[k]` is within `distance_threshold_pred` of the pursuer (decided on the device).  When no
+    trajectory survives the collision test, `sel[0]` is -1 and `best` is filled with NaN — the reference then re-plans
+    from scratch (:596-603): `replay(sync=True)` returns None in that case, like `compute_trajectory_costs`."""
 
     def __init__(self, model, batch, horizon, k, obstacle_pts, static_points, disc_points, cost_static_points,
                  collision_threshold=None, stream_conditioning=False, pursuer=None):
@@ -125,6 +156,9 @@ class ReplanGraph:
         self.terms = torch.empty(B, 3, device=dev)
         self.sel = torch.empty(8, device=dev)
         self.best = torch.empty(H, D, device=dev)
+        self._far = torch.full_like(self.disc_points, 1.0e6)          # "no pursuer in the cost cloud"
+        self._nan = torch.full((H, D), float("nan"), device=dev)
+        near_thr = model.distance_threshold_pred
 
         def tick():
             # pins from the static inputs (device-side copies: part of the graph)
@@ -137,7 +171,8 @@ class ReplanGraph:
                 model._scene_sig = None                               # encode `cloud` again on this replay
             if pursuer is not None:                                   # update_centers + generate_sphere_points, one launch
                 pursuer.tick(self.history[k], points=self.disc_points, center_out=self.disc_center)
-            self._cost_disc.copy_(self.disc_points)
+            near = (self.history[k, :2] - self.disc_center).norm() < near_thr          # :592-595
+            self._cost_disc.copy_(torch.where(near, self.disc_points, self._far))
             self.field.dynamic_cloud.repack()
             self.cost_cloud.repack()
             model._tick_batch(self.x_clean, None, k, k, B, self.cloud, self.field, out=self.batch, pins_q=self.pins_q,
@@ -145,7 +180,7 @@ class ReplanGraph:
             ops.cost_terms(self.batch, self.cost_cloud, thr, terms=self.terms)
             ops.select_best(self.terms, out=self.sel)
             idx = self.sel[0].clamp(min=0).long().reshape(1)
-            self.best.copy_(self.batch.index_select(0, idx)[0])
+            self.best.copy_(torch.where(self.sel[0] >= 0, self.batch.index_select(0, idx)[0], self._nan))
             self.best[0, 2:] = 0.0                                    # diffusion_model_dynamic.py:609
             return self.best
 
@@ -154,7 +189,18 @@ class ReplanGraph:
         if saved is not None:                                         # the warm-up passes moved the pursuer: put it back
             pursuer.center.copy_(saved[0])
             pursuer.counter.copy_(saved[1])
+        self._bind(model)
+        self._streams = stream_conditioning
 
-    def replay(self):
+    def replay(self, sync=False):
+        """Runs the tick on the current stream and returns `best` (static buffer).  sync=True reads the selection back and
+        returns None when no trajectory was collision-free (the caller then takes the replan-from-scratch path)."""
+        self._check_engine()
+        if not self._streams:        # scene constants are not graph nodes: make sure they are still this graph's cloud
+            self.model._set_scenes(self.model._groups_and_weights(self.cloud, False)[0])
         self.graph.replay()
+        if self._streams:            # the replay re-encoded `cloud` behind the host-side cache's back
+            self.model._scene_sig = None
+        if sync and int(self.sel[0].item()) < 0:
+            return None
         return self.best

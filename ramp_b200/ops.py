@@ -54,11 +54,12 @@ class Pins:
 def step(x, eps, G, weights, out, mode, pins=None, eps_bstride=None, eps_gstride=1, sqrt_recip=0.0, sqrt_recipm1=0.0,
          coef1=0.0, coef2=0.0, sigma=0.0, noise_scale=1.0, noise=None, sa_t=0.0, sb_t=1.0, sa_prev=0.0, sdir=0.0,
          x0_out=None, eps_out=None, predict_epsilon=True):
-    """One fused reverse step (mode 0 DDPM / 1 DDIM / 2 x0-only).  eps rows: (b, g) -> b*eps_bstride + g*eps_gstride."""
+    """One fused reverse step (mode 0 DDPM / 1 DDIM / 2 x0-only / 3 noise-only: eps may be None).
+    eps rows: (b, g) -> b*eps_bstride + g*eps_gstride."""
     _need_cuda(x, eps, out, noise, x0_out, eps_out)
     B, H, D = x.shape
     a = StepArgs()
-    a.x, a.eps = x.data_ptr(), eps.data_ptr()
+    a.x, a.eps = x.data_ptr(), (0 if eps is None else eps.data_ptr())
     a.eps_bstride, a.eps_gstride = (G + 1) if eps_bstride is None else eps_bstride, eps_gstride
     a.B, a.H, a.D, a.G = B, H, D, G
     for i, w in enumerate(weights):

@@ -30,7 +30,8 @@ def ddpm_sample_fn(model, x, hard_conds, context, t, traj_normalized=None, obsta
     ti = max(t_single, 0)
     noise = torch.randn_like(x)
     noise_std = 1.0 if noise_std_extra_schedule_fn is None else float(noise_std_extra_schedule_fn(t_single))
-    out = model._ddpm_step(x, ti, obstacle_pts, noise if ti > 0 else None, noise_std, compose=bool(compose))
+    out = model._ddpm_step(x, ti, obstacle_pts, noise if ti > 0 else None, noise_std, compose=bool(compose),
+                           forward_t=forward_t)
     return out, None
 
 

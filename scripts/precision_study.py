@@ -13,6 +13,9 @@ can carry (value = hi + lo), products and sums in fp32 as in the tensor-core pat
               kind::f16 takes the operand format per MMA, so hi*hi / hi*lo / lo*hi stay three MMAs on the same bytes
   fp16+bf16/attn-bf16   as fp16+bf16 for every Linear / conv, but the attention products (QK^T, PV and their gradients)
               keep bf16 + bf16 operands (the mma.sync attention kernels re-split what they load)
+  fp16+fp16   both planes fp16, residual stored as is (fp16 subnormals: absolute error <= 3e-8 per element): the variant the
+              hardware accepts — tcgen05.mma kind::f16 with A = f16, B = bf16 is an ILLEGAL INSTRUCTION on B200 (measured,
+              round 2), so every product must have same-format operands
   fp16+fp16s  both planes fp16, residual scaled by 2^11 before rounding (22 bits; needs a second accumulator or a scaled
               epilogue add, listed for reference)
 
@@ -41,6 +44,9 @@ def planes(x, scheme):
     if scheme == "fp16+bf16":
         hi = x.half().float()
         return hi + (x - hi).bfloat16().float()
+    if scheme == "fp16+fp16":             # both planes fp16, residual NOT scaled (fp16 subnormals carry it: abs error <= 3e-8)
+        hi = x.clamp(-65504.0, 65504.0).half().float()
+        return hi + (x - hi).half().float()
     if scheme == "fp16+fp16s":
         hi = x.half().float()
         return hi + ((x - hi) * 2048.0).half().float() / 2048.0
@@ -87,7 +93,7 @@ class rounded_operands:
         F.linear, F.conv1d, F.conv_transpose1d, torch.matmul = self.saved
 
 
-SCHEMES = ("fp32", "bf16+bf16", "fp16+bf16", "fp16+bf16/attn-bf16", "fp16+fp16s")
+SCHEMES = ("fp32", "bf16+bf16", "fp16+bf16", "fp16+bf16/attn-bf16", "fp16+fp16", "fp16+fp16s")
 
 
 def noise(seed, k, B=6):

@@ -45,7 +45,7 @@ def test_stage1_and_ticks_vs_reference(cuda):
     err = (x.cpu() - g["stage1_batch"]).abs().max().item()
     med = (x.cpu() - g["stage1_batch"]).abs().median().item()
     print("stage I (10 free-running DDIM steps) max err %.2e median %.2e" % (err, med))
-    assert err < 2e-3 and med < 1e-4       # free-running; the teacher-forced ticks below hold north_star's 1e-3
+    assert err < 1e-3 and med < 1e-4       # 10 free-running steps within north_star's 1e-3
     best, _, _, free, _ = compute_trajectory_costs(g["stage1_batch"].to(cuda), cloud, collision_threshold=0.02)
     assert (best.cpu() - g["stage1_best"]).abs().max() < 1e-6
     # stage II, teacher-forced on the reference's selected plans

@@ -9,14 +9,14 @@ pytestmark = pytest.mark.gpu
 
 
 def _hi_dtype():
-    """Plane layout of the loaded library (include/ramp_b200.h: ramp_plane_format): bf16 + bf16, or fp16 + bf16."""
+    """Plane layout of the loaded library (include/ramp_b200.h: ramp_plane_format): fp16 + fp16 (2) or bf16 + bf16 (0)."""
     from ramp_b200._lib import lib
-    return torch.float16 if int(lib().ramp_plane_format()) == 1 else torch.bfloat16
+    return torch.float16 if int(lib().ramp_plane_format()) == 2 else torch.bfloat16
 
 
 def _split(x):
     hi = x.clamp(-65504.0, 65504.0).to(_hi_dtype())
-    lo = (x - hi.float()).to(torch.bfloat16)
+    lo = (x - hi.float()).to(_hi_dtype())
     return hi.contiguous(), lo.contiguous()
 
 
@@ -33,7 +33,7 @@ def _gemm(a, w, taps, L_out, a_pstride=1, bias=None, bias_tab=None, row2scene=No
     out_rows = out_rows or n * o_L
     out = torch.zeros(out_rows, Nout, device=a.device)
     oh = torch.zeros(out_rows, Nout, device=a.device, dtype=_hi_dtype()) if want_split else None
-    ol = torch.zeros(out_rows, Nout, device=a.device, dtype=torch.bfloat16) if want_split else None
+    ol = torch.zeros(out_rows, Nout, device=a.device, dtype=_hi_dtype()) if want_split else None
     tp = (ctypes.c_int * (3 * len(taps)))(*[v for t in taps for v in t])
     check(lib().ramp_gemm(ptr(ah), ptr(al), n, L_in, ldA, K, a_pstride, L_out, len(taps), tp, ptr(wh), ptr(wl), Nout, Kw,
                           n_wt, ptr(bias), ptr(bias_tab), ptr(row2scene), ptr(residual), Nout, ptr(out), Nout,

@@ -175,8 +175,8 @@ def test_3d_ddpm25_vs_reference(cuda):
                                 sample_fn=ddpm_sample_fn, noise_std_extra_schedule_fn=lambda t: 0.5)
     d = (chain.cpu() - g["chain"]).abs()
     print("3d per-step max:", ["%.1e" % v for v in d.amax(dim=(1, 2, 3)).tolist()])
-    # one trajectory (384 numbers), CFG weights 6.75 / -5.75 amplify the network's ~5e-5 split-bf16 error 12x:
-    # free-running is a statistical bound, the per-step bound is teacher-forced below.
+    # one trajectory (384 numbers), CFG weights 6.75 / -5.75 amplify the network's rounding 12x; the run from x_T also
+    # carries the clamped first step (4602x), so it is reported, and the bounds below start after that step.
     print("3d free-running final: frac>1e-3 %.3f median %.1e" % ((d[-1] > 1e-3).float().mean(), d[-1].median()))
     noise = [torch.randn((1, 64, 6), generator=torch.Generator("cpu").manual_seed(g["noise_seed"] + 1 + k)) for k in range(25)]
     from ramp_b200 import ops
@@ -194,9 +194,7 @@ def test_3d_ddpm25_vs_reference(cuda):
         x = step(k, x)
     dfree = (x.cpu() - g["chain"][-1]).abs()
     print("3d free-running from step 1: final max %.1e median %.1e" % (dfree.max(), dfree.median()))
-    # CFG weights 6.75 / -5.75 amplify the network's ~5e-5 error 12x and sqrt_recipm1[23] = 4: isolated entries near the
-    # clamp can exceed 1e-3 (teacher-forced bound below is 2e-3); the bulk must sit well inside the tolerance.
-    assert (dfree > 1e-3).float().mean() < 0.05 and dfree.median() < 5e-4 and dfree.max() < 5e-3
+    assert dfree.max() < 1e-3                     # north_star's tolerance, free-running, every waypoint
 
     per = _teacher_forced(m, g["chain"], step)
     print("3d teacher-forced max:", ["%.1e" % e.max() for e in per])
@@ -204,7 +202,7 @@ def test_3d_ddpm25_vs_reference(cuda):
         if k == 0:
             assert (e > 1e-3).float().mean() < 0.02
         else:
-            assert e.max() < 2e-3 and (e > 1e-3).float().mean() < 0.01, (k, e.max())
+            assert e.max() < 1e-3, (k, e.max())
 
 
 def test_3d_batch_equals_looped_singles(cuda):

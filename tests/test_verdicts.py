@@ -7,8 +7,8 @@ thresholds 0.02 / 0.05 and the best-of-N index (mpd/models/diffusion_models/cost
 
 The first reverse step amplifies eps 4602x before the clamp, so a free run from x_T can flip isolated
 clamped entries; like tests/test_sampler_gpu.py the strict comparison therefore starts from the reference's state after that
-step (x1) and runs the remaining 24 steps freely: EVERY verdict identical, waypoints within 1e-3 for >= 95 % of the
-trajectories and within 2e-3 for all (see FREE_RUN_CAP).  A verdict is exempt
+step (x1) and runs the remaining 24 steps freely: EVERY verdict identical and EVERY trajectory's waypoints within
+north_star's 1e-3 (FREE_RUN_CAP).  A verdict is exempt
 only if the reference's own verdict on its own trajectory flips when the boxes / the distance threshold move by 2e-3
 (counted and bounded; the disagreements found are reported all at once).  The full
 run from x_T is compared as well and its disagreements are bounded."""
@@ -20,10 +20,10 @@ import torch
 
 G = os.path.join(os.path.dirname(__file__), "golden", "verdicts.pt")
 MARGIN = 2e-3
-# 24 chained steps amplify the per-step difference (teacher-forced steps are held to 1e-3 in tests/test_sampler_gpu.py):
-# measured on B200, 35 of the 36 trajectories end within 1e-3 of the reference and the worst at 1.04e-3; the oracle (same
-# torch operations as the reference) stays within 1e-3 on all.  Hard cap 2e-3, and at least 95 % within 1e-3.
-FREE_RUN_CAP = 2e-3
+# north_star's waypoint tolerance, on the FREE-RUNNING 24 steps, for every trajectory.  Round 1's bf16 + bf16 operand planes
+# measured 4.4e-4 median / 1.04e-3 max here; the fp16 + fp16 planes with a loss-scaled backward sweep (csrc/common.cuh)
+# sit at the fp32 noise floor (profiles/r2_*).
+FREE_RUN_CAP = 1e-3
 DEVIATIONS = {}
 
 
@@ -154,7 +154,7 @@ def test_product_verdicts_identical_on_the_fixed_seed_set(cuda, gold):
     print("per-trajectory deviations:", ["%.1e" % v for v in dev.tolist()])
     assert not problems, problems
     assert exempt == 0                            # no verdict of this fixture is borderline
-    assert (dev <= 1e-3).float().mean().item() >= 0.95
+    assert dev.max().item() <= FREE_RUN_CAP         # all 36, not a quantile
 
 
 @pytest.mark.gpu
