@@ -156,6 +156,8 @@ def run_ours(args):
     dist, world, rank, local, dev = _dist_setup()
     B = args.batch
     model = build_model(dev, max_rows=args.max_rows)
+    if args.eager:
+        model.cuda_graph = False
     groups_host = synthetic_cloud_2d(seed=5, groups=G).pin_memory()                # [6, 6, 64, 2]
     hc_host = {0: torch.tensor([-0.8, -0.8, 0.0, 0.0]).pin_memory(), H - 1: torch.tensor([0.8, 0.8, 0.0, 0.0]).pin_memory()}
     groups = groups_host.to(dev)
@@ -210,12 +212,16 @@ def run_ours(args):
     gather_mean = None
     if gather_ms:
         gather_mean = sum(a.elapsed_time(b) for a, b in gather_ms) / len(gather_ms)
-    # per-kernel-class device time of one more identical step (CUDA events around every engine launch)
+    # per-kernel-class device time of one more identical step (CUDA events around every engine launch); the events are
+    # recorded by the host-side launch code, so this step runs the eager loop, not the captured graph
+    graph_mode = model.cuda_graph
+    model.cuda_graph = False
     model.model.profile(True)
     resident_step()
     if args.dump_launches and rank == 0:
         model.model.profile_dump(args.dump_launches)
     prof_ms, prof_n = model.model.profile(False, fetch=True)
+    model.cuda_graph = graph_mode
 
     extras = {}
     if rank == 0 and not args.no_sections:
@@ -262,6 +268,7 @@ def run_ours(args):
                        "diffusion_steps": T, "cond_groups": G, "network_rows_per_step": B * (G + 1),
                        "cloud": "6 groups x 6 obstacles x 64 points", "weights": "random-init (seeded)",
                        "l2": "activation working set per network call (>10 GB) exceeds L2; no flush needed",
+                       "loop": "eager" if args.eager else "run_inference replays the captured 25-step loop (CUDA graph) from its third call on",
                        "sharding": "batch across ranks; all-gather of (free, length, smoothness) + select_best"},
             "e2e": {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": "trajectories/s",
                     "h2d_bytes_per_step": int(groups_host.numel() * 4 + 2 * D * 4), "d2h_bytes_per_step": int(B * H * D * 4 + 32)},
@@ -909,6 +916,7 @@ def main():
     ap.add_argument("--sweep-total", type=int, default=SWEEP_TOTAL, help="--workload sweep: trajectories over all ranks")
     ap.add_argument("--max-rows-sweep", type=int, default=8192, help="network rows per engine call of the sweep (48 GB workspace)")
     ap.add_argument("--dump-launches", default="", help="write the per-launch CUDA-event CSV of one profiled step here")
+    ap.add_argument("--eager", action="store_true", help="headline: keep run_inference on the eager loop (no CUDA-graph fast path)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -25,6 +25,9 @@ int ramp_version(void);
 int ramp_plane_format(void);
 /* number of CUDA kernels this library has launched in this process */
 unsigned long long ramp_launch_count(void);
+/* a CUDA-graph replay launches the kernels that were counted once, while the graph was captured: the host-side owner of
+ * the graph (ramp_b200/graphs.py) adds that number per replay so that the counter keeps meaning "kernels launched" */
+void ramp_launch_count_add(unsigned long long n);
 
 /* ---- low-level dense contraction (building block of the score network; exposed for tests) ----
  * D[(n,l), :] = sum_t A[n, par_t + a_pstride*(l + joff_t), 0:K] . W[wtap_t, :, 0:K]^T (+bias +bias_tab[row2scene[n]] +residual)

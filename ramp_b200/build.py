@@ -24,17 +24,20 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False, planes_bf16=False):
+def build(force=False, verbose=False, planes_bf16=False, variant=None, defines=()):
     """planes_bf16: round 1's operand-plane format (bf16 + bf16, csrc/common.cuh) as a SECOND library,
     libramp_b200_bf16.so, selected at run time with RAMP_B200_LIB=<that path> for A/B runs; the default library
     (fp16 + fp16 planes) is untouched."""
-    if os.environ.get("RAMP_B200_LIB") and not planes_bf16:
+    if planes_bf16:
+        variant, defines = "bf16", ("RAMP_PLANES_FP16=0",)
+    if os.environ.get("RAMP_B200_LIB") and not variant:
         return os.environ["RAMP_B200_LIB"]
-    if not force and not planes_bf16 and not needs_build():
+    if not force and not variant and not needs_build():
         return OUT
-    target = os.path.join(HERE, "libramp_b200_bf16.so") if planes_bf16 else OUT
-    bdir = os.path.join(HERE, "build", "bf16") if planes_bf16 else os.path.join(HERE, "build")
-    extra = ["-DRAMP_PLANES_FP16=0"] if planes_bf16 else []
+    # variant: a SECOND library libramp_b200_<variant>.so compiled with extra -D defines, for same-box A/B runs
+    target = os.path.join(HERE, "libramp_b200_%s.so" % variant) if variant else OUT
+    bdir = os.path.join(HERE, "build", variant) if variant else os.path.join(HERE, "build")
+    extra = ["-D" + d for d in defines]
     objs = []
     procs = []
     os.makedirs(bdir, exist_ok=True)
@@ -49,12 +52,16 @@ def build(force=False, verbose=False, planes_bf16=False):
         out, _ = p.communicate()
         if p.returncode != 0:
             raise RuntimeError("nvcc failed on %s:\n%s" % (src, out.decode()))
-    cmd = [NVCC, "-shared", "-cudart", "static", "-o", target] + objs + ["-ldl", "-lpthread", "-lrt"]
+    tmp = target + ".tmp"          # link beside the target, then rename: a snapshot never sees a half-written library
+    cmd = [NVCC, "-shared", "-cudart", "static", "-o", tmp] + objs + ["-ldl", "-lpthread", "-lrt"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout.decode())
+    os.replace(tmp, target)
     return target
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True, planes_bf16="--planes-bf16" in sys.argv))
+    var = sys.argv[sys.argv.index("--variant") + 1] if "--variant" in sys.argv else None
+    defs = tuple(a[2:] for a in sys.argv if a.startswith("-D"))
+    print(build(force="--force" in sys.argv, verbose=True, planes_bf16="--planes-bf16" in sys.argv, variant=var, defines=defs))

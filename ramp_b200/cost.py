@@ -15,8 +15,8 @@ def _cloud(obstacle_points):
     if c is None:
         if len(_clouds) > 16:
             _clouds.clear()
-        c = _clouds[key] = ops.CloudIndex(obstacle_points)
-    return c
+        c = _clouds[key] = (ops.CloudIndex(obstacle_points), obstacle_points)   # the key tensor stays alive with its entry
+    return c[0]
 
 
 def _terms(trajs, obstacle_points, collision_threshold):

@@ -28,6 +28,7 @@ const char* ramp_last_error(void) { return g_err.c_str(); }
 int ramp_version(void) { return 100; }
 int ramp_plane_format(void) { return RAMP_PLANES_FP16 ? 2 : 0; }
 unsigned long long ramp_launch_count(void) { return g_launches; }
+void ramp_launch_count_add(unsigned long long n) { g_launches += n; }
 
 int ramp_split_bf16(const float* x, size_t n, void* hi, void* lo, void* stream) {
   size_t b = (n + 255) / 256;

@@ -148,8 +148,9 @@ __device__ __forceinline__ float gelu_grad_f(float x) {
 // GEGLU epilogue, where the few epilogue warps are instruction-issue bound (erff + expf cost 2.5x as much).
 __device__ __forceinline__ void normal_cdf_pdf(float x, float& cdf, float& pdf) {
   const float z = fabsf(x) * 0.70710678118654752f;
-  const float t = __fdividef(1.f, fmaf(0.3275911f, z, 1.f));
-  const float e = expf(-z * z);
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.f)));      // one MUFU, 1 ulp
+  const float e = __expf(-z * z);      // ex2.approx(x log2 e): relative error ~2^-22, below the polynomial's 1.5e-7; 2 instructions instead of ~10
   const float poly = t * fmaf(t, fmaf(t, fmaf(t, fmaf(t, 1.061405429f, -1.453152027f), 1.421413741f), -0.284496736f), 0.254829592f);
   const float half = 0.5f * poly * e;
   cdf = x < 0.f ? half : 1.f - half;

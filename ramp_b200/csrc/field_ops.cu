@@ -39,10 +39,17 @@ __device__ __forceinline__ float min3f(float a, float b, float c) {
   asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
   return d;
 }
+// bounded wait (see mbar_wait in gemm_tc.cu): back-off after 2^16 failed tries, trap after 2^26
 __device__ __forceinline__ void nn_mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n.reg .pred p;\nW_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra D_%=;\nbra W_%=;\nD_%=:\n}\n"
-      ::"r"(bar), "r"(parity) : "memory");
+#pragma unroll 1
+  for (uint32_t spins = 0;; ++spins) {
+    uint32_t done;
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (done) return;
+    if (spins > (1u << 16)) __nanosleep(32);
+    if (spins > (1u << 26)) __trap();
+  }
 }
 
 template <int DIM>

@@ -41,7 +41,16 @@ static constexpr int A_TILE_BYTES = BM * BK * 2;
 //   CW = 16: 16 epilogue warps (4 groups),  64-byte row segments, <= 96 registers  - the math-heavy GEGLU forward
 // Both use 32 KB of staging tiles (one 32 x CW fp32 tile per warp).
 __host__ __device__ constexpr int epi_warps(int cw) { return cw == 32 ? 8 : 16; }
-__host__ __device__ constexpr int gemm_threads(int cw) { return 64 + 32 * epi_warps(cw); }
+// RAMP_GEMM_WG = 1: warp-group aligned roles.  Warps 0..3 = {TMA producer, MMA issuer, idle, idle}, epilogue warps start at
+// warp 4, so every 4-warp group has ONE role and `setmaxnreg` can move registers from the producer / issuer group (40 each)
+// to the epilogue groups (232 each at 8 epilogue warps instead of the 168 that 64 K / 384 threads allows): room for two
+// chunk loads in flight per thread without spills.  0: round 1's layout (epilogue from warp 2, no reallocation).
+#ifndef RAMP_GEMM_WG
+#define RAMP_GEMM_WG 1
+#endif
+static constexpr int EPI_W0 = RAMP_GEMM_WG ? 4 : 2;          // first epilogue warp
+__host__ __device__ constexpr int gemm_threads(int cw) { return 32 * (RAMP_GEMM_WG ? 4 : 2) + 32 * epi_warps(cw); }
+__host__ __device__ constexpr int epi_regs(int cw) { return cw == 32 ? 232 : 104; }   // (65536 - 128 * 40) / epilogue threads, in 8s
 static constexpr int STG_BYTES = 32 * 1024;
 
 struct GemmParams {
@@ -71,16 +80,23 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+// Bounded wait: try_wait (which itself blocks for a hardware-defined slice), a 32 ns back-off after 2^16 failed tries, and
+// after 2^26 (>= 2 s, four orders of magnitude beyond the longest legitimate wait of this kernel) a trap, so that a
+// protocol bug surfaces as a launch failure through the C ABI (ramp_last_error) instead of a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(bar), "r"(parity) : "memory");
+#pragma unroll 1
+  for (uint32_t spins = 0;; ++spins) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (done) return;
+    if (spins > (1u << 16)) __nanosleep(32);
+    if (spins > (1u << 26)) __trap();
+  }
 }
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
                                             int c2, int c3) {
@@ -366,20 +382,25 @@ __device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx<
 template <int CW>
 __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx<CW>& e, uint32_t acc, int colbase, int c0, int c1) {
   auto u_col = [&](int c) { const int j = colbase + c; return (j >> 7) * 256 + (j & 127); };
-  float4 t[CW / 4];                              // the loads in flight: gelu(gate) of chunk c, then a gelu'(gate), then chunk c + CW ...
-  chunk_ld_issue<CW>(e, p.u, 2048, u_col(c0), t);
+  // TWO chunk loads in flight per thread (gelu(gate) and a gelu'(gate) of the current chunk, then of the next one): this
+  // launch is HBM-bound on the 8 KB / token of u it reads, and with one 128-byte load per thread in flight the 8 epilogue
+  // warps covered only half of the bandwidth-delay product (ncu r1: long_scoreboard 38 %, 4.2 of 6.5 TB/s)
+  float4 ts[CW / 4], tq[CW / 4];
+  chunk_ld_issue<CW>(e, p.u, 2048, u_col(c0), ts);
+  chunk_ld_issue<CW>(e, p.u, 2048, u_col(c0) + 128, tq);
 #pragma unroll 1
   for (int c = c0; c < c1; c += CW) {
     float d[CW], x[CW];
     const int pa = u_col(c), pg = pa + 128;
+    const bool more = c + CW < c1;
     ld_acc<CW>(acc + c, d);
-    chunk_ld_finish<CW>(e, t, x);
-    chunk_ld_issue<CW>(e, p.u, 2048, pg, t);
+    chunk_ld_finish<CW>(e, ts, x);
+    if (more) chunk_ld_issue<CW>(e, p.u, 2048, u_col(c + CW), ts);
 #pragma unroll
     for (int i = 0; i < CW; ++i) x[i] *= d[i];                      // u = (gelu(gate) | a * gelu'(gate))
     chunk_store_split<CW>(e, x, p.out_hi, p.out_lo, p.ldS, pa);
-    chunk_ld_finish<CW>(e, t, x);
-    if (c + CW < c1) chunk_ld_issue<CW>(e, p.u, 2048, u_col(c + CW), t);
+    chunk_ld_finish<CW>(e, tq, x);
+    if (more) chunk_ld_issue<CW>(e, p.u, 2048, u_col(c + CW) + 128, tq);
 #pragma unroll
     for (int i = 0; i < CW; ++i) x[i] *= d[i];
     chunk_store_split<CW>(e, x, p.out_hi, p.out_lo, p.ldS, pg);
@@ -455,14 +476,20 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx<CW>
   float mean = 0.f, rstd = 0.f;
   if (e.my_ok) { const float2 st = *reinterpret_cast<const float2*>(p.ln_stats + e.my_row * 2); mean = st.x; rstd = st.y; }
   float s1 = 0.f, s2 = 0.f;
-  float4 t[CW / 4];                             // loads in flight (next ln_x chunk, or the residual chunk)
-  chunk_ld_issue<CW>(e, p.ln_x, 256, c0, t);
+  // two chunk loads in flight per thread throughout (ncu r1: long_scoreboard 63 % with one): pass 1 keeps ln_x of the
+  // current and the next chunk in flight, pass 2 the ln_x and the residual chunk of the current column range
+  float4 ta[CW / 4], tb[CW / 4];
+  chunk_ld_issue<CW>(e, p.ln_x, 256, c0, ta);
+  if (c0 + CW < c1) chunk_ld_issue<CW>(e, p.ln_x, 256, c0 + CW, tb);
+  bool use_a = true;
 #pragma unroll 1
   for (int c = c0; c < c1; c += CW) {
     float d[CW], x[CW];
     ld_acc<CW>(acc + c, d);
-    chunk_ld_finish<CW>(e, t, x);
-    chunk_ld_issue<CW>(e, p.ln_x, 256, c + CW < c1 ? c + CW : c0, t);      // the last one is the first chunk of pass 2
+    // chunk c sits in ta (even iterations) or tb (odd); refill the buffer just consumed with chunk c + 2 CW
+    if (use_a) { chunk_ld_finish<CW>(e, ta, x); if (c + 2 * CW < c1) chunk_ld_issue<CW>(e, p.ln_x, 256, c + 2 * CW, ta); }
+    else { chunk_ld_finish<CW>(e, tb, x); if (c + 2 * CW < c1) chunk_ld_issue<CW>(e, p.ln_x, 256, c + 2 * CW, tb); }
+    use_a = !use_a;
 #pragma unroll
     for (int i = 0; i < CW; i += 4) {
       const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + c + i));
@@ -472,6 +499,9 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx<CW>
     for (int i = 0; i < CW; ++i) { s1 += d[i]; s2 = fmaf(d[i], (x[i] - mean) * rstd, s2); }
     st_acc<CW>(acc + c, d);
   }
+  // pass 2's first loads go out before the row statistics are exchanged
+  chunk_ld_issue<CW>(e, p.ln_x, 256, c0, ta);
+  if (p.residual) chunk_ld_issue<CW>(e, p.residual, p.ldR, c0, tb);
   tmem_st_wait();
   {
     float2 part[NG];
@@ -485,14 +515,13 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx<CW>
     float d[CW], x[CW];
     const bool more = c + CW < c1;
     ld_acc<CW>(acc + c, d);
-    chunk_ld_finish<CW>(e, t, x);
-    if (p.residual) chunk_ld_issue<CW>(e, p.residual, p.ldR, c, t);
-    else if (more) chunk_ld_issue<CW>(e, p.ln_x, 256, c + CW, t);
+    chunk_ld_finish<CW>(e, ta, x);
+    if (more) chunk_ld_issue<CW>(e, p.ln_x, 256, c + CW, ta);
 #pragma unroll
     for (int i = 0; i < CW; ++i) d[i] = rstd * (d[i] - s1 - (x[i] - mean) * rstd * s2);
     if (p.residual) {
-      chunk_ld_finish<CW>(e, t, x);
-      if (more) chunk_ld_issue<CW>(e, p.ln_x, 256, c + CW, t);
+      chunk_ld_finish<CW>(e, tb, x);
+      if (more) chunk_ld_issue<CW>(e, p.residual, p.ldR, c + CW, tb);
 #pragma unroll
       for (int i = 0; i < CW; ++i) d[i] += x[i];
     }
@@ -549,6 +578,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");
 
+#if RAMP_GEMM_WG
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+#endif
   if (warp == 0) {
     // ---------------- TMA producer ----------------
     if (lane == 0) {
@@ -619,18 +652,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
         umma_commit(tfull0 + 8 * buf);            // accumulator complete
       }
     }
+  }
+#if RAMP_GEMM_WG
   } else {
-    // ---------------- epilogue: TMEM lane quarter q = warp % 4, group = (warp - 2) / 4 ----------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(epi_regs(CW)));
+#else
+  if (warp >= EPI_W0) {
+#endif
+    // ---------------- epilogue: TMEM lane quarter q = warp % 4, group = (warp - EPI_W0) / 4 ----------------
     constexpr int NG = epi_warps(CW) / 4;
-    const int q = warp & 3, group = (warp - 2) >> 2;
+    const int q = warp & 3, group = (warp - EPI_W0) >> 2;
     if (group < p.ngroups) {
       float* stg_all = reinterpret_cast<float*>(smem_gen + p.stages * stage_bytes);
       EpiCtx<CW> e;
       using E = EpiCtx<CW>;
       e.lane = lane;
       e.bar_id = 1 + q;
-      e.stg = stg_all + (warp - 2) * (32 * CW);
-      e.stg_q = stg_all + ((warp - 2) & 3) * (32 * CW);
+      e.stg = stg_all + (warp - EPI_W0) * (32 * CW);
+      e.stg_q = stg_all + ((warp - EPI_W0) & 3) * (32 * CW);
       const int cols = p.BN / p.ngroups;                      // tile columns this group drains
       const int c0 = group * cols, c1 = c0 + cols;
       const int r = q * 32 + lane;

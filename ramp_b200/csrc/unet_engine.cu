@@ -6,10 +6,26 @@
 namespace ramp {
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+#define TRY_RC(expr) do { int _rc = (expr); if (_rc) return _rc; } while (0)
 
 UnetEngine::~UnetEngine() {
   for (void* p : owned_) cudaFree(p);
   if (arena_) cudaFree(arena_);
+  for (int i = 0; i < 4; ++i) {
+    if (side_[i]) cudaStreamDestroy(side_[i]);
+    if (join_ev_[i]) cudaEventDestroy(join_ev_[i]);
+  }
+  if (fork_ev_) cudaEventDestroy(fork_ev_);
+}
+
+int UnetEngine::ensure_side_streams() {
+  if (fork_ev_) return 0;
+  RAMP_CUDA_OK(cudaEventCreateWithFlags(&fork_ev_, cudaEventDisableTiming));
+  for (int i = 0; i < split_; ++i) {
+    RAMP_CUDA_OK(cudaStreamCreateWithFlags(&side_[i], cudaStreamNonBlocking));
+    RAMP_CUDA_OK(cudaEventCreateWithFlags(&join_ev_[i], cudaEventDisableTiming));
+  }
+  return 0;
 }
 
 void* UnetEngine::dev_alloc(size_t bytes) {
@@ -283,12 +299,22 @@ int UnetEngine::finalize(cudaStream_t s) {
   RAMP_CHECK(g_missing.empty(), "state dict is incomplete or mis-shaped: " + g_missing);
   RAMP_CUDA_OK(cudaDeviceSynchronize());
 
-  // size the workspace with a dry run at max_rows
+  // RAMP_UNET_SPLIT = n (1..4): run calls of >= RAMP_UNET_SPLIT_MIN rows as n parts on side streams (see unet_engine.cuh)
+  if (const char* v = getenv("RAMP_UNET_SPLIT")) { split_ = atoi(v); if (split_ < 1) split_ = 1; if (split_ > 4) split_ = 4; }
+  if (const char* v = getenv("RAMP_UNET_SPLIT_MIN")) { split_min_rows_ = atoi(v); if (split_min_rows_ < 32) split_min_rows_ = 32; }
+  // size the workspace with a dry run at max_rows (and, in split mode, as the parts it would be run as)
   dry_ = true; arena_off_ = 0;
   rc = run(nullptr, cfg_.max_rows, 1, 0.f, nullptr, nullptr, nullptr, s);
+  size_t need = arena_off_;
+  if (!rc && split_ > 1) {
+    arena_off_ = 0;
+    const int per = (cfg_.max_rows + split_ - 1) / split_ + 16;
+    for (int p = 0; p < split_ && !rc; ++p) rc = run(nullptr, per, 1, 0.f, nullptr, nullptr, nullptr, s);
+    if (arena_off_ > need) need = arena_off_;
+  }
   dry_ = false;
   if (rc) return rc;
-  arena_bytes_ = arena_off_ + 256;
+  arena_bytes_ = need + 256;
   RAMP_CUDA_OK(cudaMalloc((void**)&arena_, arena_bytes_));
   RAMP_CUDA_OK(cudaMemset(arena_, 0, arena_bytes_));
   finalized_ = true;
@@ -308,7 +334,28 @@ int UnetEngine::energy_grad(const float* x, int n_rows, int x_repeat, float t, c
   RAMP_CHECK(n_scenes_ > 0, "energy_grad before set_scenes");
   RAMP_CHECK(n_rows >= 1 && n_rows <= cfg_.max_rows, "n_rows exceeds max_rows of this engine");
   arena_off_ = 0;
-  return run(x, n_rows, x_repeat, t, row2scene, eps_out, f_out, s);
+  if (split_ <= 1 || n_rows < split_min_rows_ || prof_) return run(x, n_rows, x_repeat, t, row2scene, eps_out, f_out, s);
+  // row-split: parts are whole trajectories (multiples of x_repeat rows) and multiples of 16 rows, so every part's
+  // padding and tile layout equal those of a stand-alone call (rows do not depend on their launch: bit-identical results)
+  if (ensure_side_streams()) return -1;
+  const int H = cfg_.horizon, D = cfg_.state_dim;
+  int unit = x_repeat;
+  while (unit % 16) unit += x_repeat;
+  int per = ((n_rows + split_ - 1) / split_ + unit - 1) / unit * unit;
+  TRY_RC(time_cond(time_w_, t, (const CondBlock*)cond_blocks_dev_, 16, s));
+  RAMP_CUDA_OK(cudaEventRecord(fork_ev_, s));
+  skip_time_cond_ = true;
+  int rc = 0, used = 0;
+  for (int p = 0, r0 = 0; p < split_ && r0 < n_rows && !rc; ++p, r0 += per, ++used) {
+    const int n = n_rows - r0 < per ? n_rows - r0 : per;
+    RAMP_CUDA_OK(cudaStreamWaitEvent(side_[p], fork_ev_, 0));
+    rc = run(x + (size_t)(r0 / x_repeat) * H * D, n, x_repeat, t, row2scene ? row2scene + r0 : nullptr,
+             eps_out ? eps_out + (size_t)r0 * H * D : nullptr, f_out ? f_out + (size_t)r0 * H * D : nullptr, side_[p]);
+    if (!rc) RAMP_CUDA_OK(cudaEventRecord(join_ev_[p], side_[p]));
+  }
+  skip_time_cond_ = false;
+  for (int p = 0; p < used; ++p) RAMP_CUDA_OK(cudaStreamWaitEvent(s, join_ev_[p], 0));
+  return rc;
 }
 
 UnetEngine::ProfScope::ProfScope(UnetEngine* eng, int cat) : e(eng), idx(-1) {

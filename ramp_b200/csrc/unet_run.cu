@@ -301,7 +301,7 @@ int UnetEngine::run(const float* x, int n_rows, int x_repeat, float t, const int
   if (!dry_) {
     RAMP_CUDA_OK(cudaMemsetAsync(r2s, 0, (size_t)npad_ * sizeof(int), s));
     if (row2scene) RAMP_CUDA_OK(cudaMemcpyAsync(r2s, row2scene, (size_t)n_rows * sizeof(int), cudaMemcpyDeviceToDevice, s));
-    TRY(time_cond(time_w_, t, (const CondBlock*)cond_blocks_dev_, 16, s));
+    if (!skip_time_cond_) TRY(time_cond(time_w_, t, (const CondBlock*)cond_blocks_dev_, 16, s));
   }
   Split xin = allocs((size_t)npad_ * H * 16);
   if (!dry_) TRY(prep_input(x, n_rows, npad_, H, D, x_repeat, xin.hi, xin.lo, s));

@@ -18,6 +18,9 @@ from ._lib import RampError
 from .sample_functions import apply_hard_conditioning, ddpm_sample_fn, extract  # noqa: F401 (re-exported)
 
 
+_TORCH_RANDN, _TORCH_RANDN_LIKE = torch.randn, torch.randn_like     # to notice a patched RNG (a noise tape)
+
+
 def make_timesteps(batch_size, i, device):
     return torch.full((batch_size,), i, device=device, dtype=torch.long)
 
@@ -149,6 +152,7 @@ class _DiffusionBase(nn.Module):
         unet.set_scene_latents(lat)
         self._G = groups.shape[0]
         self._scene_sig = (groups.data_ptr(), tuple(groups.shape), groups._version, self.model._engine_key)
+        self._scene_src = groups          # pointer-keyed caches hold their key tensor: its memory cannot be recycled under them
         return self._G
 
     def _ensure_engine(self, horizon, rows):
@@ -214,6 +218,60 @@ class _DiffusionBase(nn.Module):
                         sqrt_recip=s['sqrt_recip'][t], sqrt_recipm1=s['sqrt_recipm1'][t],
                         predict_epsilon=self.predict_epsilon, **self._ddim_scalars(t, t_prev))
 
+    # ------------------------------------------------------------------ CUDA-graph fast path of the DDPM loop
+    # 'auto': the third call with the same shapes captures the whole loop (graphs.DdpmLoopGraph) and later calls replay it —
+    # one graph launch instead of ~7,500 host launches per sampling (north_star (3)); True: capture at the first call;
+    # False: always eager.  A replay draws from torch's default CUDA generator exactly like the eager loop (bit-identical
+    # under the same torch.manual_seed, tests/test_loops_gpu.py); a patched torch.randn (noise tape) disables the path.
+    cuda_graph = 'auto'
+
+    def _loop_graph(self, shape, hard_conds, obstacle_pts, sample_fn, noise_fn, extra_steps):
+        if self.cuda_graph is False or sample_fn is not ddpm_sample_fn or not self.betas.is_cuda or self.APF:
+            return None        # (the APF branch packs its cloud outside the graph: eager only)
+        if torch.randn is not _TORCH_RANDN or torch.randn_like is not _TORCH_RANDN_LIKE:
+            return None
+        if torch.cuda.is_current_stream_capturing():
+            return None
+        B, H, D = shape
+        steps = list(reversed(range(-extra_steps, self.n_diffusion_steps)))
+        scales = tuple(1.0 if noise_fn is None else float(noise_fn(i)) for i in steps)
+        graphs = self.__dict__.setdefault('_loop_graphs', {})
+        key = (B, H, D, scales, bool(self.compose), bool(self.APF), tuple(obstacle_pts.shape), str(self.betas.device))
+        ent = graphs.setdefault(key, {'calls': 0, 'graph': None, 'src': None})
+        pins = ops.Pins.from_hard_conds(hard_conds, B, H, D, self.betas.device)
+        g = ent['graph']
+        if g is not None and (g.pins.val.shape != pins.val.shape or not torch.equal(g.pins.mask, pins.mask)):
+            g = ent['graph'] = None
+        if g is None:
+            ent['calls'] += 1
+            if self.cuda_graph is not True and ent['calls'] <= 2:
+                return None
+            from .graphs import DdpmLoopGraph
+            if len(graphs) > 4:                        # each graph pins a chain and noise buffers: keep a handful
+                for k in [k for k in graphs if k != key]:
+                    del graphs[k]
+            g = ent['graph'] = DdpmLoopGraph(self, B, H, hard_conds, obstacle_pts, noise_scale=list(scales),
+                                             extra_steps=extra_steps, own_cloud=True)
+            ent['src'] = None
+        g.pins.val.copy_(pins.val)
+        src = (obstacle_pts.data_ptr(), obstacle_pts._version)
+        if ent['src'] is None or ent['src'][0] != src:
+            g.set_cloud(obstacle_pts)
+            ent['src'] = (src, obstacle_pts)          # holding the tensor keeps its pointer from being recycled under the key
+        return g
+
+    def _replay_loop(self, g):
+        """-> chain [T+1, B, H, D] as a fresh tensor (the graph's own chain buffer is overwritten by the next replay), or
+        None when the engine was rebuilt since the capture (the caller falls back to the eager loop; a new graph is
+        captured on a later call)."""
+        try:
+            return g.replay().clone()
+        except RampError:
+            for ent in self.__dict__.get('_loop_graphs', {}).values():
+                if ent['graph'] is g:
+                    ent['graph'], ent['calls'] = None, 0
+            return None
+
     # ------------------------------------------------------------------ reference helper surface
     def predict_start_from_noise(self, x_t, t, noise):
         if self.predict_epsilon:
@@ -262,8 +320,8 @@ class _CloudCache:
         if key not in self._d:
             if len(self._d) > 8:
                 self._d.clear()
-            self._d[key] = ops.CloudIndex(pts)
-        return self._d[key]
+            self._d[key] = (ops.CloudIndex(pts), pts)      # the key tensor stays alive with its entry
+        return self._d[key][0]
 
 
 class StaticGaussianDiffusionModel(_DiffusionBase):
@@ -291,7 +349,7 @@ class StaticGaussianDiffusionModel(_DiffusionBase):
             g = obstacle_pts if obstacle_pts.dim() == 4 else obstacle_pts.unsqueeze(0)
             if not compose:
                 g = g[:1]
-            self._groups_cache = (key, g.to(torch.float32).contiguous())
+            self._groups_cache = (key, g.to(torch.float32).contiguous(), obstacle_pts)
         g = self._groups_cache[1]
         G = g.shape[0]
         if not compose:
@@ -350,12 +408,16 @@ class StaticGaussianDiffusionModel(_DiffusionBase):
         B, H, D = shape
         if not self.compose and obstacle_pts.dim() == 3:
             obstacle_pts = obstacle_pts.unsqueeze(0)
+        noise_fn = sample_kwargs.get('noise_std_extra_schedule_fn')
+        g = self._loop_graph(shape, hard_conds, obstacle_pts, sample_fn, noise_fn, n_diffusion_steps_without_noise)
+        chain = self._replay_loop(g) if g is not None else None
+        if chain is not None:
+            return (chain[-1], chain.transpose(0, 1)) if return_chain else chain[-1]
         pins = ops.Pins.from_hard_conds(hard_conds, B, H, D, device)
         n_total = self.n_diffusion_steps + n_diffusion_steps_without_noise
         chain = torch.empty(n_total + 1, B, H, D, device=device)
         chain[0] = torch.randn(shape, device=device)
         ops.inpaint(chain[0], pins)
-        noise_fn = sample_kwargs.get('noise_std_extra_schedule_fn')
         k = 0
         for i in reversed(range(-n_diffusion_steps_without_noise, self.n_diffusion_steps)):
             x = chain[k]
@@ -391,7 +453,7 @@ class StaticGaussianDiffusionModel(_DiffusionBase):
             key = (obstacle_pts.data_ptr(), tuple(obstacle_pts.shape), obstacle_pts._version)
             if getattr(self, '_apf_key', None) != key:
                 self._apf_pts = torch.cat([obstacle_pts[0], obstacle_pts[1][:4]], dim=0).reshape(-1, 2).contiguous()
-                self._apf_key = key
+                self._apf_key, self._apf_src = key, obstacle_pts
             return self._clouds.get(self._apf_pts)
         return self._clouds.get(obstacle_pts)
 
@@ -498,7 +560,7 @@ class GaussianDiffusionModel3d(_DiffusionBase):
             g = obstacle_pts if obstacle_pts.dim() == 4 else obstacle_pts.unsqueeze(0)
             if not compose:
                 g = g[:1]
-            self._groups_cache = (key, g.to(torch.float32).contiguous())
+            self._groups_cache = (key, g.to(torch.float32).contiguous(), obstacle_pts)
         g = self._groups_cache[1]
         G = g.shape[0]
         if not compose:
@@ -525,12 +587,16 @@ class GaussianDiffusionModel3d(_DiffusionBase):
         B, H, D = shape
         if not self.compose and obstacle_pts.dim() == 3:
             obstacle_pts = obstacle_pts.unsqueeze(0)
+        noise_fn = sample_kwargs.get('noise_std_extra_schedule_fn')
+        g = self._loop_graph(shape, hard_conds, obstacle_pts, sample_fn, noise_fn, n_diffusion_steps_without_noise)
+        chain = self._replay_loop(g) if g is not None else None
+        if chain is not None:
+            return (chain[-1], chain.transpose(0, 1)) if return_chain else chain[-1]
         pins = ops.Pins.from_hard_conds(hard_conds, B, H, D, device)
         n_total = self.n_diffusion_steps + n_diffusion_steps_without_noise
         chain = torch.empty(n_total + 1, B, H, D, device=device)
         chain[0] = torch.randn(shape, device=device)
         ops.inpaint(chain[0], pins)
-        noise_fn = sample_kwargs.get('noise_std_extra_schedule_fn')
         k = 0
         for i in reversed(range(-n_diffusion_steps_without_noise, self.n_diffusion_steps)):
             x = chain[k]

@@ -66,7 +66,7 @@ class DynamicGaussianDiffusionModel(_DiffusionBase):
             g = obstacle_pts
             while g.dim() > 3:
                 g = g[0]
-            self._groups_cache = (key, g.unsqueeze(0).to(torch.float32).contiguous())
+            self._groups_cache = (key, g.unsqueeze(0).to(torch.float32).contiguous(), obstacle_pts)
         return self._groups_cache[1], [self.cfg_weight]
 
     def _row_scenes(self, B, G, device):

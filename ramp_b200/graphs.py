@@ -41,8 +41,16 @@ class _EngineGuard:
                             "pointers are stale — capture a new graph")
 
 
+def _launches():
+    import ctypes
+    from ._lib import lib
+    lib().ramp_launch_count.restype = ctypes.c_ulonglong
+    return int(lib().ramp_launch_count())
+
+
 def _capture(fn, warmup=2):
-    """Warm up on a side stream (lazy initialisation, autotuned launch attributes, scene cache), then capture."""
+    """Warm up on a side stream (lazy initialisation, autotuned launch attributes, scene cache), then capture.
+    Returns (graph, fn's result, number of library kernels in the graph)."""
     s = torch.cuda.Stream()
     s.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(s):
@@ -51,15 +59,26 @@ def _capture(fn, warmup=2):
     torch.cuda.current_stream().wait_stream(s)
     torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
+    n0 = _launches()
     with torch.cuda.graph(g):
         out = fn()
-    return g, out
+    return g, out, _launches() - n0
+
+
+def _count_replay(n):
+    import ctypes
+    from ._lib import lib
+    lib().ramp_launch_count_add.restype = None
+    lib().ramp_launch_count_add(ctypes.c_ulonglong(n))
 
 
 class DdpmLoopGraph(_EngineGuard):
     """Graph of one complete DDPM sampling (x_T draw, T reverse steps, inpainting) for a fixed batch."""
 
-    def __init__(self, model, batch, horizon, hard_conds, obstacle_pts, noise_scale=0.5, extra_steps=0):
+    def __init__(self, model, batch, horizon, hard_conds, obstacle_pts, noise_scale=0.5, extra_steps=0, own_cloud=False):
+        """noise_scale: one float, or one per step (the values `noise_std_extra_schedule_fn(i)` takes in the loop).
+        own_cloud: keep a private copy of the conditioning cloud (`set_cloud` then re-conditions the graph without
+        touching the caller's tensor)."""
         if not next(model.parameters()).is_cuda:
             raise RampError("graphs need a CUDA model")
         self.model = model
@@ -71,20 +90,32 @@ class DdpmLoopGraph(_EngineGuard):
         if not model.compose and obstacle_pts.dim() == 3:
             obstacle_pts = obstacle_pts.unsqueeze(0)
         self.cloud = obstacle_pts.to(dev).float().contiguous()
+        if own_cloud:
+            self.cloud = self.cloud.clone()
+        self._own_cloud = own_cloud
         self.chain = torch.empty(T + extra_steps + 1, B, H, D, device=dev)
         steps = [max(i, 0) for i in reversed(range(-extra_steps, T))]
+        scales = list(noise_scale) if isinstance(noise_scale, (list, tuple)) else [noise_scale] * len(steps)
 
         def loop():
             self.chain[0] = torch.randn((B, H, D), device=dev)
             ops.inpaint(self.chain[0], self.pins)
             for k, t in enumerate(steps):
                 noise = torch.randn((B, H, D), device=dev)
-                model._ddpm_step(self.chain[k], t, self.cloud, noise if t > 0 else None, noise_scale,
+                model._ddpm_step(self.chain[k], t, self.cloud, noise if t > 0 else None, scales[k],
                                  compose=model.compose, pins=self.pins, out=self.chain[k + 1], forward_t=k)
             return self.chain
 
-        self.graph, _ = _capture(loop)
+        self.graph, _, self.n_kernels = _capture(loop)
         self._bind(model)
+
+    def set_cloud(self, obstacle_pts):
+        """New conditioning cloud of the same shape (own_cloud graphs): copied into the graph's buffer; the next replay
+        re-encodes it (the scene constants are established eagerly before every replay)."""
+        if not self._own_cloud:
+            raise RampError("set_cloud needs a graph created with own_cloud=True")
+        src = obstacle_pts if self.cloud.dim() == obstacle_pts.dim() else obstacle_pts.unsqueeze(0)
+        self.cloud.copy_(src.to(self.cloud.device).float())
 
     def replay(self):
         """Runs the captured loop on the current stream; returns the chain [T+1, B, H, D] (static buffer).
@@ -93,6 +124,7 @@ class DdpmLoopGraph(_EngineGuard):
         self._check_engine()
         self.model._set_scenes(self.model._groups_and_weights(self.cloud, self.model.compose)[0])
         self.graph.replay()
+        _count_replay(self.n_kernels)
         return self.chain
 
 
@@ -185,7 +217,7 @@ class ReplanGraph(_EngineGuard):
             return self.best
 
         saved = None if pursuer is None else (pursuer.center.clone(), pursuer.counter.clone())
-        self.graph, _ = _capture(tick)
+        self.graph, _, self.n_kernels = _capture(tick)
         if saved is not None:                                         # the warm-up passes moved the pursuer: put it back
             pursuer.center.copy_(saved[0])
             pursuer.counter.copy_(saved[1])
@@ -199,6 +231,7 @@ class ReplanGraph(_EngineGuard):
         if not self._streams:        # scene constants are not graph nodes: make sure they are still this graph's cloud
             self.model._set_scenes(self.model._groups_and_weights(self.cloud, False)[0])
         self.graph.replay()
+        _count_replay(self.n_kernels)
         if self._streams:            # the replay re-encoded `cloud` behind the host-side cache's back
             self.model._scene_sig = None
         if sync and int(self.sel[0].item()) < 0:

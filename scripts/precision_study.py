@@ -16,6 +16,9 @@ can carry (value = hi + lo), products and sums in fp32 as in the tensor-core pat
   fp16+fp16   both planes fp16, residual stored as is (fp16 subnormals: absolute error <= 3e-8 per element): the variant the
               hardware accepts — tcgen05.mma kind::f16 with A = f16, B = bf16 is an ILLEGAL INSTRUCTION on B200 (measured,
               round 2), so every product must have same-format operands
+  fp16+fp16/g256   fp16+fp16 with the backward sweep loss-scaled by 2^8 (what csrc/common.cuh RAMP_GRAD_SCALE does: the
+              input-gradient packing of final_conv.1 carries the factor, run() divides it out): gradients (typically
+              1e-3, i.e. near the fp16 subnormal range for their residuals) move into the well-resolved range
   fp16+fp16s  both planes fp16, residual scaled by 2^11 before rounding (22 bits; needs a second accumulator or a scaled
               epilogue add, listed for reference)
 
@@ -63,6 +66,8 @@ class _RoundGrad(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
+        if ctx.scheme == "fp16+fp16/g256":
+            return planes(g * 256.0, "fp16+fp16") / 256.0, None
         return planes(g, ctx.scheme), None
 
 
@@ -73,9 +78,10 @@ class rounded_operands:
         self.scheme, self.mm_scheme = scheme, scheme
         if scheme == "fp16+bf16/attn-bf16":          # GEMM operands fp16 + bf16, attention products re-split to bf16 + bf16
             self.scheme, self.mm_scheme = "fp16+bf16", "bf16+bf16"
+        self.fwd = "fp16+fp16" if scheme == "fp16+fp16/g256" else None     # forward operands: unscaled
 
     def _q(self, t):
-        return t + (planes(t.detach(), self.scheme) - t.detach())       # rounded value, straight-through gradient
+        return t + (planes(t.detach(), self.fwd or self.scheme) - t.detach())       # rounded value, straight-through gradient
 
     def __enter__(self):
         self.saved = (F.linear, F.conv1d, F.conv_transpose1d, torch.matmul)
@@ -85,7 +91,7 @@ class rounded_operands:
         F.conv1d = lambda x, w, b=None, **kw: _RoundGrad.apply(c1(q(x), q(w), b, **kw), s)
         F.conv_transpose1d = lambda x, w, b=None, **kw: _RoundGrad.apply(ct(q(x), q(w), b, **kw), s)
         ms = self.mm_scheme
-        qm = lambda t: t + (planes(t.detach(), ms) - t.detach())  # noqa: E731
+        qm = lambda t: t + (planes(t.detach(), self.fwd or ms) - t.detach())  # noqa: E731
         torch.matmul = lambda a, b: _RoundGrad.apply(mm(qm(a), qm(b)), ms)
         return self
 
@@ -93,7 +99,7 @@ class rounded_operands:
         F.linear, F.conv1d, F.conv_transpose1d, torch.matmul = self.saved
 
 
-SCHEMES = ("fp32", "bf16+bf16", "fp16+bf16", "fp16+bf16/attn-bf16", "fp16+fp16", "fp16+fp16s")
+SCHEMES = ("fp32", "bf16+bf16", "fp16+bf16", "fp16+fp16", "fp16+fp16/g256", "fp16+fp16s")
 
 
 def noise(seed, k, B=6):
@@ -115,7 +121,7 @@ def main():
                                      predict_epsilon=True)
     sd, sch = synthetic_state_dict(m, 0), O.make_schedule(25)
     hc = {0: torch.tensor([-0.8, -0.8, 0.0, 0.0]), 63: torch.tensor([0.8, 0.8, 0.0, 0.0])}
-    print("%-11s %-5s %10s %10s %10s   (free run of 24 steps from the reference's x1, vs the reference's final waypoints)"
+    print("%-15s %-5s %10s %10s %10s   (free run of 24 steps from the reference's x1, vs the reference's final waypoints)"
           % ("scheme", "seed", "max", "median", "row err"))
     for ci in which:
         case = gold["cases"][ci]
@@ -131,7 +137,7 @@ def main():
                     x = O.ddpm_step(sch, x, t, O.eps_combined(sd, x, t, lat, [2.0]), noise(case["seed"], 1 + j), 0.5)
                     x = O.inpaint(x, hc)
             dev = (x - case["final"]).abs().amax(dim=(1, 2))
-            print("%-11s %-5d %10.2e %10.2e %10.2e   %.0f s" % (scheme, case["seed"], dev.max(), dev.median(), row,
+            print("%-15s %-5d %10.2e %10.2e %10.2e   %.0f s" % (scheme, case["seed"], dev.max(), dev.median(), row,
                                                               time.time() - t0), flush=True)
 
 

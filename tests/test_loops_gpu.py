@@ -141,6 +141,7 @@ def test_ddpm_loop_graph_equals_eager_loop(cuda):
     from ramp_b200.testing import synthetic_cloud_2d
     m, _ = build(cuda, "static", 25, compose=True, max_rows=7 * 16)
     m.ddim = False
+    m.cuda_graph = False                                 # `want` below must come from the eager loop
     groups = synthetic_cloud_2d(seed=5, groups=6).to(cuda)
     g = DdpmLoopGraph(m, batch=16, horizon=64, hard_conds=hc(4, cuda), obstacle_pts=groups)
     for seed in (11, 12):
@@ -151,6 +152,45 @@ def test_ddpm_loop_graph_equals_eager_loop(cuda):
                                traj_normalized=torch.zeros(64, 4, device=cuda), obstacle_pts=groups,
                                sample_fn=ddpm_sample_fn, noise_std_extra_schedule_fn=lambda t: 0.5)
         assert torch.equal(got, want), (got - want).abs().max().item()
+
+
+def test_run_inference_graph_fast_path_equals_eager(cuda):
+    """run_inference captures the 25-step loop at its third identical call (`cuda_graph = 'auto'`) and replays it from then
+    on: the replays equal the eager loop bit for bit under the same seed, follow a NEW cloud and new hard conditions, count
+    their kernels, and fall back to the eager loop when the engine is rebuilt."""
+    import ctypes
+    from ramp_b200._lib import lib
+    from ramp_b200.sample_functions import ddpm_sample_fn
+    from ramp_b200.testing import synthetic_cloud_2d
+    m, _ = build(cuda, "static", 25, compose=True, max_rows=7 * 16)       # the engine is sized by the first call (56 rows)
+    m.ddim = False
+    clouds = [synthetic_cloud_2d(seed=s, groups=6).to(cuda) for s in (5, 6)]
+    hcs = [hc(4, cuda), {0: torch.tensor([-0.7, -0.6, 0.0, 0.0], device=cuda), 63: torch.tensor([0.6, 0.7, 0.0, 0.0], device=cuda)}]
+    kw = dict(horizon=64, return_chain=True, traj_normalized=torch.zeros(64, 4, device=cuda), sample_fn=ddpm_sample_fn,
+              noise_std_extra_schedule_fn=lambda t: 0.5)
+
+    def run(cloud, h, seed, n=8):
+        torch.manual_seed(seed)
+        return m.run_inference(None, h, n_samples=n, obstacle_pts=cloud, **kw).clone()
+
+    m.cuda_graph = False
+    want = {(c, h): run(clouds[c], hcs[h], 40 + c + 2 * h) for c in (0, 1) for h in (0, 1)}
+    m.cuda_graph = 'auto'
+    assert torch.equal(run(clouds[0], hcs[0], 40), want[0, 0])            # call 1: eager
+    assert torch.equal(run(clouds[0], hcs[0], 40), want[0, 0])            # call 2: eager
+    lib().ramp_launch_count.restype = ctypes.c_ulonglong
+    got = run(clouds[0], hcs[0], 40)                                      # call 3: captures, then replays
+    assert len(m._loop_graphs) == 1 and next(iter(m._loop_graphs.values()))['graph'] is not None
+    assert torch.equal(got, want[0, 0])
+    n0 = int(lib().ramp_launch_count())
+    for c in (1, 0):
+        for h in (1, 0):
+            assert torch.equal(run(clouds[c], hcs[h], 40 + c + 2 * h), want[c, h]), (c, h)
+    assert int(lib().ramp_launch_count()) - n0 > 4 * 25 * 100            # replays are counted as the kernels they launch
+    key0 = m.model._engine_key
+    big = run(clouds[0], hcs[0], 41, n=16)                                # 112 rows > 56: the engine is rebuilt
+    assert big.shape == (26, 16, 64, 4) and m.model._engine_key != key0
+    assert torch.equal(run(clouds[0], hcs[0], 40), want[0, 0])            # the stale graph is dropped, eager again
 
 
 def _tick_setup(cuda, near):
