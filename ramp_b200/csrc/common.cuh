@@ -147,12 +147,14 @@ __device__ __forceinline__ float gelu_grad_f(float x) {
 // no cancellation on the negative side), phi(x) = exp(-x^2/2) / sqrt(2 pi) shares the exponential.  Used by the fused
 // GEGLU epilogue, where the few epilogue warps are instruction-issue bound (erff + expf cost 2.5x as much).
 __device__ __forceinline__ void normal_cdf_pdf(float x, float& cdf, float& pdf) {
-  const float z = fabsf(x) * 0.70710678118654752f;
-  float t;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.f)));      // one MUFU, 1 ulp
-  const float e = __expf(-z * z);      // ex2.approx(x log2 e): relative error ~2^-22, below the polynomial's 1.5e-7; 2 instructions instead of ~10
-  const float poly = t * fmaf(t, fmaf(t, fmaf(t, fmaf(t, 1.061405429f, -1.453152027f), 1.421413741f), -0.284496736f), 0.254829592f);
-  const float half = 0.5f * poly * e;
+  // z = |x| / sqrt 2 never materialises: its factor is folded into the rational's slope and into the exponent
+  // (exp(-z^2) = 2^(x^2 * (-0.5 log2 e))), the 0.5 of Phi into the polynomial's coefficients
+  float t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f * 0.70710678118654752f, fabsf(x), 1.f)));   // one MUFU, 1 ulp
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752044448170f));   // relative error ~2^-22 < the polynomial's 1.5e-7
+  const float poly = t * fmaf(t, fmaf(t, fmaf(t, fmaf(t, 0.5f * 1.061405429f, 0.5f * -1.453152027f), 0.5f * 1.421413741f),
+                                      0.5f * -0.284496736f), 0.5f * 0.254829592f);
+  const float half = poly * e;
   cdf = x < 0.f ? half : 1.f - half;
   pdf = 0.39894228040143268f * e;
 }
