@@ -234,6 +234,9 @@ def run_ours(args):
         if args.replan_ticks > 0:
             extras["replan"] = replan_latency(dev, args.replan_ticks, max(3, args.replan_ticks // 10))
             extras["replan25"] = replan_latency(dev, max(10, args.replan_ticks // 3), 3, high=25, low=25)
+            p1 = replan_latency(dev, max(10, args.replan_ticks // 2), 3, precision=1)
+            extras["replan_single_mma_non_parity"] = {k: p1[k] for k in ("p50_ms", "p95_ms", "device_p50_ms", "ticks", "batch", "ddim_steps", "mma_per_product", "parity_mode")}
+            extras["replan_single_mma_non_parity"]["note"] = "hi*hi only (one MMA per product): breaks north_star's 1e-3 waypoint tolerance, reported for context, never the headline"
         extras["field"] = field_roofline(dev, local)
         extras["maze3d"] = maze3d_section(dev, local)
         if world == 1:
@@ -483,14 +486,14 @@ def _cpu_scene_encoder(pts):
 # Per tick the host uploads the new conditioning cloud (pinned -> device), replays the graph and reads the
 # selection back; latency = host wall clock between synchronised points (what TimerCUDA measures).
 # ---------------------------------------------------------------------------------------------------
-def replan_latency(dev, ticks, warm, batch=1024, high=10, low=5):
+def replan_latency(dev, ticks, warm, batch=1024, high=10, low=5, precision=3):
     import numpy as np
     from ramp_b200.apf_dynamic import generate_box_points
     from ramp_b200.dynamic import DynamicGaussianDiffusionModel
     from ramp_b200.graphs import ReplanGraph
     from ramp_b200.testing import SyntheticPursuitDataset, pursuit_cloud_2d, synthetic_state_dict
     from ramp_b200.unet import TemporalUnetInference
-    net = TemporalUnetInference(n_support_points=H, state_dim=D, max_rows=2 * batch, max_scenes=2)
+    net = TemporalUnetInference(n_support_points=H, state_dim=D, max_rows=2 * batch, max_scenes=2, precision=precision)
     m = DynamicGaussianDiffusionModel(model=net, n_diffusion_steps=100, predict_epsilon=True)
     m.load_state_dict(synthetic_state_dict(m, 0))
     m = m.to(dev).eval()
@@ -541,13 +544,14 @@ def replan_latency(dev, ticks, warm, batch=1024, high=10, low=5):
     flops = rows * low * F_ROW
     out = {"p50_ms": q(lat_ms, 0.5), "p95_ms": q(lat_ms, 0.95), "device_p50_ms": q(dev_ms, 0.5), "ticks": ticks,
            "warmup_ticks": warm, "batch": batch, "ddim_steps": low, "of_inference_steps": high,
+           "mma_per_product": precision, "parity_mode": precision == 3,
            "network_rows_per_step": rows, "reference_rows_per_step": 2 * batch,
            "ticks_with_a_collision_free_plan": survivors,
            "apf_cloud_points": 3840 + 256, "cost_cloud_points": 4096, "cuda_graph": True,
            "h2d_bytes_per_tick": int(cond_host.numel()) * 4, "d2h_bytes_per_tick": 32,
            "conditioning": "cloud uploaded and re-encoded (scene encoder kernels) inside the graph every tick",
            "pursuer": "motion law + 256-point disc computed by ramp_pursuer_tick inside the graph (no host step)",
-           "tensor_floor_ms": 1e3 * 3 * flops / (peaks()[0] * 1e12),
+           "tensor_floor_ms": 1e3 * precision * flops / (peaks()[0] * 1e12),
            "tensor_floor_ms_reference_rows": 1e3 * 3 * (2 * batch * low * F_ROW) / (peaks()[0] * 1e12),
            "bf16_1x_floor_ms_reference_rows": 1e3 * (2 * batch * low * F_ROW) / (peaks()[0] * 1e12),
            "note": "The reference stacks the batch twice for CFG, but with an even batch its odd-row latent mask makes both "

@@ -42,3 +42,4 @@ print('$lib'.split('/')[-1], 'traj/s', round(d['value'],1), {k: round(x,1) for k
 " | tee -a ${O}_epi.log
 done
 unset RAMP_B200_LIB
+timeout 300 python scripts/profile_tick.py > ${O}_tick_levels.txt 2> ${O}_tick_levels.err; tail -4 ${O}_tick_levels.txt
