@@ -304,8 +304,8 @@ def run_ours(args):
 # ---------------------------------------------------------------------------------------------------
 def cfg_b1024_ours(dev, model, groups, hc, zeros_traj, B=1024):
     from ramp_b200.sample_functions import ddpm_sample_fn
-    was = model.compose
-    model.compose = False
+    was, was_graph = model.compose, model.cuda_graph
+    model.compose, model.cuda_graph = False, True          # capture at the first (warm-up) call, time replays
     cloud = groups[0].contiguous()
 
     def run():
@@ -313,7 +313,7 @@ def cfg_b1024_ours(dev, model, groups, hc, zeros_traj, B=1024):
                             obstacle_pts=cloud, sample_fn=ddpm_sample_fn, noise_std_extra_schedule_fn=lambda t: 0.5)
 
     ms = _time_gpu(run, 3, warm=2)
-    model.compose = was
+    model.compose, model.cuda_graph = was, was_graph
     return {"batch": B, "network_rows_per_step": 2 * B, "ms_per_sampling": ms, "trajectories_per_s": B / (ms * 1e-3),
             "network_rows_per_s": 2 * B * T / (ms * 1e-3)}
 
@@ -579,6 +579,7 @@ def maze3d_section(dev, gpu_index, B=1024):
     m = GaussianDiffusionModel3d(model=net, n_diffusion_steps=T, predict_epsilon=True)
     m.load_state_dict(synthetic_state_dict(m, 0))
     m = m.to(dev).eval()
+    m.cuda_graph = True                                                        # capture at the first (warm-up) call, time replays
     enc_cloud = synthetic_cloud_3d().to(dev)                                   # [25, 64, 3]
     gen = torch.Generator("cpu").manual_seed(11)
     centres = synthetic_cloud_3d().mean(dim=1)                                  # the same 25 obstacles, resampled densely
@@ -595,6 +596,7 @@ def maze3d_section(dev, gpu_index, B=1024):
         sel_host.copy_(ops.select_best(terms), non_blocking=True)
 
     ms = _time_gpu(step, 3, warm=2)
+    m.cuda_graph = False                         # the per-class events are recorded by the host-side launch code: eager step
     m.model.profile(True)
     step()
     prof_ms, prof_n = m.model.profile(False, fetch=True)

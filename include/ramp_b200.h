@@ -118,13 +118,16 @@ int ramp_smooth_segment(float* x, int B, int H, int D, int start, int n, float d
 /* ---- point cloud: nearest point, APF, cost, selection ------------------------------------------
  * ramp_cloud_pack: cloud [P, dim] fp32 -> packed buffer of ramp_cloud_packed_points(P) float4
  * ramp_nn_query  : cKDTree.query(k=1, distance_upper_bound) (APFhelper.py:17-35): for q[i*qstride + 0..dim-1],
- *                  out_dist = distance (inf if >= upper_bound), out_idx = index (P if none). */
+ *                  out_dist = distance (inf if >= upper_bound), out_idx = index (P if none), exact in fp32 with the lowest
+ *                  index on ties.  perm (may be NULL): the packed cloud is a permutation of the caller's cloud (a spatially
+ *                  sorted copy, which keeps the exact-tie fallback rare on dense clouds); perm[i] = caller's index of
+ *                  packed point i, and out_idx / the tie rule refer to the caller's order. */
 size_t ramp_cloud_packed_points(int P);
 /* FP32 FMA micro-benchmark (measurement aid): fills every SM with independent FFMA chains on `stream`, waits,
  * and writes the achieved TFLOP/s (2 flops per FFMA) to *tflops_host: the denominator of the nearest-point kernel's roofline. */
 int ramp_fp32_fma_probe(float* tflops_host, void* stream);
 int ramp_cloud_pack(const float* cloud, int P, int dim, void* packed, void* stream);
-int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int qstride, float upper_bound,
+int ramp_nn_query(const void* packed, const int32_t* perm, int P, int dim, const float* q, int Q, int qstride, float upper_bound,
                   float* out_dist, int32_t* out_idx, void* stream);
 /* avoidance (APFhelper.py:37-104): windowed Gaussian push away from the nearest point; out may alias x */
 int ramp_apf_static(const float* x, int B, int H, int D, int dim, const float* dist, const int32_t* idx,

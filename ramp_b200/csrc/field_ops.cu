@@ -61,7 +61,8 @@ __device__ __forceinline__ float nn_key(const float4 p, float mx, float my, floa
 
 // R = waypoints per thread (register blocking), TILE = cloud points per shared-memory buffer (two buffers per CTA)
 template <int DIM, int R, int TILE>
-__global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __restrict__ cloud4, int P, int Ppad,
+__global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __restrict__ cloud4, const int* __restrict__ perm,
+                                                              int P, int Ppad,
                                                               const float* __restrict__ q, int Q, int qstride, float thr,
                                                               float* __restrict__ out_d, int* __restrict__ out_idx) {
   extern __shared__ __align__(128) unsigned char nn_smem[];
@@ -128,8 +129,11 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
   // from d^2 - |q|^2: |error| <= 2^-24 (4 |p|^2 + 2 |q| |p| + |k|), with |p| <= |q| + d.  Every chunk whose minimum key lies
   // within twice that bound (+ margin) of the best key may hold the true nearest point and is re-scanned with the direct
   // form (q - p)^2, lowest index winning ties: the winning chunk, the runner-up chunk, and - when a THIRD chunk is that
-  // close too (dense clouds: the 1 M-point sweep has a mean nearest d^2 of 1e-6, the size of the bound itself) - the whole
-  // cloud, by the warp together (the lanes stride over the points, then an argmin reduction).
+  // close too (dense clouds: the 1 M-point sweep has a median nearest d^2 of 1e-6, the size of the bound itself) - the whole
+  // cloud, by the warp together (the lanes stride over the points, then an argmin reduction).  That fallback reads the
+  // whole cloud from L2 per query, so large clouds are packed in MORTON ORDER (ramp_b200/ops.py, `perm` = sorted position ->
+  // caller's index): near-tie points are spatial neighbours of each other, hence of the same or the adjacent chunk, and a
+  // third tying chunk becomes rare (measured: 2-D sweep shape 131 ms unsorted -> see profiles/r2_*).
   const int lane = tid & 31;
 #pragma unroll
   for (int r = 0; r < R; ++r) {
@@ -155,7 +159,7 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
           const float dx = qx - p.x, dy = qy - p.y;
           float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
           if (DIM == 3) { const float dz = qz - p.z; d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
-          const int g = ch * NN_CHUNK + j;
+          const int g = perm ? perm[ch * NN_CHUNK + j] : ch * NN_CHUNK + j;      // index in the caller's order
           if (d2 < bd2 || (d2 == bd2 && g < gi)) { bd2 = d2; gi = g; }
         }
       }
@@ -165,12 +169,15 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
       const float sx = __shfl_sync(0xffffffffu, qx, src), sy = __shfl_sync(0xffffffffu, qy, src);
       const float sz = __shfl_sync(0xffffffffu, qz, src);
       float wd = FLT_MAX; int wi = P;
-      for (int g = lane; g < P; g += 32) {            // ascending g per lane: strict < keeps the lowest index
+      for (int g = lane; g < P; g += 32) {
         const float4 p = cloud4[g];
         const float dx = sx - p.x, dy = sy - p.y;
         float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
         if (DIM == 3) { const float dz = sz - p.z; d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
-        if (d2 < wd) { wd = d2; wi = g; }
+        if (d2 <= wd) {                                 // ties: lowest index in the caller's order
+          const int og = perm ? perm[g] : g;
+          if (d2 < wd || og < wi) { wd = d2; wi = og; }
+        }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
@@ -414,23 +421,23 @@ __global__ void __launch_bounds__(256) fma_probe_kernel(float* __restrict__ sink
 using namespace ramp;
 
 template <int DIM, int R, int TILE>
-static int nn_launch(const float4* c4, int P, int Ppad, const float* q, int Q, int qstride, float thr, float* od, int* oi,
-                     cudaStream_t s) {
+static int nn_launch(const float4* c4, const int* perm, int P, int Ppad, const float* q, int Q, int qstride, float thr,
+                     float* od, int* oi, cudaStream_t s) {
   static bool attr = false;
   const int smem = 2 * TILE * 16;
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(nn_query_kernel<DIM, R, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
   const int per = NN_THREADS * R;
-  nn_query_kernel<DIM, R, TILE><<<(Q + per - 1) / per, NN_THREADS, smem, s>>>(c4, P, Ppad, q, Q, qstride, thr, od, oi);
+  nn_query_kernel<DIM, R, TILE><<<(Q + per - 1) / per, NN_THREADS, smem, s>>>(c4, perm, P, Ppad, q, Q, qstride, thr, od, oi);
   RAMP_LAUNCH_OK();
   return 0;
 }
 // dispatch over the instantiated (R, TILE) pairs
 template <int DIM>
-static int nn_dispatch(int R, int TILE, const float4* c4, int P, int Ppad, const float* q, int Q, int qstride, float thr,
-                       float* od, int* oi, cudaStream_t s) {
+static int nn_dispatch(int R, int TILE, const float4* c4, const int* perm, int P, int Ppad, const float* q, int Q, int qstride,
+                       float thr, float* od, int* oi, cudaStream_t s) {
 #define RAMP_NN_CASE(r) \
-  case r: return TILE == 2048 ? nn_launch<DIM, r, 2048>(c4, P, Ppad, q, Q, qstride, thr, od, oi, s) \
-                              : nn_launch<DIM, r, 1024>(c4, P, Ppad, q, Q, qstride, thr, od, oi, s);
+  case r: return TILE == 2048 ? nn_launch<DIM, r, 2048>(c4, perm, P, Ppad, q, Q, qstride, thr, od, oi, s) \
+                              : nn_launch<DIM, r, 1024>(c4, perm, P, Ppad, q, Q, qstride, thr, od, oi, s);
   switch (R) {
     RAMP_NN_CASE(1) RAMP_NN_CASE(2) RAMP_NN_CASE(4) RAMP_NN_CASE(6) RAMP_NN_CASE(8) RAMP_NN_CASE(10) RAMP_NN_CASE(12)
   }
@@ -509,8 +516,8 @@ int ramp_cloud_pack(const float* cloud, int P, int dim, void* packed, void* stre
   return 0;
 }
 
-int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int qstride, float upper_bound,
-                  float* out_dist, int32_t* out_idx, void* stream) {
+int ramp_nn_query(const void* packed, const int32_t* perm, int P, int dim, const float* q, int Q, int qstride,
+                  float upper_bound, float* out_dist, int32_t* out_idx, void* stream) {
   RAMP_CHECK(dim == 2 || dim == 3, "ramp_nn_query: dim must be 2 or 3");
   if (Q == 0) return 0;
   RAMP_CHECK(packed && q && out_dist && out_idx, "ramp_nn_query: null argument");
@@ -520,10 +527,10 @@ int ramp_nn_query(const void* packed, int P, int dim, const float* q, int Q, int
   int R = 1, TILE = 2048;
   if (dim == 2) {
     if (nn_choose<2>(Q, &R, &TILE)) return -1;
-    return nn_dispatch<2>(R, TILE, c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+    return nn_dispatch<2>(R, TILE, c4, perm, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
   }
   if (nn_choose<3>(Q, &R, &TILE)) return -1;
-  return nn_dispatch<3>(R, TILE, c4, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
+  return nn_dispatch<3>(R, TILE, c4, perm, P, Ppad, q, Q, qstride, upper_bound, out_dist, out_idx, s);
 }
 
 int ramp_apf_static(const float* x, int B, int H, int D, int dim, const float* dist, const int32_t* idx,

@@ -299,7 +299,8 @@ int UnetEngine::finalize(cudaStream_t s) {
   RAMP_CHECK(g_missing.empty(), "state dict is incomplete or mis-shaped: " + g_missing);
   RAMP_CUDA_OK(cudaDeviceSynchronize());
 
-  // RAMP_UNET_SPLIT = n (1..4): run calls of >= RAMP_UNET_SPLIT_MIN rows as n parts on side streams (see unet_engine.cuh)
+  // RAMP_UNET_SPLIT = n (1..4, default 2): run calls of >= RAMP_UNET_SPLIT_MIN (default 2048) rows as n parts on side
+  // streams (see unet_engine.cuh)
   if (const char* v = getenv("RAMP_UNET_SPLIT")) { split_ = atoi(v); if (split_ < 1) split_ = 1; if (split_ > 4) split_ = 4; }
   if (const char* v = getenv("RAMP_UNET_SPLIT_MIN")) { split_min_rows_ = atoi(v); if (split_min_rows_ < 32) split_min_rows_ = 32; }
   // size the workspace with a dry run at max_rows (and, in split mode, as the parts it would be run as)

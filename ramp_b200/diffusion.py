@@ -250,8 +250,13 @@ class _DiffusionBase(nn.Module):
             if len(graphs) > 4:                        # each graph pins a chain and noise buffers: keep a handful
                 for k in [k for k in graphs if k != key]:
                     del graphs[k]
+            # the capture's warm-up passes draw from the default generator: put its state back afterwards, so that THIS call
+            # (the first replay) consumes exactly the draws the eager loop would have consumed
+            dev = self.betas.device
+            rng = torch.cuda.get_rng_state(dev)
             g = ent['graph'] = DdpmLoopGraph(self, B, H, hard_conds, obstacle_pts, noise_scale=list(scales),
                                              extra_steps=extra_steps, own_cloud=True)
+            torch.cuda.set_rng_state(rng, dev)
             ent['src'] = None
         g.pins.val.copy_(pins.val)
         src = (obstacle_pts.data_ptr(), obstacle_pts._version)

@@ -68,8 +68,12 @@ def _capture(fn, warmup=2):
 def _count_replay(n):
     import ctypes
     from ._lib import lib
-    lib().ramp_launch_count_add.restype = None
-    lib().ramp_launch_count_add(ctypes.c_ulonglong(n))
+    try:
+        fn = lib().ramp_launch_count_add
+    except AttributeError:          # an older A/B library without the counter hook
+        return
+    fn.restype = None
+    fn(ctypes.c_ulonglong(n))
 
 
 class DdpmLoopGraph(_EngineGuard):

@@ -106,8 +106,27 @@ def q_sample(x0, noise, out, sqrt_ac, sqrt_1mac, pins=None):
     return out
 
 
+def _morton_order(pts):
+    """argsort of the points along a Z-order curve over their bounding box (device-side torch ops, once per cloud)."""
+    P, dim = pts.shape
+    bits = 16 if dim == 2 else 10
+    lo = pts.amin(dim=0, keepdim=True)
+    span = (pts.amax(dim=0, keepdim=True) - lo).clamp_min(1e-30)
+    cell = ((pts - lo) / span * (2 ** bits - 1)).round().to(torch.int64).clamp_(0, 2 ** bits - 1)
+    code = torch.zeros(P, dtype=torch.int64, device=pts.device)
+    for b in range(bits):
+        for d in range(dim):
+            code |= ((cell[:, d] >> b) & 1) << (b * dim + d)
+    return torch.argsort(code, stable=True).to(torch.int32)
+
+
 class CloudIndex:
-    """A point cloud resident in HBM in the packed layout of the nearest-point kernel."""
+    """A point cloud resident in HBM in the packed layout of the nearest-point kernel.  Clouds of >= SORT_MIN points are
+    also kept in Morton order for the queries (`packed_sorted`, `perm`): the kernel's exact-tie fallback re-scans the whole
+    cloud when three 64-point chunks tie within the rounding bound of the scan key, which on dense clouds (the 1 M-point
+    sweep) is common in arrival order and rare once near-tie points — spatial neighbours — share a chunk.  Indices returned
+    by `query` always refer to the caller's order; `packed` (caller's order) is what the APF kernels fetch neighbours from."""
+    SORT_MIN = 16384
 
     def __init__(self, points):
         pts = points.detach().reshape(-1, points.shape[-1]).to(torch.float32).contiguous()
@@ -118,11 +137,19 @@ class CloudIndex:
         lib().ramp_cloud_packed_points.restype = ctypes.c_size_t
         n = int(lib().ramp_cloud_packed_points(self.P))
         self.packed = torch.empty(n, 4, device=pts.device)
-        check(lib().ramp_cloud_pack(ptr(pts), self.P, self.dim, ptr(self.packed), _stream()), "ramp_cloud_pack")
+        self.perm, self.packed_sorted = None, None
+        self.repack()
 
     def repack(self):
-        """Re-pack after `self.points` was updated in place (a moving pursuer): one kernel, graph-capturable."""
+        """(Re-)pack after `self.points` was set or updated in place (a moving pursuer).  Small clouds: one kernel,
+        graph-capturable; clouds of >= SORT_MIN points are re-sorted too (torch ops)."""
         check(lib().ramp_cloud_pack(ptr(self.points), self.P, self.dim, ptr(self.packed), _stream()), "ramp_cloud_pack")
+        if self.P >= self.SORT_MIN:
+            self.perm = _morton_order(self.points)
+            srt = self.points.index_select(0, self.perm.long()).contiguous()
+            if self.packed_sorted is None:
+                self.packed_sorted = torch.empty_like(self.packed)
+            check(lib().ramp_cloud_pack(ptr(srt), self.P, self.dim, ptr(self.packed_sorted), _stream()), "ramp_cloud_pack")
         return self
 
     def query(self, x, upper_bound, dist=None, idx=None):
@@ -131,8 +158,9 @@ class CloudIndex:
         Q = x.numel() // x.shape[-1]
         dist = torch.empty(x.shape[:-1], device=x.device) if dist is None else dist
         idx = torch.empty(x.shape[:-1], device=x.device, dtype=torch.int32) if idx is None else idx
-        check(lib().ramp_nn_query(ptr(self.packed), self.P, self.dim, ptr(x), Q, x.shape[-1], _c_float(upper_bound),
-                                  ptr(dist), ptr(idx), _stream()), "ramp_nn_query")
+        packed = self.packed if self.perm is None else self.packed_sorted
+        check(lib().ramp_nn_query(ptr(packed), ptr(self.perm), self.P, self.dim, ptr(x), Q, x.shape[-1],
+                                  _c_float(upper_bound), ptr(dist), ptr(idx), _stream()), "ramp_nn_query")
         return dist, idx
 
 
