@@ -224,10 +224,8 @@ def run_ours(args):
     model.cuda_graph = graph_mode
 
     extras = {}
-    if rank == 0 and not args.no_sections:
-        cfg2d = None
-        if world == 1:
-            cfg2d = cfg_b1024_ours(dev, model, groups, hc, zeros_traj)
+    if world == 1 and not args.no_sections:          # the other BASELINE configs: single-GPU sections of the N = 1 line only
+        cfg2d = cfg_b1024_ours(dev, model, groups, hc, zeros_traj)
         extras["scene_encoder"] = scene_encoder_latency(dev, model, local)
         model.model.release_engine()
         torch.cuda.empty_cache()
@@ -239,9 +237,8 @@ def run_ours(args):
             extras["replan_single_mma_non_parity"]["note"] = "hi*hi only (one MMA per product): breaks north_star's 1e-3 waypoint tolerance, reported for context, never the headline"
         extras["field"] = field_roofline(dev, local)
         extras["maze3d"] = maze3d_section(dev, local)
-        if world == 1:
-            extras["sweep"] = sweep_section(dev, 8192, "per-GPU share of the 65,536-trajectory sweep at 8 GPUs")
-            extras["reference_gpu_eager"] = reference_gpu_eager(dev, cfg2d)
+        extras["sweep"] = sweep_section(dev, 8192, "per-GPU share of the 65,536-trajectory sweep at 8 GPUs")
+        extras["reference_gpu_eager"] = reference_gpu_eager(dev, cfg2d)
     if rank == 0:
         peak_tf, peak_bw, how = peaks()
         rows_per_step = B * (G + 1) * T
