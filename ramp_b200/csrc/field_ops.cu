@@ -21,6 +21,11 @@ namespace ramp {
 static constexpr int NN_CHUNK = 64;          // argmin recovery granularity (points)
 static constexpr int NN_TILE = 2048;         // points per shared-memory tile (32 KB)
 static constexpr int NN_THREADS = 128;
+// RAMP_NN_TOP3 = 1: the scan tracks the three smallest chunk minima with their chunks (+ the value of the fourth); 0: two (+ the
+// value of the third).  More tracked chunks = fewer whole-cloud fallbacks on dense clouds, more registers per waypoint.
+#ifndef RAMP_NN_TOP3
+#define RAMP_NN_TOP3 1
+#endif
 
 // cloud [P, d] -> packed float4 (x, y, z|0, |p|^2), padded to a multiple of NN_TILE with +inf norms
 __global__ void nn_pack_kernel(const float* __restrict__ cloud, int P, int dim, int Ppad, float4* __restrict__ out) {
@@ -61,7 +66,7 @@ __device__ __forceinline__ float nn_key(const float4 p, float mx, float my, floa
 
 // R = waypoints per thread (register blocking), TILE = cloud points per shared-memory buffer (two buffers per CTA)
 template <int DIM, int R, int TILE>
-__global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __restrict__ cloud4, const int* __restrict__ perm,
+__global__ void __launch_bounds__(NN_THREADS, RAMP_NN_TOP3 ? (R >= 8 ? 3 : (R >= 6 ? 4 : 6)) : 1) nn_query_kernel(const float4* __restrict__ cloud4, const int* __restrict__ perm,
                                                               int P, int Ppad,
                                                               const float* __restrict__ q, int Q, int qstride, float thr,
                                                               float* __restrict__ out_d, int* __restrict__ out_idx) {
@@ -87,8 +92,8 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
   };
   if (tid == 0) issue(0);
 
-  float mx[R], my[R], mz[R], best[R], second[R], third[R];
-  int bchunk[R], schunk[R];
+  float mx[R], my[R], mz[R], best[R], second[R], third[R], fourth[R];
+  int bchunk[R], schunk[R], tchunk[R];
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const int qi = (blockIdx.x * R + r) * NN_THREADS + tid;
@@ -98,7 +103,7 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
       my[r] = -2.f * q[(size_t)qi * qstride + 1];
       if (DIM == 3) mz[r] = -2.f * q[(size_t)qi * qstride + 2];
     }
-    best[r] = second[r] = third[r] = FLT_MAX; bchunk[r] = schunk[r] = 0;
+    best[r] = second[r] = third[r] = fourth[r] = FLT_MAX; bchunk[r] = schunk[r] = tchunk[r] = 0;
   }
   for (int t = 0; t < ntiles; ++t) {
     if (tid == 0 && t + 1 < ntiles) issue(t + 1);
@@ -117,10 +122,25 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
       }
       const int gc = t * (TILE / NN_CHUNK) + c;
 #pragma unroll
-      for (int r = 0; r < R; ++r) {   // the two smallest chunk minima with their chunks, and the value of the third
+      for (int r = 0; r < R; ++r) {   // the three smallest chunk minima with their chunks, and the value of the fourth
+#if !RAMP_NN_TOP3
         if (cm[r] < best[r]) { third[r] = second[r]; second[r] = best[r]; schunk[r] = bchunk[r]; best[r] = cm[r]; bchunk[r] = gc; }
         else if (cm[r] < second[r]) { third[r] = second[r]; second[r] = cm[r]; schunk[r] = gc; }
         else third[r] = fminf(third[r], cm[r]);
+#else
+        if (cm[r] < fourth[r]) {      // rare after the first few chunks: most chunks are nowhere near this waypoint
+          if (cm[r] < best[r]) {
+            fourth[r] = third[r]; third[r] = second[r]; tchunk[r] = schunk[r]; second[r] = best[r]; schunk[r] = bchunk[r];
+            best[r] = cm[r]; bchunk[r] = gc;
+          } else if (cm[r] < second[r]) {
+            fourth[r] = third[r]; third[r] = second[r]; tchunk[r] = schunk[r]; second[r] = cm[r]; schunk[r] = gc;
+          } else if (cm[r] < third[r]) {
+            fourth[r] = third[r]; third[r] = cm[r]; tchunk[r] = gc;
+          } else {
+            fourth[r] = cm[r];
+          }
+        }
+#endif
       }
     }
     __syncthreads();
@@ -128,9 +148,9 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
   // Exact decision.  The scan key k = |p|^2 - 2 q.p is three roundings of |p|^2 (pack) and two fused multiply-adds away
   // from d^2 - |q|^2: |error| <= 2^-24 (4 |p|^2 + 2 |q| |p| + |k|), with |p| <= |q| + d.  Every chunk whose minimum key lies
   // within twice that bound (+ margin) of the best key may hold the true nearest point and is re-scanned with the direct
-  // form (q - p)^2, lowest index winning ties: the winning chunk, the runner-up chunk, and - when a THIRD chunk is that
-  // close too (dense clouds: the 1 M-point sweep has a median nearest d^2 of 1e-6, the size of the bound itself) - the whole
-  // cloud, by the warp together (the lanes stride over the points, then an argmin reduction).  That fallback reads the
+  // form (q - p)^2, lowest index winning ties: the winning chunk, the two runner-up chunks, and - when a FOURTH chunk is
+  // that close too (dense clouds: the 1 M-point sweep has a median nearest d^2 of 1e-6, the size of the bound itself) - the
+  // whole cloud, by the warp together (the lanes stride over the points, then an argmin reduction).  That fallback reads the
   // whole cloud from L2 per query, so large clouds are packed in MORTON ORDER (ramp_b200/ops.py, `perm` = sorted position ->
   // caller's index): near-tie points are spatial neighbours of each other, hence of the same or the adjacent chunk, and a
   // third tying chunk becomes rare (measured: 2-D sweep shape 131 ms unsorted -> see profiles/r2_*).
@@ -146,12 +166,17 @@ __global__ void __launch_bounds__(NN_THREADS) nn_query_kernel(const float4* __re
     const float qn = sqrtf(q2), pn = qn + sqrtf(fmaxf(best[r] + q2, 0.f));
     const float tol = 1.5e-7f * (4.f * pn * pn + 2.f * qn * pn + fabsf(best[r])) + 1e-30f;    // 2.5 x 2^-24 x (...)
     float bd2 = FLT_MAX; int gi = P;
+#if RAMP_NN_TOP3
+    const bool crowded = live && fourth[r] <= best[r] + tol;
+    const int ncand = second[r] <= best[r] + tol ? (third[r] <= best[r] + tol ? 3 : 2) : 1;
+#else
     const bool crowded = live && third[r] <= best[r] + tol;
+    const int ncand = second[r] <= best[r] + tol ? 2 : 1;
+#endif
     const unsigned need = __ballot_sync(0xffffffffu, crowded);
     if (live && !crowded) {
-      const int ncand = (second[r] <= best[r] + tol && schunk[r] != bchunk[r]) ? 2 : 1;
       for (int cnd = 0; cnd < ncand; ++cnd) {
-        const int ch = cnd == 0 ? bchunk[r] : schunk[r];
+        const int ch = cnd == 0 ? bchunk[r] : (cnd == 1 ? schunk[r] : tchunk[r]);
         const float4* cp = cloud4 + (size_t)ch * NN_CHUNK;
         for (int j = 0; j < NN_CHUNK; ++j) {
           const float4 p = cp[j];

@@ -109,6 +109,53 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+// ---- CTA-pair (cta_group::2) variants: M = 256 tile over two SMs of a TPC; each CTA stages its own 128 A rows and HALF of
+// the B rows, the leader CTA (cluster rank 0) issues the MMAs for both, commits are multicast to both CTAs' barriers ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA loads of a CTA pair signal the LEADER's mbarrier: same smem offset, peer bit (24) of the cluster address cleared
+static constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;
+__device__ __forceinline__ void tma_load_4d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
+                                                 int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar & PEER_BIT_MASK), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar & PEER_BIT_MASK), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {        // arrives on `bar` in BOTH CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+// arrive on the barrier at the same smem offset in cluster CTA `rank`
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(bar), "r"(rank) : "memory");
+}
+
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                           uint32_t accumulate) {
   asm volatile(
@@ -534,7 +581,10 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx<CW>
 // kernel
 // ---------------------------------------------------------------------------------------------
 // One instantiation per epilogue mode: each gets its own register allocation (the modes' live sets differ a lot).
-template <int EPI, int CW>
+// CG = CTAs per tile: 1, or 2 = a CTA pair (cluster of two) on one 256 x BN tile (tcgen05 cta_group::2): every CTA stages its
+// own 128 A rows but only BN / 2 rows of the weights, which cuts the L2 -> SM operand traffic per MMA by a third (the cap
+// that bounds the weight-heavy launches: ~6300 B / clk chip-wide, B300_MICROARCH.md; FF1^T at L = 64 ran at 9.5 TB/s).
+template <int EPI, int CW, int CG>
 __global__ void __launch_bounds__(gemm_threads(CW), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant__ CUtensorMap mapAlo,
                const __grid_constant__ CUtensorMap mapBhi, const __grid_constant__ CUtensorMap mapBlo,
@@ -543,7 +593,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b_tile_bytes = p.BN * BK * 2;
+  const int cta_rank = CG == 2 ? (int)cluster_ctarank() : 0;
+  const int b_tile_bytes = (p.BN / CG) * BK * 2;        // this CTA's share of the weight tile
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + b_tile_bytes);
   const uint32_t stg_base = smem_base + p.stages * stage_bytes;            // the epilogue warps' staging tiles
   const uint32_t bar_base = stg_base + STG_BYTES;
@@ -551,24 +602,33 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   const uint32_t tfull0 = bar_base + 16 * p.stages, tempty0 = tfull0 + 16;  // 2 + 2 accumulator barriers
   const uint32_t tmem_slot = tempty0 + 16;
   const int iters = p.ntaps * p.kblocks;
-  const int total_tiles = p.m_tiles * p.n_tiles;
+  // work units: (tile pair along M) x n-tile; unit u -> m-tile CG * (u / n_tiles) + cta_rank (an odd tile count leaves the
+  // last pair's second CTA an out-of-range tile: its TMA boxes are zero-filled, its rows masked in the epilogue)
+  const int total_tiles = ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
+  const int unit0 = blockIdx.x / CG, unit_step = gridDim.x / CG;
   uint32_t tmem_cols = 32;
   while ((int)tmem_cols < 2 * p.BN) tmem_cols <<= 1;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(tfull0 + 8 * b, 1); mbar_init(tempty0 + 8 * b, 4 * p.ngroups); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull0 + 8 * b, 1); mbar_init(tempty0 + 8 * b, 4 * p.ngroups * CG); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAhi) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBhi) : "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if constexpr (CG == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();     // barriers and TMEM of BOTH CTAs exist from here on
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   uint32_t tmem_acc;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_acc) : "r"(tmem_slot));
@@ -586,9 +646,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
     // ---------------- TMA producer ----------------
     if (lane == 0) {
       int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
-        const int c3 = tile_m * p.nb;
+      for (int tile = unit0; tile < total_tiles; tile += unit_step) {
+        const int pair_m = tile / p.n_tiles, tile_n = tile - pair_m * p.n_tiles;
+        const int c3 = (pair_m * CG + cta_rank) * p.nb;
         for (int t = 0; t < p.ntaps; ++t) {
           for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
             const int s = it % p.stages;
@@ -596,33 +656,45 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
             mbar_wait(empty0 + 8 * s, ph ^ 1);
             const uint32_t st = smem_base + s * stage_bytes;
             const uint32_t fb = full0 + 8 * s;
-            mbar_expect_tx(fb, (uint32_t)(p.nplanes * (p.nb * p.L_out * BK * 2 + b_tile_bytes)));
-            tma_load_4d(st, &mapAhi, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3);
-            uint32_t off = A_TILE_BYTES;
-            if (p.nplanes == 2) { tma_load_4d(st + off, &mapAlo, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3); off += A_TILE_BYTES; }
-            tma_load_2d(st + off, &mapBhi, fb, kb * BK, p.tap_wrow[t] + tile_n * p.BN);
-            off += b_tile_bytes;
-            if (p.nplanes == 2) tma_load_2d(st + off, &mapBlo, fb, kb * BK, p.tap_wrow[t] + tile_n * p.BN);
+            const int brow = p.tap_wrow[t] + tile_n * p.BN + cta_rank * (p.BN / CG);
+            if constexpr (CG == 2) {
+              // the leader's barrier collects the bytes of both CTAs; only the leader arrives on it
+              if (cta_rank == 0) mbar_expect_tx(fb, (uint32_t)(2 * p.nplanes * (A_TILE_BYTES + b_tile_bytes)));
+              tma_load_4d_pair(st, &mapAhi, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3);
+              uint32_t off = A_TILE_BYTES;
+              if (p.nplanes == 2) { tma_load_4d_pair(st + off, &mapAlo, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3); off += A_TILE_BYTES; }
+              tma_load_2d_pair(st + off, &mapBhi, fb, kb * BK, brow);
+              off += b_tile_bytes;
+              if (p.nplanes == 2) tma_load_2d_pair(st + off, &mapBlo, fb, kb * BK, brow);
+            } else {
+              mbar_expect_tx(fb, (uint32_t)(p.nplanes * (p.nb * p.L_out * BK * 2 + b_tile_bytes)));
+              tma_load_4d(st, &mapAhi, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3);
+              uint32_t off = A_TILE_BYTES;
+              if (p.nplanes == 2) { tma_load_4d(st + off, &mapAlo, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3); off += A_TILE_BYTES; }
+              tma_load_2d(st + off, &mapBhi, fb, kb * BK, brow);
+              off += b_tile_bytes;
+              if (p.nplanes == 2) tma_load_2d(st + off, &mapBlo, fb, kb * BK, brow);
+            }
           }
         }
       }
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer ----------------
-    if (lane == 0) {
+    if (lane == 0 && cta_rank == 0) {       // a CTA pair's MMAs are issued by its leader alone
       // instruction descriptor: D = f32 (bit 4), A format bits [7,10), B format bits [10,13) (0 = f16, 1 = bf16), both
-      // K-major, N = BN, M = 128.  A and B of one MMA must share a format (a mixed f16 x bf16 descriptor is an illegal
-      // instruction on B200).
-      const uint32_t idesc0 = (1u << 4) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      // K-major, N = BN, M = 128 per CTA.  A and B of one MMA must share a format (a mixed f16 x bf16 descriptor is an
+      // illegal instruction on B200).
+      const uint32_t idesc0 = (1u << 4) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)((BM * CG) >> 4) << 24);
 #if RAMP_PLANES_FP16
       const uint32_t idesc_lh = idesc0, idesc_hl = idesc0, idesc_hh = idesc0;                 // all planes fp16
 #else
       const uint32_t idesc_lh = idesc0 | (1u << 7) | (1u << 10), idesc_hl = idesc_lh, idesc_hh = idesc_lh;   // all bf16
 #endif
       int it = 0, lt = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      for (int tile = unit0; tile < total_tiles; tile += unit_step, ++lt) {
         const int buf = lt & 1;
-        mbar_wait(tempty0 + 8 * buf, ((lt >> 1) & 1) ^ 1);      // epilogue has drained this accumulator
+        mbar_wait(tempty0 + 8 * buf, ((lt >> 1) & 1) ^ 1);      // epilogue (of both CTAs) has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t dacc = tmem_acc + (uint32_t)(buf * p.BN);
         for (int i = 0; i < iters; ++i, ++it) {
@@ -639,7 +711,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
           for (int k = 0; k < BK / 16; ++k) {
             const uint32_t ko = k * 32;   // 16 bf16 = 32 B inside the 128 B swizzle row
             const uint32_t first = (i == 0 && k == 0) ? 0u : 1u;
-            if (p.nplanes == 2) {
+            if constexpr (CG == 2) {
+              if (p.nplanes == 2) {
+                umma_f16_pair(dacc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc_lh, first);
+                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc_hl, 1u);
+                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, 1u);
+              } else {
+                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, first);
+              }
+            } else if (p.nplanes == 2) {
               umma_bf16(dacc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc_lh, first);
               umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc_hl, 1u);
               umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, 1u);
@@ -647,9 +727,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
               umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, first);
             }
           }
-          umma_commit(empty0 + 8 * s);           // frees the smem stage when these MMAs retire
+          if constexpr (CG == 2) umma_commit_pair(empty0 + 8 * s); else umma_commit(empty0 + 8 * s);   // frees the smem stage (of both CTAs) when these MMAs retire
         }
-        umma_commit(tfull0 + 8 * buf);            // accumulator complete
+        if constexpr (CG == 2) umma_commit_pair(tfull0 + 8 * buf); else umma_commit(tfull0 + 8 * buf);   // accumulator complete
       }
     }
   }
@@ -675,8 +755,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
       const int r = q * 32 + lane;
       const int n_local = r / p.L_out, l = r - n_local * p.L_out;
       int lt = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-        const int tile_m = tile / p.n_tiles, tile_n = tile - tile_m * p.n_tiles;
+      for (int tile = unit0; tile < total_tiles; tile += unit_step, ++lt) {
+        const int pair_m = tile / p.n_tiles, tile_n = tile - pair_m * p.n_tiles;
+        const int tile_m = pair_m * CG + cta_rank;
         const int buf = lt & 1;
         e.my_sample = tile_m * p.nb + n_local;
         e.my_ok = n_local < p.nb && e.my_sample < p.n_samples;
@@ -700,15 +781,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
         else epi_ln_bwd<CW, NG>(p, e, acc, c0, c1);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncwarp();
-        if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
+        if (lane == 0) {
+          if (CG == 2 && cta_rank != 0) mbar_arrive_remote(tempty0 + 8 * buf, 0);      // the leader's issuer waits for both CTAs
+          else mbar_arrive(tempty0 + 8 * buf);
+        }
       }
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(tmem_cols) : "memory");
+    if constexpr (CG == 2)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(tmem_cols) : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(tmem_cols) : "memory");
   }
 }
 
@@ -723,6 +810,11 @@ static int g_max_smem = 0;
 static int g_num_sms = 148;
 // tuning knob (environment, read once): RAMP_GEMM_L2PROMO=128|256 picks the tensor-map L2 promotion
 static int g_l2promo = 256;
+// RAMP_GEMM_PAIR: 0 = every tile on one CTA; 1 = CTA pairs (cta_group::2) for launches with BN >= 128 and enough M tiles
+#ifndef RAMP_GEMM_PAIR_DEFAULT
+#define RAMP_GEMM_PAIR_DEFAULT 0
+#endif
+static int g_pair = RAMP_GEMM_PAIR_DEFAULT;
 
 int gemm_init() {
   if (g_encode) return 0;
@@ -735,13 +827,14 @@ int gemm_init() {
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   RAMP_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   const int dyn = g_max_smem;
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_PLAIN, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_PLAIN, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_GEGLU_FWD, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_GEGLU_BWD, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_LN_FWD, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<EPI_LN_BWD, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+#define RAMP_GEMM_ATTR(E, C)                                                                                         \
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<E, C, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));      \
+  RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<E, C, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+  RAMP_GEMM_ATTR(EPI_PLAIN, 32) RAMP_GEMM_ATTR(EPI_PLAIN, 16) RAMP_GEMM_ATTR(EPI_GEGLU_FWD, 16)
+  RAMP_GEMM_ATTR(EPI_GEGLU_BWD, 32) RAMP_GEMM_ATTR(EPI_LN_FWD, 32) RAMP_GEMM_ATTR(EPI_LN_BWD, 32)
+#undef RAMP_GEMM_ATTR
   if (const char* v = getenv("RAMP_GEMM_L2PROMO")) g_l2promo = atoi(v);
+  if (const char* v = getenv("RAMP_GEMM_PAIR")) g_pair = atoi(v);
   g_encode = (EncodeTiledFn)fn;
   return 0;
 }
@@ -839,11 +932,13 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   const int cw = (d.epi == EPI_GEGLU_FWD || p.BN == 16) ? 16 : 32;     // epilogue configuration (see epi_warps)
   p.ngroups = p.BN / cw < epi_warps(cw) / 4 ? p.BN / cw : epi_warps(cw) / 4;
   p.nplanes = d.precision == 3 ? 2 : 1;
-  const int stage_bytes = p.nplanes * (A_TILE_BYTES + p.BN * BK * 2);
+  // CTA pairs: worth it where the weight tile is large (BN >= 128) and there are enough tile pairs to fill the pairs of SMs
+  const int cg = (g_pair && p.BN >= 128 && (long)((p.m_tiles + 1) / 2) * p.n_tiles >= g_num_sms / 2) ? 2 : 1;
+  const int stage_bytes = p.nplanes * (A_TILE_BYTES + (p.BN / cg) * BK * 2);
   const int fixed = 1024 + STG_BYTES + 256;
   int stages = (g_max_smem - fixed) / stage_bytes;
   if (stages > 6) stages = 6;
-  const long total_iters = (long)p.ntaps * p.kblocks * ((long)p.m_tiles * p.n_tiles + g_num_sms - 1) / g_num_sms;
+  const long total_iters = (long)p.ntaps * p.kblocks * ((long)((p.m_tiles + cg - 1) / cg) * p.n_tiles + g_num_sms / cg - 1) / (g_num_sms / cg);
   if (stages > total_iters) stages = (int)total_iters;
   RAMP_CHECK(stages >= 1, "gemm: tile does not fit shared memory");
   p.stages = stages;
@@ -870,27 +965,38 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   {
     uint64_t dims[2] = {(uint64_t)d.K, (uint64_t)d.n_wtaps * d.Nout};
     uint64_t str[1] = {(uint64_t)d.Kw * 2};
-    uint32_t box[2] = {(uint32_t)BK, (uint32_t)p.BN};
+    uint32_t box[2] = {(uint32_t)BK, (uint32_t)(p.BN / cg)};      // a CTA of a pair stages half of the tile's weight rows
     if (make_map(&mBhi, d.w_hi, 2, dims, str, box)) return -3;
     if (p.nplanes == 2) { if (make_map(&mBlo, d.w_lo, 2, dims, str, box)) return -3; } else mBlo = mBhi;
   }
   const size_t smem = (size_t)stages * stage_bytes + fixed;
-  const long tiles = (long)p.m_tiles * p.n_tiles;
-  dim3 grid((unsigned)(tiles < g_num_sms ? tiles : g_num_sms));
+  const long tiles = (long)((p.m_tiles + cg - 1) / cg) * p.n_tiles * cg;      // CTAs that have work
+  const long max_ctas = g_num_sms / cg * cg;
+  dim3 grid((unsigned)(tiles < max_ctas ? tiles : max_ctas));
   // RAMP_PDL=1: launch with programmatic stream serialization, so this kernel's prologue overlaps the tail of the previous
   // kernel in the stream (it blocks at griddepcontrol.wait until that kernel has completed and flushed)
   const int use_pdl = pdl_mode() & 1;
   cudaLaunchConfig_t cfg;
   std::memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = grid; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-  cudaLaunchAttribute pdl_attr[1];
-  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = pdl_attr; cfg.numAttrs = use_pdl ? 1 : 0;
+  cudaLaunchAttribute attrs[2];
+  int na = 0;
+  if (use_pdl) {
+    attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (cg == 2) {
+    attrs[na].id = cudaLaunchAttributeClusterDimension;
+    attrs[na].val.clusterDim.x = 2; attrs[na].val.clusterDim.y = 1; attrs[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = attrs; cfg.numAttrs = na;
 #define RAMP_GEMM_LAUNCH(E, C)                                                                       \
   do {                                                                                               \
     cfg.blockDim = dim3(gemm_threads(C));                                                            \
-    RAMP_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<E, C>, mAhi, mAlo, mBhi, mBlo, p));         \
+    if (cg == 2) RAMP_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<E, C, 2>, mAhi, mAlo, mBhi, mBlo, p));  \
+    else RAMP_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<E, C, 1>, mAhi, mAlo, mBhi, mBlo, p));          \
   } while (0)
   switch (d.epi) {
     case EPI_PLAIN: if (cw == 16) RAMP_GEMM_LAUNCH(EPI_PLAIN, 16); else RAMP_GEMM_LAUNCH(EPI_PLAIN, 32); break;

@@ -109,3 +109,22 @@ def test_transposed_up(cuda):
     out = (ev + od).double().reshape(n, 2 * L, C)
     ref = F.conv_transpose1d(ar.transpose(1, 2), wr.permute(2, 1, 0), stride=2, padding=1).transpose(1, 2)
     assert (out - ref).abs().max().item() < 5e-5
+
+
+@pytest.mark.parametrize("n,L,K,Nout", [(600, 64, 256, 256), (601, 64, 256, 768), (2400, 8, 2048, 256), (1203, 16, 256, 2048)])
+def test_linear_many_tiles(cuda, n, L, K, Nout):
+    """Enough M tiles to fill the GPU (and an odd tile count): the shapes where RAMP_GEMM_PAIR=1 puts a 256-row tile on a CTA
+    pair (tcgen05 cta_group::2, half of the weight rows staged per CTA); the same test runs in either mode."""
+    g = torch.Generator(device="cpu").manual_seed(n + K)
+    a = torch.randn(n, L, K, generator=g).to(cuda)
+    w = (torch.randn(1, Nout, K, generator=g) / K ** 0.5).to(cuda)
+    bias = torch.randn(Nout, generator=g).to(cuda)
+    res = torch.randn(n * L, Nout, generator=g).to(cuda)
+    out, (oh, ol), ar, wr = _gemm(a, w, [(0, 0, 0)], L, bias=bias, residual=res, want_split=True)
+    # fp64 reference in row blocks (the full product is 38400 x 2048 x 256)
+    err = 0.0
+    for s in range(0, n * L, 8192):
+        r = ar.reshape(-1, K)[s:s + 8192] @ wr[0].T + bias.double() + res[s:s + 8192].double()
+        err = max(err, (out[s:s + 8192].double() - r).abs().max().item() / max(1.0, r.abs().max().item()))
+    assert err < 2e-5, err
+    assert (oh.float() + ol.float() - out).abs().max().item() < 1e-4
