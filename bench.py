@@ -253,7 +253,8 @@ def run_ours(args):
             if os.path.exists(tpath) and prof_n["gemm"] > 0:
                 with open(tpath) as f:
                     tj = json.load(f)
-                traffic = tj["dram_bytes_per_launch"]
+                # the ncu pass covers `rows` network rows per launch; the profiled (unsplit) launches cover B * (G + 1)
+                traffic = tj["dram_bytes_per_launch"] * (B * (G + 1) / float(tj.get("rows", B * (G + 1))))
                 gbps = traffic * prof_n["gemm"] / (prof_ms["gemm"] * 1e-3) / 1e9
                 hbm_view = {"achieved": gbps, "peak": peak_bw, "unit": "GB/s", "frac": gbps / peak_bw, "source": name,
                             "taken_at_commit": tj.get("commit"),
