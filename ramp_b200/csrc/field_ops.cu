@@ -18,13 +18,17 @@
 
 namespace ramp {
 
-static constexpr int NN_CHUNK = 64;          // argmin recovery granularity (points)
+static constexpr int NN_CHUNK = 256;         // argmin recovery granularity (points): the per-chunk bookkeeping is amortised over 256 keys
 static constexpr int NN_TILE = 2048;         // points per shared-memory tile (32 KB)
 static constexpr int NN_THREADS = 128;
-// RAMP_NN_TOP3 = 1: the scan tracks the three smallest chunk minima with their chunks (+ the value of the fourth); 0: two (+ the
-// value of the third).  More tracked chunks = fewer whole-cloud fallbacks on dense clouds, more registers per waypoint.
-#ifndef RAMP_NN_TOP3
-#define RAMP_NN_TOP3 1
+// NN_TOP3(dim): the scan tracks the three smallest chunk minima with their chunks (+ the value of the fourth) instead of two
+// (+ the value of the third).  More tracked chunks = fewer whole-cloud fallbacks on dense clouds, more registers per waypoint:
+// measured on the sweep's 1 M-point cloud (profiles/r2_nn_sweep.txt) three win in 2-D (73.9 vs 83.0 ms), two in 3-D (81.9 vs
+// 103.7 ms: ties are rare there and the registers matter).  RAMP_NN_TOP3 = 0 / 1 forces one for both.
+#ifdef RAMP_NN_TOP3
+#define NN_TOP3(dim) (RAMP_NN_TOP3 != 0)
+#else
+#define NN_TOP3(dim) ((dim) == 2)
 #endif
 
 // cloud [P, d] -> packed float4 (x, y, z|0, |p|^2), padded to a multiple of NN_TILE with +inf norms
@@ -66,7 +70,7 @@ __device__ __forceinline__ float nn_key(const float4 p, float mx, float my, floa
 
 // R = waypoints per thread (register blocking), TILE = cloud points per shared-memory buffer (two buffers per CTA)
 template <int DIM, int R, int TILE>
-__global__ void __launch_bounds__(NN_THREADS, RAMP_NN_TOP3 ? (R >= 8 ? 3 : (R >= 6 ? 4 : 6)) : 1) nn_query_kernel(const float4* __restrict__ cloud4, const int* __restrict__ perm,
+__global__ void __launch_bounds__(NN_THREADS, NN_TOP3(DIM) ? (R >= 8 ? 3 : (R >= 6 ? 4 : 6)) : 1) nn_query_kernel(const float4* __restrict__ cloud4, const int* __restrict__ perm,
                                                               int P, int Ppad,
                                                               const float* __restrict__ q, int Q, int qstride, float thr,
                                                               float* __restrict__ out_d, int* __restrict__ out_idx) {
@@ -123,12 +127,11 @@ __global__ void __launch_bounds__(NN_THREADS, RAMP_NN_TOP3 ? (R >= 8 ? 3 : (R >=
       const int gc = t * (TILE / NN_CHUNK) + c;
 #pragma unroll
       for (int r = 0; r < R; ++r) {   // the three smallest chunk minima with their chunks, and the value of the fourth
-#if !RAMP_NN_TOP3
-        if (cm[r] < best[r]) { third[r] = second[r]; second[r] = best[r]; schunk[r] = bchunk[r]; best[r] = cm[r]; bchunk[r] = gc; }
-        else if (cm[r] < second[r]) { third[r] = second[r]; second[r] = cm[r]; schunk[r] = gc; }
-        else third[r] = fminf(third[r], cm[r]);
-#else
-        if (cm[r] < fourth[r]) {      // rare after the first few chunks: most chunks are nowhere near this waypoint
+        if constexpr (!NN_TOP3(DIM)) {
+          if (cm[r] < best[r]) { third[r] = second[r]; second[r] = best[r]; schunk[r] = bchunk[r]; best[r] = cm[r]; bchunk[r] = gc; }
+          else if (cm[r] < second[r]) { third[r] = second[r]; second[r] = cm[r]; schunk[r] = gc; }
+          else third[r] = fminf(third[r], cm[r]);
+        } else if (cm[r] < fourth[r]) {      // rare after the first few chunks: most chunks are nowhere near this waypoint
           if (cm[r] < best[r]) {
             fourth[r] = third[r]; third[r] = second[r]; tchunk[r] = schunk[r]; second[r] = best[r]; schunk[r] = bchunk[r];
             best[r] = cm[r]; bchunk[r] = gc;
@@ -140,7 +143,6 @@ __global__ void __launch_bounds__(NN_THREADS, RAMP_NN_TOP3 ? (R >= 8 ? 3 : (R >=
             fourth[r] = cm[r];
           }
         }
-#endif
       }
     }
     __syncthreads();
@@ -166,13 +168,8 @@ __global__ void __launch_bounds__(NN_THREADS, RAMP_NN_TOP3 ? (R >= 8 ? 3 : (R >=
     const float qn = sqrtf(q2), pn = qn + sqrtf(fmaxf(best[r] + q2, 0.f));
     const float tol = 1.5e-7f * (4.f * pn * pn + 2.f * qn * pn + fabsf(best[r])) + 1e-30f;    // 2.5 x 2^-24 x (...)
     float bd2 = FLT_MAX; int gi = P;
-#if RAMP_NN_TOP3
-    const bool crowded = live && fourth[r] <= best[r] + tol;
-    const int ncand = second[r] <= best[r] + tol ? (third[r] <= best[r] + tol ? 3 : 2) : 1;
-#else
-    const bool crowded = live && third[r] <= best[r] + tol;
-    const int ncand = second[r] <= best[r] + tol ? 2 : 1;
-#endif
+    const bool crowded = live && (NN_TOP3(DIM) ? fourth[r] : third[r]) <= best[r] + tol;
+    const int ncand = second[r] <= best[r] + tol ? ((NN_TOP3(DIM) && third[r] <= best[r] + tol) ? 3 : 2) : 1;
     const unsigned need = __ballot_sync(0xffffffffu, crowded);
     if (live && !crowded) {
       for (int cnd = 0; cnd < ncand; ++cnd) {

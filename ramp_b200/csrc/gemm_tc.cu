@@ -812,7 +812,7 @@ static int g_num_sms = 148;
 static int g_l2promo = 256;
 // RAMP_GEMM_PAIR: 0 = every tile on one CTA; 1 = CTA pairs (cta_group::2) for launches with BN >= 128 and enough M tiles
 #ifndef RAMP_GEMM_PAIR_DEFAULT
-#define RAMP_GEMM_PAIR_DEFAULT 0
+#define RAMP_GEMM_PAIR_DEFAULT 1      // measured on B200 (profiles/r2_cta_pair_ab.txt): +4.1 % on the headline, LN-backward launches -15 %
 #endif
 static int g_pair = RAMP_GEMM_PAIR_DEFAULT;
 

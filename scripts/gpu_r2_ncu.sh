@@ -16,6 +16,7 @@ for d in 2 3; do
   ncu -i ${O}_nn$d.ncu-rep --page source --csv > ${O}_nn$d.source.csv 2>/dev/null
   [ $d = 3 ] && rm -f ${O}_nn$d.ncu-rep
 done
+export RAMP_UNET_SPLIT=1       # whole 7168-row calls (one chain of 260 GEMM launches) for the per-launch evidence
 python scripts/profile_unet.py > ${O}_unet.plain 2>&1 && \
 $NCU --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --kernel-name regex:gemm_tc_kernel \
     --launch-skip 260 --launch-count 260 --csv --log-file ${O}_gemm_traffic.csv python scripts/profile_unet.py > ${O}_traffic.log 2>&1
@@ -26,11 +27,12 @@ full() {  # name kernel-regex skip
   ncu -i ${O}_$1.ncu-rep --page raw --csv > ${O}_$1.raw.csv 2>/dev/null
   rm -f ${O}_$1.ncu-rep      # gpurun_out/ is limited to 64 MiB: keep the raw page
 }
-full e1 "gemm_tc_kernel<1" 16
-full e2 "gemm_tc_kernel<2" 30
-full e4ff "gemm_tc_kernel<4" 60
-full attn_bwd64 "attn_bwd_tc<64" 3
-full attn_fwd64 "attn_fwd_tc<64" 3
+full e1 "gemm_tc_kernel<.int.1," 16
+full e2 "gemm_tc_kernel<.int.2," 30
+full e4ff "gemm_tc_kernel<.int.4," 60
+full attn_bwd64 "attn_bwd_tc<.int.64," 3
+full attn_fwd64 "attn_fwd_tc<.int.64," 3
+unset RAMP_UNET_SPLIT
 python bench.py --steps 1 --warmup 3 --cpu-sample 0 --no-sections --eager > ${O}_bench.plain 2> ${O}_bench.plain.err && \
 $NCU --metrics gpu__time_duration.sum --launch-skip 7700 --launch-count 7600 --csv --log-file ${O}_launches.csv \
     python bench.py --steps 1 --warmup 3 --cpu-sample 0 --no-sections --eager > ${O}_ncu_bench.log 2>&1
