@@ -191,6 +191,18 @@ int ramp_path_sums(const float* x, int B, int H, int D, int c0, int c1, float* o
 size_t ramp_waypoint_variance_workspace_bytes(int n, int H);
 int ramp_waypoint_variance(const float* x, int n, int H, int D, void* workspace, float* out1, void* stream);
 int ramp_vector_stats(const float* v, int n, float* out3, void* stream);
+/* ramp_waypoint_variance_static: NO COUNTERPART IN THE REFERENCE — added for callers
+ * that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same result
+ * as ramp_waypoint_variance, but the scratch is a file-scope `static __device__` array of
+ * ramp_waypoint_variance_static_max_bytes() = 1 MiB that every GPU loading the library holds until exit; the call allocates
+ * nothing (no cudaMalloc / cudaFree / allocating library routine).  Limit: H * T (T + 1) / 2 * 16 bytes <= 1 MiB with
+ * T = ceil(n / 128) tiles, e.g. n <= 4096 trajectories at H = 64 (n <= 5632 is the last size that fits); larger sizes are
+ * rejected with status -2 and a message in ramp_last_error().  All calls on a GPU share the one array, which keeps the last
+ * call's contents (every entry read is rewritten by the same call, so nothing needs clearing): calls that overlap on the GPU
+ * (different streams, or graph branches running concurrently) RACE — serialise them.  The first call on each device fetches
+ * the array's device address (cudaGetSymbolAddress, with that device current); make it once outside a graph capture. */
+size_t ramp_waypoint_variance_static_max_bytes(void);
+int ramp_waypoint_variance_static(const float* x, int n, int H, int D, float* out1, void* stream);
 
 /* ---- caller-side state of the dynamic planner on the device --------------------------------
  * ramp_pursuer_tick: one launch = MultiSphereFieldDynamics.update_centers (deps/torch_robotics/.../primitives.py:

@@ -153,11 +153,59 @@ __global__ void __launch_bounds__(256) vector_stats_kernel(const float* __restri
   }
 }
 
+// ---- no-allocation variant of the waypoint variance (no reference counterpart) ----
+// The partial sums of waypoint_pairs_kernel live in THIS file-scope device array instead of caller scratch: every GPU that
+// loads the library holds WV_STATIC_BYTES (1 MiB) until exit.  In host code `g_wv_scratch` is only a host-side stand-in for
+// the symbol, not a device address: the address is fetched once per device with cudaGetSymbolAddress (wv_static_ptr).
+static constexpr size_t WV_STATIC_BYTES = 1u << 20;
+static __device__ __align__(256) double g_wv_scratch[WV_STATIC_BYTES / sizeof(double)];
+static constexpr int WV_MAX_DEVICES = 64;
+static double* g_wv_ptr[WV_MAX_DEVICES] = {nullptr};
+
+// set-up, once per device, with that device current: device address of the static scratch (no allocation)
+static int wv_static_ptr(double** out) {
+  int dev = 0;
+  RAMP_CUDA_OK(cudaGetDevice(&dev));
+  RAMP_CHECK(dev >= 0 && dev < WV_MAX_DEVICES, "ramp_waypoint_variance_static: device index out of range");
+  if (!g_wv_ptr[dev]) {
+    double* p = nullptr;
+    RAMP_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_wv_scratch));
+    RAMP_CHECK(p != nullptr, "ramp_waypoint_variance_static: cudaGetSymbolAddress returned null");
+    g_wv_ptr[dev] = p;
+  }
+  *out = g_wv_ptr[dev];
+  return 0;
+}
+
 }  // namespace ramp
 
 using namespace ramp;
 
 extern "C" {
+
+size_t ramp_waypoint_variance_static_max_bytes(void) { return WV_STATIC_BYTES; }
+
+int ramp_waypoint_variance_static(const float* x, int n, int H, int D, float* out1, void* stream) {
+  RAMP_CHECK(x && out1, "ramp_waypoint_variance_static: null argument");
+  RAMP_CHECK(n >= 2 && H >= 1 && D >= 2, "ramp_waypoint_variance_static: need at least 2 trajectories");
+  const int nt = (n + WV_TILE - 1) / WV_TILE, npairs = nt * (nt + 1) / 2;
+  const size_t need = (size_t)H * npairs * 2 * sizeof(double);
+  if (need > WV_STATIC_BYTES) {
+    char buf[224];
+    snprintf(buf, sizeof(buf), "ramp_waypoint_variance_static: n = %d trajectories x H = %d needs %zu bytes of scratch, the "
+             "static array holds %zu (use ramp_waypoint_variance with caller scratch)", n, H, need, (size_t)WV_STATIC_BYTES);
+    set_error(buf);
+    return -2;
+  }
+  double* ws = nullptr;
+  if (wv_static_ptr(&ws)) return -1;
+  // every partial the final kernel reads is written by the pairs kernel of THIS call: nothing has to start at zero
+  waypoint_pairs_kernel<<<H * npairs, 256, 0, (cudaStream_t)stream>>>(x, n, H, D, nt, ws);
+  RAMP_LAUNCH_OK();
+  waypoint_var_final_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(ws, n, H, npairs, out1);
+  RAMP_LAUNCH_OK();
+  return 0;
+}
 
 int ramp_collision_intensity(const float* x, int B, int H, int D, const float* box_centers, const float* box_sizes,
                              int size_stride, int n_boxes, float* out, void* stream) {
