@@ -11,6 +11,10 @@
 // Inputs are the bf16 hi/lo planes the QKV / out-projection GEMMs write; outputs are hi/lo planes for the next GEMM.
 #include "unet_ops.cuh"
 
+#ifndef RAMP_ATTN_ALIAS
+#define RAMP_ATTN_ALIAS 1      // 0: round 1's layout (P / dS in their own 4 PT bytes) for same-box A/B runs
+#endif
+
 namespace ramp {
 
 __device__ __forceinline__ uint32_t s_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -185,7 +189,10 @@ template <int L> struct TcShape {
   static constexpr int TILE = L * 128;             // bytes of one [L][64] bf16 tile
   static constexpr int PT = L * L * 2;             // bytes of one [L][L] bf16 tile
   static constexpr int FWD_BYTES = 6 * TILE;       // Q, K, V hi/lo
-  static constexpr int BWD_BYTES = 8 * TILE + 4 * PT;   // Q, K, V, dO hi/lo + P, dS hi/lo
+  // Q, K, V, dO hi/lo.  P and dS (hi/lo, 4 PT <= 4 TILE) are parked over K and V once every warp of the problem is done
+  // with them: 64 KB instead of 96 KB per L = 64 problem, i.e. three CTAs per SM instead of two (ncu r2: the backward at
+  // L = 64 ran at sm__warps_active 17.7 %, 2.3x its HBM floor, with its load / compute / store phases serialised per CTA)
+  static constexpr int BWD_BYTES = RAMP_ATTN_ALIAS ? 8 * TILE : 8 * TILE + 4 * PT;
 };
 
 template <int L, int LV>     // L = tile rows (multiple of 16), LV = tokens (LV < L: zero-padded queries / masked keys)
@@ -272,7 +279,7 @@ __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_
   const uint32_t base = s_addr(sm_tc) + pl * S::BWD_BYTES;
   const uint32_t Qh = base, Ql = base + S::TILE, Kh = base + 2 * S::TILE, Kl = base + 3 * S::TILE, Vh = base + 4 * S::TILE,
                  Vl = base + 5 * S::TILE, Dh = base + 6 * S::TILE, Dl = base + 7 * S::TILE;
-  const uint32_t Ph = base + 8 * S::TILE, Pl = Ph + S::PT, Gh = Pl + S::PT, Gl = Gh + S::PT;     // G = dS
+  const uint32_t Ph = RAMP_ATTN_ALIAS ? Kh : base + 8 * S::TILE, Pl = Ph + S::PT, Gh = Pl + S::PT, Gl = Gh + S::PT;     // G = dS; aliases K / V (see TcShape)
   if (live) {
     const size_t off = (size_t)n * LV * 768 + h * 64, offd = (size_t)n * LV * 256 + h * 64;
     const int t = wp * 32 + lane, nth = S::W * 32;
@@ -286,8 +293,8 @@ __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_
   const int m0 = 16 * wp;
   const size_t row0 = (size_t)n * LV + m0;
   const bool half2 = m0 + 8 < LV;
+  float p[L / 8][4], dp[L / 8][4];
   if (live) {
-    float p[L / 8][4], dp[L / 8][4];
     qk_product<L>(Qh, Ql, Kh, Kl, m0, lane, p);
     softmax_frag<L, LV>(p);
     qk_product<L>(Dh, Dl, Vh, Vl, m0, lane, dp);           // dP = dO V^T
@@ -303,11 +310,14 @@ __global__ void __launch_bounds__(128) attn_bwd_tc(const bf16* __restrict__ qkv_
         dp[nt][2 * hh + 1] = p[nt][2 * hh + 1] * (dp[nt][2 * hh + 1] - acc) * 0.125f;
       }
     }
-    park_frag<L>(p, Ph, Pl, m0, lane);
-    park_frag<L>(dp, Gh, Gl, m0, lane);
     float o[8][4];
     pv_product<L>(dp, Kh, Kl, lane, o);                     // dQ = dS K
     store_frag(o, dq_hi, dq_lo, row0, 768, h * 64, lane, half2);
+  }
+  __syncthreads();                                          // K and V are dead from here on
+  if (live) {
+    park_frag<L>(p, Ph, Pl, m0, lane);
+    park_frag<L>(dp, Gh, Gl, m0, lane);
   }
   __syncthreads();
   if (live) {

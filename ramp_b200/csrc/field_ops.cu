@@ -5,10 +5,10 @@
 //   cost terms    : cost.py:3-7,19-54            selection   : cost.py:56-88
 // The reference's "potential field" is a k=1 nearest-neighbour push, so the hot loop is a min/argmin
 // over the cloud per waypoint: FP32-pipe bound.  Cloud tiles are staged in shared memory by TMA bulk
-// copies (double buffered, mbarrier completion); each thread keeps R waypoints in registers and
-// evaluates |p|^2 - 2 q.p with d FFMA per pair plus one 3-input min per two pairs; the argmin is
-// recovered by re-scanning, in the direct form (q - p)^2, every 64-point chunk whose minimum key is within the key's
-// rounding bound of the best one (normally one or two chunks; the whole cloud by the warp when three or more tie), so
+// copies (double buffered, mbarrier completion) and re-laid there as point pairs; each thread keeps R waypoints in
+// registers and evaluates |p|^2 - 2 q.p for both points of a pair with d packed FFMA2 plus one 3-input min; the argmin is
+// recovered by re-scanning, in the direct form (q - p)^2, every 256-point chunk whose minimum key is within the key's
+// rounding bound of the best one (normally one to three chunks; the whole cloud by the warp when four or more tie), so
 // the index is the fp32-exact nearest point with the lowest index on ties, and the distance is re-derived exactly.
 #include "../../include/ramp_b200.h"
 #include "common.cuh"
@@ -19,17 +19,15 @@
 namespace ramp {
 
 static constexpr int NN_CHUNK = 256;         // argmin recovery granularity (points): the per-chunk bookkeeping is amortised over 256 keys
-static constexpr int NN_TILE = 2048;         // points per shared-memory tile (32 KB)
+static constexpr int NN_TILE = 2048;         // cloud padding granularity (points); the kernel's shared-memory tiles divide it
 static constexpr int NN_THREADS = 128;
-// NN_TOP3(dim): the scan tracks the three smallest chunk minima with their chunks (+ the value of the fourth) instead of two
-// (+ the value of the third).  More tracked chunks = fewer whole-cloud fallbacks on dense clouds, more registers per waypoint:
-// measured on the sweep's 1 M-point cloud (profiles/r2_nn_sweep.txt) three win in 2-D (73.9 vs 83.0 ms), two in 3-D (81.9 vs
-// 103.7 ms: ties are rare there and the registers matter).  RAMP_NN_TOP3 = 0 / 1 forces one for both.
-#ifdef RAMP_NN_TOP3
-#define NN_TOP3(dim) (RAMP_NN_TOP3 != 0)
-#else
-#define NN_TOP3(dim) ((dim) == 2)
-#endif
+// Per waypoint the scan tracks the three smallest chunk minima with their chunks, plus the VALUE of the fourth.  Only that
+// value (the threshold a chunk minimum must beat to matter at all) lives in a register; the other six words per waypoint are
+// touched once in a few hundred chunks and sit in shared memory ([word][waypoint slot][thread], conflict-free).  Round 2's
+// first version kept all seven in registers: 168 registers at 10 waypoints per thread = 3 CTAs (12 warps) per SM, and ncu
+// showed the FP32 pipe waiting on issue (smsp__issue_active 65 %, stall "wait" 30 %).  With the bookkeeping out of the
+// register file the hot loop needs ~4 registers per waypoint and 5-6 CTAs fit.
+static constexpr int NN_BK_WORDS = 6;        // best, second, third (float) + their chunks (int)
 
 // cloud [P, d] -> packed float4 (x, y, z|0, |p|^2), padded to a multiple of NN_TILE with +inf norms
 __global__ void nn_pack_kernel(const float* __restrict__ cloud, int P, int dim, int Ppad, float4* __restrict__ out) {
@@ -61,21 +59,54 @@ __device__ __forceinline__ void nn_mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
-template <int DIM>
-__device__ __forceinline__ float nn_key(const float4 p, float mx, float my, float mz) {
-  float k = fmaf(my, p.y, p.w);
-  if (DIM == 3) k = fmaf(mz, p.z, k);
-  return fmaf(mx, p.x, k);
+// Packed FP32 FMA (sm_100 FFMA2): two IEEE fused multiply-adds per issue slot, each half bit-identical to fmaf.  The scan is
+// issue-bound with scalar FFMAs (d FFMA + 1/2 FMNMX3 per pair and one instruction per clock per scheduler: ncu r2 showed
+// the FP32 pipe 49 % busy at 65 % issue utilisation), so the cloud tile is re-laid in shared memory as point PAIRS
+// ({x0, x1, y0, y1}, {w0, w1} | {z0, z1, w0, w1}) and one FFMA2 produces the partial keys of both points for one waypoint.
+__device__ __forceinline__ unsigned long long nn_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned long long nn_pack2(float lo, float hi) {
+  unsigned long long d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+  return d;
+}
+__device__ __forceinline__ void nn_unpack2(unsigned long long v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+
+// shared memory per CTA: two staged cloud tiles (float4 per point, as packed in HBM) + the current tile as point pairs
+// (16 B + 8 B per pair in 2-D, 16 B + 16 B in 3-D) + the bookkeeping words
+__host__ __device__ constexpr int nn_pair_bytes(int DIM, int TILE) { return (TILE / 2) * (DIM == 2 ? 24 : 32); }
+__host__ __device__ constexpr int nn_smem_bytes(int DIM, int R, int TILE) {
+  return 2 * TILE * 16 + nn_pair_bytes(DIM, TILE) + NN_BK_WORDS * R * NN_THREADS * 4;
+}
+// CTAs per SM the launch bounds ask for: what shared memory allows (228 KB per SM, 1 KB reserved per CTA), at most what
+// the hot loop's registers allow (~(DIM + 2) per waypoint + ~36 for the points in flight and addressing)
+__host__ __device__ constexpr int nn_min_ctas(int DIM, int R, int TILE) {
+  int by_smem = (228 * 1024) / (nn_smem_bytes(DIM, R, TILE) + 1024);
+  int regs = (DIM + 2) * R + 48;          // -2 q per component (FFMA2 takes it as a broadcast scalar), chunk minimum, threshold
+  regs = (regs + 7) / 8 * 8;
+  int by_regs = 65536 / (NN_THREADS * regs);
+  int n = by_smem < by_regs ? by_smem : by_regs;
+  return n < 1 ? 1 : (n > 8 ? 8 : n);
 }
 
 // R = waypoints per thread (register blocking), TILE = cloud points per shared-memory buffer (two buffers per CTA)
 template <int DIM, int R, int TILE>
-__global__ void __launch_bounds__(NN_THREADS, NN_TOP3(DIM) ? (R >= 8 ? 3 : (R >= 6 ? 4 : 6)) : 1) nn_query_kernel(const float4* __restrict__ cloud4, const int* __restrict__ perm,
-                                                              int P, int Ppad,
-                                                              const float* __restrict__ q, int Q, int qstride, float thr,
-                                                              float* __restrict__ out_d, int* __restrict__ out_idx) {
+__global__ void __launch_bounds__(NN_THREADS, nn_min_ctas(DIM, R, TILE))
+nn_query_kernel(const float4* __restrict__ cloud4, const int* __restrict__ perm, int P, int Ppad,
+                const float* __restrict__ q, int Q, int qstride, float thr, float* __restrict__ out_d,
+                int* __restrict__ out_idx) {
   extern __shared__ __align__(128) unsigned char nn_smem[];
-  float4* tile = reinterpret_cast<float4*>(nn_smem);                       // 2 x TILE
+  float4* tile = reinterpret_cast<float4*>(nn_smem);                       // 2 x TILE, staged by TMA
+  ulonglong2* pairA = reinterpret_cast<ulonglong2*>(nn_smem + 2 * TILE * 16);            // per point pair: {x0 x1 | y0 y1}
+  unsigned long long* pairW = reinterpret_cast<unsigned long long*>(pairA + TILE / 2);   // 2-D: {w0 w1}
+  ulonglong2* pairB = reinterpret_cast<ulonglong2*>(pairA + TILE / 2);                   // 3-D: {z0 z1 | w0 w1}
+  float* bkf = reinterpret_cast<float*>(nn_smem + 2 * TILE * 16 + nn_pair_bytes(DIM, TILE));   // [3][R][threads]: best, second, third
+  int* bki = reinterpret_cast<int*>(bkf + 3 * R * NN_THREADS);              // [3][R][threads]: their chunks
   __shared__ __align__(8) unsigned long long bars[2];
   const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&bars[0]);
   const uint32_t tile0 = (uint32_t)__cvta_generic_to_shared(tile);
@@ -96,51 +127,79 @@ __global__ void __launch_bounds__(NN_THREADS, NN_TOP3(DIM) ? (R >= 8 ? 3 : (R >=
   };
   if (tid == 0) issue(0);
 
-  float mx[R], my[R], mz[R], best[R], second[R], third[R], fourth[R];
-  int bchunk[R], schunk[R], tchunk[R];
+  // word w of waypoint slot r of this thread (only this thread ever touches it: no synchronisation needed)
+#define NN_BKF(w, r) bkf[((w) * R + (r)) * NN_THREADS + tid]
+#define NN_BKI(w, r) bki[((w) * R + (r)) * NN_THREADS + tid]
+  unsigned long long mx[R], my[R], mz[R];      // (-2 q, -2 q): both halves of an FFMA2 operand
+  float fourth[R];
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const int qi = (blockIdx.x * R + r) * NN_THREADS + tid;
-    mx[r] = my[r] = mz[r] = 0.f;
+    float ax = 0.f, ay = 0.f, az = 0.f;
     if (qi < Q) {
-      mx[r] = -2.f * q[(size_t)qi * qstride];
-      my[r] = -2.f * q[(size_t)qi * qstride + 1];
-      if (DIM == 3) mz[r] = -2.f * q[(size_t)qi * qstride + 2];
+      ax = -2.f * q[(size_t)qi * qstride];
+      ay = -2.f * q[(size_t)qi * qstride + 1];
+      if (DIM == 3) az = -2.f * q[(size_t)qi * qstride + 2];
     }
-    best[r] = second[r] = third[r] = fourth[r] = FLT_MAX; bchunk[r] = schunk[r] = tchunk[r] = 0;
+    mx[r] = nn_pack2(ax, ax); my[r] = nn_pack2(ay, ay); mz[r] = nn_pack2(az, az);
+    fourth[r] = FLT_MAX;
+    NN_BKF(0, r) = FLT_MAX; NN_BKF(1, r) = FLT_MAX; NN_BKF(2, r) = FLT_MAX;
+    NN_BKI(0, r) = 0; NN_BKI(1, r) = 0; NN_BKI(2, r) = 0;
   }
   for (int t = 0; t < ntiles; ++t) {
     if (tid == 0 && t + 1 < ntiles) issue(t + 1);
     nn_mbar_wait(bar0 + 8 * (t & 1), (t >> 1) & 1);
     const float4* tp = tile + (t & 1) * TILE;
+    // staged tile -> point pairs (the previous tile's pairs were last read before the barrier that ended its scan)
+    for (int i = tid; i < TILE / 2; i += NN_THREADS) {
+      const float4 pa = tp[2 * i], pb = tp[2 * i + 1];
+      pairA[i] = make_ulonglong2(nn_pack2(pa.x, pb.x), nn_pack2(pa.y, pb.y));
+      if (DIM == 2) pairW[i] = nn_pack2(pa.w, pb.w);
+      else pairB[i] = make_ulonglong2(nn_pack2(pa.z, pb.z), nn_pack2(pa.w, pb.w));
+    }
+    __syncthreads();
+#pragma unroll 1
     for (int c = 0; c < TILE / NN_CHUNK; ++c) {
       float cm[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) cm[r] = FLT_MAX;
 #pragma unroll 8
-      for (int j = 0; j < NN_CHUNK; j += 2) {
-        const float4 pa = tp[c * NN_CHUNK + j], pb = tp[c * NN_CHUNK + j + 1];
+      for (int j = 0; j < NN_CHUNK / 2; ++j) {
+        // keys k = |p|^2 - 2 q.p of both points of the pair, accumulated in the order y, (z,) x - the same three roundings
+        // per key as the scalar form the exactness bound below is derived for
+        const ulonglong2 a = pairA[c * (NN_CHUNK / 2) + j];
+        if (DIM == 2) {
+          const unsigned long long w = pairW[c * (NN_CHUNK / 2) + j];
 #pragma unroll
-        for (int r = 0; r < R; ++r)
-          cm[r] = min3f(cm[r], nn_key<DIM>(pa, mx[r], my[r], mz[r]), nn_key<DIM>(pb, mx[r], my[r], mz[r]));
+          for (int r = 0; r < R; ++r) {
+            float k0, k1;
+            nn_unpack2(nn_fma2(mx[r], a.x, nn_fma2(my[r], a.y, w)), k0, k1);
+            cm[r] = min3f(cm[r], k0, k1);
+          }
+        } else {
+          const ulonglong2 b = pairB[c * (NN_CHUNK / 2) + j];
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            float k0, k1;
+            nn_unpack2(nn_fma2(mx[r], a.x, nn_fma2(mz[r], b.x, nn_fma2(my[r], a.y, b.y))), k0, k1);
+            cm[r] = min3f(cm[r], k0, k1);
+          }
+        }
       }
       const int gc = t * (TILE / NN_CHUNK) + c;
 #pragma unroll
-      for (int r = 0; r < R; ++r) {   // the three smallest chunk minima with their chunks, and the value of the fourth
-        if constexpr (!NN_TOP3(DIM)) {
-          if (cm[r] < best[r]) { third[r] = second[r]; second[r] = best[r]; schunk[r] = bchunk[r]; best[r] = cm[r]; bchunk[r] = gc; }
-          else if (cm[r] < second[r]) { third[r] = second[r]; second[r] = cm[r]; schunk[r] = gc; }
-          else third[r] = fminf(third[r], cm[r]);
-        } else if (cm[r] < fourth[r]) {      // rare after the first few chunks: most chunks are nowhere near this waypoint
-          if (cm[r] < best[r]) {
-            fourth[r] = third[r]; third[r] = second[r]; tchunk[r] = schunk[r]; second[r] = best[r]; schunk[r] = bchunk[r];
-            best[r] = cm[r]; bchunk[r] = gc;
-          } else if (cm[r] < second[r]) {
-            fourth[r] = third[r]; third[r] = second[r]; tchunk[r] = schunk[r]; second[r] = cm[r]; schunk[r] = gc;
-          } else if (cm[r] < third[r]) {
-            fourth[r] = third[r]; third[r] = cm[r]; tchunk[r] = gc;
+      for (int r = 0; r < R; ++r) {
+        if (cm[r] < fourth[r]) {      // rare after the first few chunks: most chunks are nowhere near this waypoint
+          const float v = cm[r], b = NN_BKF(0, r), s2 = NN_BKF(1, r), t3 = NN_BKF(2, r);
+          if (v < t3) {
+            fourth[r] = t3;
+            if (v < s2) {
+              NN_BKF(2, r) = s2; NN_BKI(2, r) = NN_BKI(1, r);
+              if (v < b) { NN_BKF(1, r) = b; NN_BKI(1, r) = NN_BKI(0, r); NN_BKF(0, r) = v; NN_BKI(0, r) = gc; }
+              else { NN_BKF(1, r) = v; NN_BKI(1, r) = gc; }
+            } else { NN_BKF(2, r) = v; NN_BKI(2, r) = gc; }
           } else {
-            fourth[r] = cm[r];
+            fourth[r] = v;
           }
         }
       }
@@ -165,15 +224,16 @@ __global__ void __launch_bounds__(NN_THREADS, NN_TOP3(DIM) ? (R >= 8 ? 3 : (R >=
     const float qx = q[qo], qy = q[qo + 1];
     const float qz = DIM == 3 ? q[qo + 2] : 0.f;
     const float q2 = qx * qx + qy * qy + qz * qz;
-    const float qn = sqrtf(q2), pn = qn + sqrtf(fmaxf(best[r] + q2, 0.f));
-    const float tol = 1.5e-7f * (4.f * pn * pn + 2.f * qn * pn + fabsf(best[r])) + 1e-30f;    // 2.5 x 2^-24 x (...)
+    const float best = NN_BKF(0, r), second = NN_BKF(1, r), third = NN_BKF(2, r);
+    const float qn = sqrtf(q2), pn = qn + sqrtf(fmaxf(best + q2, 0.f));
+    const float tol = 1.5e-7f * (4.f * pn * pn + 2.f * qn * pn + fabsf(best)) + 1e-30f;    // 2.5 x 2^-24 x (...)
     float bd2 = FLT_MAX; int gi = P;
-    const bool crowded = live && (NN_TOP3(DIM) ? fourth[r] : third[r]) <= best[r] + tol;
-    const int ncand = second[r] <= best[r] + tol ? ((NN_TOP3(DIM) && third[r] <= best[r] + tol) ? 3 : 2) : 1;
+    const bool crowded = live && fourth[r] <= best + tol;
+    const int ncand = second <= best + tol ? (third <= best + tol ? 3 : 2) : 1;
     const unsigned need = __ballot_sync(0xffffffffu, crowded);
     if (live && !crowded) {
       for (int cnd = 0; cnd < ncand; ++cnd) {
-        const int ch = cnd == 0 ? bchunk[r] : (cnd == 1 ? schunk[r] : tchunk[r]);
+        const int ch = NN_BKI(cnd, r);
         const float4* cp = cloud4 + (size_t)ch * NN_CHUNK;
         for (int j = 0; j < NN_CHUNK; ++j) {
           const float4 p = cp[j];
@@ -216,6 +276,8 @@ __global__ void __launch_bounds__(NN_THREADS, NN_TOP3(DIM) ? (R >= 8 ? 3 : (R >=
       out_idx[qi] = hit ? gi : P;
     }
   }
+#undef NN_BKF
+#undef NN_BKI
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -446,7 +508,7 @@ template <int DIM, int R, int TILE>
 static int nn_launch(const float4* c4, const int* perm, int P, int Ppad, const float* q, int Q, int qstride, float thr,
                      float* od, int* oi, cudaStream_t s) {
   static bool attr = false;
-  const int smem = 2 * TILE * 16;
+  const int smem = nn_smem_bytes(DIM, R, TILE);
   if (!attr) { RAMP_CUDA_OK(cudaFuncSetAttribute(nn_query_kernel<DIM, R, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
   const int per = NN_THREADS * R;
   nn_query_kernel<DIM, R, TILE><<<(Q + per - 1) / per, NN_THREADS, smem, s>>>(c4, perm, P, Ppad, q, Q, qstride, thr, od, oi);
@@ -458,38 +520,38 @@ template <int DIM>
 static int nn_dispatch(int R, int TILE, const float4* c4, const int* perm, int P, int Ppad, const float* q, int Q, int qstride,
                        float thr, float* od, int* oi, cudaStream_t s) {
 #define RAMP_NN_CASE(r) \
-  case r: return TILE == 2048 ? nn_launch<DIM, r, 2048>(c4, perm, P, Ppad, q, Q, qstride, thr, od, oi, s) \
-                              : nn_launch<DIM, r, 1024>(c4, perm, P, Ppad, q, Q, qstride, thr, od, oi, s);
+  case r: return nn_launch<DIM, r, 512>(c4, perm, P, Ppad, q, Q, qstride, thr, od, oi, s);
   switch (R) {
-    RAMP_NN_CASE(1) RAMP_NN_CASE(2) RAMP_NN_CASE(4) RAMP_NN_CASE(6) RAMP_NN_CASE(8) RAMP_NN_CASE(10) RAMP_NN_CASE(12)
+    RAMP_NN_CASE(1) RAMP_NN_CASE(2) RAMP_NN_CASE(4) RAMP_NN_CASE(6) RAMP_NN_CASE(8) RAMP_NN_CASE(10) RAMP_NN_CASE(12) RAMP_NN_CASE(16)
   }
 #undef RAMP_NN_CASE
   set_error("ramp_nn_query: unsupported register blocking");
   return -2;
 }
 // The grid is one CTA per 128 R waypoints, each scanning the whole cloud, so an SM works through
-// ceil(CTAs / SMs) * R blocks of 128 waypoints.  The cost of one block depends on R: more waypoints per thread amortise
-// the shared-memory loads of a cloud point over more FFMAs, until register pressure costs occupancy (3-D: three
-// coordinates per waypoint).  Relative costs per block measured on B200 (8192 x 64 waypoints, 1 M points; R = 1, 2
-// extrapolated); the launch takes the R with the smallest ceil(CTAs / SMs) * R * cost[R].
+// ceil(CTAs / SMs) * R blocks of 128 waypoints.  The cost of one block depends little on R since the chunk bookkeeping left
+// the register file (more waypoints per thread amortise the shared-memory loads of a point pair over more FFMA2s, fewer
+// leave more CTAs resident), so the choice is mostly about filling whole waves.  Relative costs per block measured on B200
+// (profiles/r2_nn_sweep_ffma2.txt: 8192 x 64 waypoints, 1 M points, 512-point tiles; R = 1, 2 extrapolated); the launch
+// takes the R with the smallest ceil(CTAs / SMs) * R * cost[R].  1024-point tiles were 0-5 % slower at every R.
 template <int DIM>
 static int nn_choose(int Q, int* R_out, int* TILE_out) {
-  static const int Rs[7] = {1, 2, 4, 6, 8, 10, 12};
-  static const double cost2[7] = {4.64, 3.17, 2.43, 2.20, 2.19, 1.97, 1.94};
-  static const double cost3[7] = {5.20, 3.55, 2.72, 3.07, 3.00, 3.46, 3.50};
+  static const int Rs[8] = {1, 2, 4, 6, 8, 10, 12, 16};
+  static const double cost2[8] = {3.60, 2.60, 2.171, 2.166, 2.121, 2.160, 2.105, 2.196};
+  static const double cost3[8] = {4.20, 3.00, 2.500, 2.466, 2.469, 2.451, 2.478, 2.496};
   static int sms = 0;
   if (!sms) {
     int dev = 0;
     cudaGetDevice(&dev);
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 148;
   }
-  *TILE_out = 1024;                                   // 32 KB of buffers per CTA: up to 7 CTAs resident per SM
+  *TILE_out = 512;                                    // the only instantiated tile: 16 KB staged + 6-8 KB as pairs per CTA
   if (const char* v = getenv("RAMP_NN_FORCE")) {      // "R,TILE" - tuning knob
     int r = 0, t = 0;
-    if (sscanf(v, "%d,%d", &r, &t) == 2) { *R_out = r; *TILE_out = t; return 0; }
+    if (sscanf(v, "%d,%d", &r, &t) >= 1) { *R_out = r; return 0; }
   }
   double best = 1e300;
-  for (int ri = 0; ri < 7; ++ri) {
+  for (int ri = 0; ri < 8; ++ri) {
     const long ctas = ((long)Q + NN_THREADS * Rs[ri] - 1) / (NN_THREADS * Rs[ri]);
     const double t = (double)((ctas + sms - 1) / sms) * Rs[ri] * (DIM == 2 ? cost2[ri] : cost3[ri]);
     if (t < best) { best = t; *R_out = Rs[ri]; }

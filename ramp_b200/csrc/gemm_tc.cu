@@ -31,6 +31,12 @@
 #include <unordered_map>
 #include <vector>
 
+// RAMP_GEMM_DIAG (diagnostic builds only, results are WRONG): bit 0 drops the epilogues' global loads, bit 1 their global
+// stores - timing the launches without one side shows which one binds an HBM-bound epilogue (scripts/gpu_r2_i.sh).
+#ifndef RAMP_GEMM_DIAG
+#define RAMP_GEMM_DIAG 0
+#endif
+
 namespace ramp {
 
 static constexpr int BM = 128;
@@ -289,7 +295,7 @@ __device__ __forceinline__ void chunk_store_f32(const EpiCtx<CW>& e, const float
 #pragma unroll
   for (int i = 0; i < E::NP; ++i) {
     const float4 t = s4[stg_idx<CW>(rsub + E::RP * i, c4)];
-    if ((e.okn >> i) & 1u) *reinterpret_cast<float4*>(base + (size_t)e.rown[i] * ld + col0 + 4 * c4) = t;
+    if (!(RAMP_GEMM_DIAG & 2) && ((e.okn >> i) & 1u)) *reinterpret_cast<float4*>(base + (size_t)e.rown[i] * ld + col0 + 4 * c4) = t;
   }
   __syncwarp();
 }
@@ -313,7 +319,7 @@ __device__ __forceinline__ void chunk_store_split(const EpiCtx<CW>& e, const flo
 #pragma unroll
   for (int i = 0; i < E::NP; ++i) {
     const uint4 t = s4[stg_idx<CW>(rsub + E::RP * i, c4)];
-    if ((e.okn >> i) & 1u) *reinterpret_cast<uint4*>(plane + (size_t)e.rown[i] * ld + col0 + 8 * (c4 % H)) = t;
+    if (!(RAMP_GEMM_DIAG & 2) && ((e.okn >> i) & 1u)) *reinterpret_cast<uint4*>(plane + (size_t)e.rown[i] * ld + col0 + 8 * (c4 % H)) = t;
   }
   __syncwarp();
 }
@@ -328,7 +334,7 @@ __device__ __forceinline__ void chunk_ld_issue(const EpiCtx<CW>& e, const float*
 #pragma unroll
   for (int i = 0; i < E::NP; ++i) {
     t[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if ((e.okn >> i) & 1u) t[i] = __ldg(reinterpret_cast<const float4*>(base + (size_t)e.rown[i] * ld + col0 + 4 * c4));
+    if (!(RAMP_GEMM_DIAG & 1) && ((e.okn >> i) & 1u)) t[i] = __ldg(reinterpret_cast<const float4*>(base + (size_t)e.rown[i] * ld + col0 + 4 * c4));
   }
 }
 template <int CW>
