@@ -36,6 +36,9 @@
 #ifndef RAMP_GEMM_DIAG
 #define RAMP_GEMM_DIAG 0
 #endif
+#ifndef RAMP_GEMM_RELAXED_ARRIVE
+#define RAMP_GEMM_RELAXED_ARRIVE 1      // 0: the .release form (MEMBAR.ALL.GPU + ERRBAR per tile), for same-box A/B runs
+#endif
 
 namespace ramp {
 
@@ -73,7 +76,12 @@ struct GemmParams {
   int epi, ngroups;                           // ngroups = epilogue groups that drain a tile: min(BN / CW, epilogue warps / 4)
   const float* ln_gamma; const float* ln_beta; float* ln_stats; const float* ln_x; const float* u;
   bf16* out2_hi; bf16* out2_lo; int ldS2;
+  int tma_store;                              // 1: dense output rows -> the epilogue stores through TMA (see EpiMaps)
 };
+// Tensor maps of the outputs (fp32 copy, hi / lo planes, second hi / lo planes) for the TMA store path.  Used when the
+// tile's 128 accumulator rows are 128 consecutive output rows (o_L == L_out, o_stride == 1, o_off == 0: every launch of
+// the transformer blocks and most of the convolutions); boxes are 32 rows x CW columns = one warp's staging tile.
+struct EpiMaps { CUtensorMap f32, hi, lo, hi2, lo2; };
 
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers
@@ -115,6 +123,16 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+// TMA store of one staging tile (box = 32 rows x CW columns) at (column c0, row c1) of an output tensor; completion is
+// tracked by the issuing thread's bulk async-group
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 // ---- CTA-pair (cta_group::2) variants: M = 256 tile over two SMs of a TPC; each CTA stages its own 128 A rows and HALF of
 // the B rows, the leader CTA (cluster rank 0) issues the MMAs for both, commits are multicast to both CTAs' barriers ----
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -152,13 +170,22 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {        // arriv
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                ::"r"(bar), "h"((uint16_t)3) : "memory");
 }
-// arrive on the barrier at the same smem offset in cluster CTA `rank`
+// arrive on the barrier at the same smem offset in cluster CTA `rank`.  RELAXED on purpose: the arrival only tells the
+// leader's MMA issuer that this warp's tcgen05.ld of the accumulator have completed (tcgen05.wait::ld + the tcgen05 fence
+// before it); nothing this kernel's other threads read depends on the warp's global stores.  The default .release form
+// compiles to MEMBAR.ALL.GPU + ERRBAR in front of the arrive, i.e. every epilogue warp of the pair's second CTA waited once
+// per tile for ALL its outstanding global stores to be acknowledged (ncu r2 run K, GEGLU forward: 8 % of the stall samples
+// on those three instructions, and the leader's MMAs wait for the slower CTA).
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) {
   asm volatile(
       "{\n"
       ".reg .b32 ra;\n"
       "mapa.shared::cluster.u32 ra, %0, %1;\n"
+#if RAMP_GEMM_RELAXED_ARRIVE
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n"
+#else
       "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+#endif
       "}\n" ::"r"(bar), "r"(rank) : "memory");
 }
 
@@ -275,6 +302,8 @@ struct EpiCtx {
   static constexpr int G = CW / 4, RP = 32 / G, NP = G;   // groups per row, rows per pass, passes
   float* stg;              // this warp's staging tile
   float* stg_q;            // staging tile of group 0's warp for this lane quarter (+ 4 * 32 * CW floats per group)
+  const EpiMaps* maps;     // TMA store path: output tensor maps, else nullptr
+  int row0;                // first output row of this warp's 32 accumulator rows (TMA store path)
   int lane, bar_id;
   bool my_ok; size_t my_row; int my_sample;
   unsigned okn; uint32_t rown[NP];
@@ -284,27 +313,82 @@ template <int NG>
 __device__ __forceinline__ void row_sync(int bar_id) { asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(32 * NG) : "memory"); }
 
 // v[CW] (this thread's row, columns col0..col0+CW-1) -> base[row * ld + col0 ..] for every live row of the warp
+// The staging tile may still be read by a TMA store of this warp: wait (elected lane, its bulk group) before writing it
 template <int CW>
-__device__ __forceinline__ void chunk_store_f32(const EpiCtx<CW>& e, const float (&v)[CW], float* base, int ld, int col0) {
+__device__ __forceinline__ void stg_acquire(const EpiCtx<CW>& e) {
+  if (e.maps) {
+    if (e.lane == 0) tma_store_wait_read();
+    __syncwarp();
+  }
+}
+template <int CW>
+__device__ __forceinline__ void chunk_store_f32(const EpiCtx<CW>& e, const float (&v)[CW], float* base, int ld, int col0,
+                                                const CUtensorMap* map = nullptr) {
   using E = EpiCtx<CW>;
   float4* s4 = reinterpret_cast<float4*>(e.stg);
+  stg_acquire<CW>(e);
 #pragma unroll
   for (int k = 0; k < E::G; ++k) s4[stg_idx<CW>(e.lane, k)] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+  if (map) {
+    // row = lane, 16-byte group k at k ^ f(row): exactly the SWIZZLE_128B (CW = 32) / SWIZZLE_64B (CW = 16) image of a
+    // [32 rows x CW fp32] box, so the tile goes out as ONE bulk tensor store (rows past the tensor's end are clipped)
+    fence_async_smem();
+    __syncwarp();
+    if (e.lane == 0) {
+      if (!(RAMP_GEMM_DIAG & 2)) tma_store_2d(map, smem_u32(e.stg), col0, e.row0);
+      tma_store_commit();
+    }
+    return;
+  }
   __syncwarp();
   const int rsub = e.lane / E::G, c4 = e.lane % E::G;
+  // all read-backs first, then the stores: with one register quad per pass the LDS -> STG pairs ran strictly one after
+  // the other (ncu r2 run K: STG waiting on the short scoreboard = 11 % of the GEGLU launches' stall samples)
+  float4 t[E::NP];
 #pragma unroll
-  for (int i = 0; i < E::NP; ++i) {
-    const float4 t = s4[stg_idx<CW>(rsub + E::RP * i, c4)];
-    if (!(RAMP_GEMM_DIAG & 2) && ((e.okn >> i) & 1u)) *reinterpret_cast<float4*>(base + (size_t)e.rown[i] * ld + col0 + 4 * c4) = t;
-  }
+  for (int i = 0; i < E::NP; ++i) t[i] = s4[stg_idx<CW>(rsub + E::RP * i, c4)];
+#pragma unroll
+  for (int i = 0; i < E::NP; ++i)
+    if (!(RAMP_GEMM_DIAG & 2) && ((e.okn >> i) & 1u)) *reinterpret_cast<float4*>(base + (size_t)e.rown[i] * ld + col0 + 4 * c4) = t[i];
   __syncwarp();
 }
 // same, as bf16 hi / lo planes (ld, col0 in bf16 elements): staging row = [hi 2 CW bytes | lo 2 CW bytes]
+// 16-byte group k of row r in a [32 rows x CW 16-bit] plane tile (2 CW bytes per row): the SWIZZLE_64B (CW = 32) /
+// SWIZZLE_32B (CW = 16) image of that box
 template <int CW>
-__device__ __forceinline__ void chunk_store_split(const EpiCtx<CW>& e, const float (&v)[CW], bf16* hi, bf16* lo, int ld, int col0) {
+__device__ __forceinline__ int plane_idx(int r, int k) {
+  if constexpr (CW == 32) return r * 4 + (k ^ ((r >> 1) & 3));
+  else return r * 2 + (k ^ ((r >> 2) & 1));
+}
+template <int CW>
+__device__ __forceinline__ void chunk_store_split(const EpiCtx<CW>& e, const float (&v)[CW], bf16* hi, bf16* lo, int ld, int col0,
+                                                  const CUtensorMap* map_hi = nullptr, const CUtensorMap* map_lo = nullptr) {
   using E = EpiCtx<CW>;
   constexpr int H = E::G / 2;
   uint4* s4 = reinterpret_cast<uint4*>(e.stg);
+  stg_acquire<CW>(e);
+  if (map_hi) {
+    // the staging tile holds the hi plane tile in its first half and the lo plane tile in its second: two bulk stores
+    uint4* l4 = s4 + 32 * H;
+#pragma unroll
+    for (int k = 0; k < H; ++k) {
+      uint32_t h[4], l[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) split2_bf16(v[8 * k + 2 * j], v[8 * k + 2 * j + 1], h[j], l[j]);
+      s4[plane_idx<CW>(e.lane, k)] = make_uint4(h[0], h[1], h[2], h[3]);
+      l4[plane_idx<CW>(e.lane, k)] = make_uint4(l[0], l[1], l[2], l[3]);
+    }
+    fence_async_smem();
+    __syncwarp();
+    if (e.lane == 0) {
+      if (!(RAMP_GEMM_DIAG & 2)) {
+        tma_store_2d(map_hi, smem_u32(s4), col0, e.row0);
+        tma_store_2d(map_lo, smem_u32(l4), col0, e.row0);
+      }
+      tma_store_commit();
+    }
+    return;
+  }
 #pragma unroll
   for (int k = 0; k < H; ++k) {
     uint32_t h[4], l[4];
@@ -316,11 +400,12 @@ __device__ __forceinline__ void chunk_store_split(const EpiCtx<CW>& e, const flo
   __syncwarp();
   const int rsub = e.lane / E::G, c4 = e.lane % E::G;
   bf16* plane = (c4 < H) ? hi : lo;
+  uint4 t[E::NP];
 #pragma unroll
-  for (int i = 0; i < E::NP; ++i) {
-    const uint4 t = s4[stg_idx<CW>(rsub + E::RP * i, c4)];
-    if (!(RAMP_GEMM_DIAG & 2) && ((e.okn >> i) & 1u)) *reinterpret_cast<uint4*>(plane + (size_t)e.rown[i] * ld + col0 + 8 * (c4 % H)) = t;
-  }
+  for (int i = 0; i < E::NP; ++i) t[i] = s4[stg_idx<CW>(rsub + E::RP * i, c4)];
+#pragma unroll
+  for (int i = 0; i < E::NP; ++i)
+    if (!(RAMP_GEMM_DIAG & 2) && ((e.okn >> i) & 1u)) *reinterpret_cast<uint4*>(plane + (size_t)e.rown[i] * ld + col0 + 8 * (c4 % H)) = t[i];
   __syncwarp();
 }
 // Loads come in two phases: `chunk_ld_issue` puts the row-contiguous 16-byte loads of a chunk in flight (registers),
@@ -342,6 +427,7 @@ __device__ __forceinline__ void chunk_ld_finish(const EpiCtx<CW>& e, const float
   using E = EpiCtx<CW>;
   const int rsub = e.lane / E::G, c4 = e.lane % E::G;
   float4* s4 = reinterpret_cast<float4*>(e.stg);
+  stg_acquire<CW>(e);
 #pragma unroll
   for (int i = 0; i < E::NP; ++i) s4[stg_idx<CW>(rsub + E::RP * i, c4)] = t[i];
   __syncwarp();
@@ -399,8 +485,8 @@ __device__ __forceinline__ void epi_plain(const GemmParams& p, const EpiCtx<CW>&
     float v[CW];
     ld_acc<CW>(acc + c, v);
     epi_affine_pf<CW>(p, e, v, colbase + c, t, colbase + c + CW, c + CW < c1);
-    if (p.out_f32) chunk_store_f32<CW>(e, v, p.out_f32, p.ldO, colbase + c);
-    if (p.out_hi) chunk_store_split<CW>(e, v, p.out_hi, p.out_lo, p.ldS, colbase + c);
+    if (p.out_f32) chunk_store_f32<CW>(e, v, p.out_f32, p.ldO, colbase + c, e.maps ? &e.maps->f32 : nullptr);
+    if (p.out_hi) chunk_store_split<CW>(e, v, p.out_hi, p.out_lo, p.ldS, colbase + c, e.maps ? &e.maps->hi : nullptr, e.maps ? &e.maps->lo : nullptr);
   }
 }
 // GEGLU forward (layers_attention_mini.py:38-45): tile columns [0,128) = a, [128,256) = gate; a group drains the same
@@ -424,10 +510,10 @@ __device__ __forceinline__ void epi_geglu_fwd(const GemmParams& p, const EpiCtx<
       s_[i] = sgl;
     }
     if (p.out_f32) {
-      chunk_store_f32<CW>(e, s_, p.out_f32, p.ldO, colbase + c);
-      chunk_store_f32<CW>(e, g, p.out_f32, p.ldO, colbase + 128 + c);
+      chunk_store_f32<CW>(e, s_, p.out_f32, p.ldO, colbase + c, e.maps ? &e.maps->f32 : nullptr);
+      chunk_store_f32<CW>(e, g, p.out_f32, p.ldO, colbase + 128 + c, e.maps ? &e.maps->f32 : nullptr);
     }
-    chunk_store_split<CW>(e, a, p.out2_hi, p.out2_lo, p.ldS2, tile_n * 128 + c);
+    chunk_store_split<CW>(e, a, p.out2_hi, p.out2_lo, p.ldS2, tile_n * 128 + c, e.maps ? &e.maps->hi2 : nullptr, e.maps ? &e.maps->lo2 : nullptr);
   }
 }
 // GEGLU backward: acc = d(a * gelu(gate)) for natural columns colbase + c; u = (gelu(gate) | a gelu'(gate)) and du are
@@ -451,18 +537,19 @@ __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx<
     if (more) chunk_ld_issue<CW>(e, p.u, 2048, u_col(c + CW), ts);
 #pragma unroll
     for (int i = 0; i < CW; ++i) x[i] *= d[i];                      // u = (gelu(gate) | a * gelu'(gate))
-    chunk_store_split<CW>(e, x, p.out_hi, p.out_lo, p.ldS, pa);
+    chunk_store_split<CW>(e, x, p.out_hi, p.out_lo, p.ldS, pa, e.maps ? &e.maps->hi : nullptr, e.maps ? &e.maps->lo : nullptr);
     chunk_ld_finish<CW>(e, tq, x);
     if (more) chunk_ld_issue<CW>(e, p.u, 2048, u_col(c + CW) + 128, tq);
 #pragma unroll
     for (int i = 0; i < CW; ++i) x[i] *= d[i];
-    chunk_store_split<CW>(e, x, p.out_hi, p.out_lo, p.ldS, pg);
+    chunk_store_split<CW>(e, x, p.out_hi, p.out_lo, p.ldS, pg, e.maps ? &e.maps->hi : nullptr, e.maps ? &e.maps->lo : nullptr);
   }
 }
 // The NG threads that own the parts of a 256-channel row publish a float2 each (through their warps' staging tiles,
 // idle at that point) and read all of them back: everyone combines them in the same order, so they agree to the bit.
 template <int CW, int NG>
 __device__ __forceinline__ void row_exchange(const EpiCtx<CW>& e, float2 mine, float2 (&all)[NG]) {
+  stg_acquire<CW>(e);
   reinterpret_cast<float2*>(e.stg)[e.lane] = mine;
   row_sync<NG>(e.bar_id);
 #pragma unroll
@@ -481,8 +568,8 @@ __device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx<CW>
     float v[CW];
     ld_acc<CW>(acc + c, v);
     epi_affine_pf<CW>(p, e, v, c, t, c + CW, c + CW < c1);
-    if (p.out_f32) chunk_store_f32<CW>(e, v, p.out_f32, p.ldO, c);
-    if (p.out_hi) chunk_store_split<CW>(e, v, p.out_hi, p.out_lo, p.ldS, c);
+    if (p.out_f32) chunk_store_f32<CW>(e, v, p.out_f32, p.ldO, c, e.maps ? &e.maps->f32 : nullptr);
+    if (p.out_hi) chunk_store_split<CW>(e, v, p.out_hi, p.out_lo, p.ldS, c, e.maps ? &e.maps->hi : nullptr, e.maps ? &e.maps->lo : nullptr);
     st_acc<CW>(acc + c, v);
     if (c == c0) shift = v[0];
 #pragma unroll
@@ -520,7 +607,7 @@ __device__ __forceinline__ void epi_ln_fwd(const GemmParams& p, const EpiCtx<CW>
       v[i] = (v[i] - mean) * rstd * g.x + b.x; v[i + 1] = (v[i + 1] - mean) * rstd * g.y + b.y;
       v[i + 2] = (v[i + 2] - mean) * rstd * g.z + b.z; v[i + 3] = (v[i + 3] - mean) * rstd * g.w + b.w;
     }
-    chunk_store_split<CW>(e, v, p.out2_hi, p.out2_lo, p.ldS2, c);
+    chunk_store_split<CW>(e, v, p.out2_hi, p.out2_lo, p.ldS2, c, e.maps ? &e.maps->hi2 : nullptr, e.maps ? &e.maps->lo2 : nullptr);
   }
 }
 // out = residual + LayerNorm_backward(ln_x, acc): dx = rstd * (dyh - mean(dyh) - xh * mean(dyh * xh)), dyh = acc * gamma
@@ -578,8 +665,8 @@ __device__ __forceinline__ void epi_ln_bwd(const GemmParams& p, const EpiCtx<CW>
 #pragma unroll
       for (int i = 0; i < CW; ++i) d[i] += x[i];
     }
-    if (p.out_f32) chunk_store_f32<CW>(e, d, p.out_f32, p.ldO, c);
-    if (p.out_hi) chunk_store_split<CW>(e, d, p.out_hi, p.out_lo, p.ldS, c);
+    if (p.out_f32) chunk_store_f32<CW>(e, d, p.out_f32, p.ldO, c, e.maps ? &e.maps->f32 : nullptr);
+    if (p.out_hi) chunk_store_split<CW>(e, d, p.out_hi, p.out_lo, p.ldS, c, e.maps ? &e.maps->hi : nullptr, e.maps ? &e.maps->lo : nullptr);
   }
 }
 
@@ -594,7 +681,7 @@ template <int EPI, int CW, int CG>
 __global__ void __launch_bounds__(gemm_threads(CW), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant__ CUtensorMap mapAlo,
                const __grid_constant__ CUtensorMap mapBhi, const __grid_constant__ CUtensorMap mapBlo,
-               const GemmParams p) {
+               const __grid_constant__ EpiMaps omaps, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -753,6 +840,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
       EpiCtx<CW> e;
       using E = EpiCtx<CW>;
       e.lane = lane;
+      e.maps = p.tma_store ? &omaps : nullptr;
       e.bar_id = 1 + q;
       e.stg = stg_all + (warp - EPI_W0) * (32 * CW);
       e.stg_q = stg_all + ((warp - EPI_W0) & 3) * (32 * CW);
@@ -768,6 +856,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
         e.my_sample = tile_m * p.nb + n_local;
         e.my_ok = n_local < p.nb && e.my_sample < p.n_samples;
         e.my_row = (size_t)e.my_sample * p.o_L + (size_t)l * p.o_stride + p.o_off;
+        e.row0 = tile_m * BM + q * 32;            // dense outputs: accumulator row r of tile m is output row m * 128 + r
         e.okn = 0;
 #pragma unroll
         for (int i = 0; i < E::NP; ++i) {
@@ -792,6 +881,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
           else mbar_arrive(tempty0 + 8 * buf);
         }
       }
+      if (p.tma_store && lane == 0) tma_store_wait_all();      // shared memory must outlive the last bulk stores
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -821,6 +911,9 @@ static int g_l2promo = 256;
 #define RAMP_GEMM_PAIR_DEFAULT 1      // measured on B200 (profiles/r2_cta_pair_ab.txt): +4.1 % on the headline, LN-backward launches -15 %
 #endif
 static int g_pair = RAMP_GEMM_PAIR_DEFAULT;
+// RAMP_GEMM_TMA_STORE: 1 = launches whose tile rows are consecutive output rows store through TMA (bulk tensor stores of
+// the epilogue warps' staging tiles); 0 = every launch uses the LDS -> STG read-back path (round 1 / A/B runs)
+static int g_tma_store = 1;
 
 int gemm_init() {
   if (g_encode) return 0;
@@ -841,12 +934,13 @@ int gemm_init() {
 #undef RAMP_GEMM_ATTR
   if (const char* v = getenv("RAMP_GEMM_L2PROMO")) g_l2promo = atoi(v);
   if (const char* v = getenv("RAMP_GEMM_PAIR")) g_pair = atoi(v);
+  if (const char* v = getenv("RAMP_GEMM_TMA_STORE")) g_tma_store = atoi(v);
   g_encode = (EncodeTiledFn)fn;
   return 0;
 }
 
 struct MapKey {
-  const void* ptr; uint64_t d[4]; uint64_t s[3]; uint32_t box[4]; int rank;
+  const void* ptr; uint64_t d[4]; uint64_t s[3]; uint32_t box[4]; int rank; int dtype; int swizzle; int pad_;
   bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
 };
 struct MapKeyHash {
@@ -861,10 +955,11 @@ static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 static std::mutex g_maps_mu;
 
 static int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                    const uint32_t* box) {
+                    const uint32_t* box, CUtensorMapDataType dtype = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                    CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   MapKey key;
   std::memset(&key, 0, sizeof(key));
-  key.ptr = ptr; key.rank = rank;
+  key.ptr = ptr; key.rank = rank; key.dtype = (int)dtype; key.swizzle = (int)swizzle;
   for (int i = 0; i < rank; ++i) { key.d[i] = dims[i]; key.box[i] = box[i]; }
   for (int i = 0; i < rank - 1; ++i) key.s[i] = strides_bytes[i];
   std::lock_guard<std::mutex> lk(g_maps_mu);
@@ -873,8 +968,8 @@ static int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t*
   cuuint64_t gd[4]; cuuint64_t gs[3]; cuuint32_t bx[4]; cuuint32_t es[4] = {1, 1, 1, 1};
   for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; }
   for (int i = 0; i < rank - 1; ++i) gs[i] = strides_bytes[i];
-  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gd, gs, bx, es,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  CUresult r = g_encode(out, dtype, (cuuint32_t)rank, const_cast<void*>(ptr), gd, gs, bx, es,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
                         g_l2promo == 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -975,6 +1070,24 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
     if (make_map(&mBhi, d.w_hi, 2, dims, str, box)) return -3;
     if (p.nplanes == 2) { if (make_map(&mBlo, d.w_lo, 2, dims, str, box)) return -3; } else mBlo = mBhi;
   }
+  // output tensor maps of the TMA store path: [rows = n_samples * L_out][ld] arrays, boxes of 32 rows x cw columns
+  EpiMaps om;
+  std::memset(&om, 0, sizeof(om));
+  p.tma_store = (g_tma_store && d.o_L == d.L_out && d.o_stride == 1 && d.o_off == 0 && BM % d.L_out == 0) ? 1 : 0;
+  if (p.tma_store) {
+    const uint64_t rows = (uint64_t)d.n_samples * d.L_out;
+    const uint32_t box[2] = {(uint32_t)cw, 32u};
+    auto omap = [&](CUtensorMap* m, const void* ptr, int ld, bool f32) -> int {
+      if (!ptr) return 0;
+      uint64_t dims[2] = {(uint64_t)ld, rows};
+      uint64_t str[1] = {(uint64_t)ld * (f32 ? 4 : 2)};
+      const CUtensorMapSwizzle sw = f32 ? (cw == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B)
+                                        : (cw == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+      return make_map(m, ptr, 2, dims, str, box, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, sw);
+    };
+    if (omap(&om.f32, d.out_f32, d.ldO, true) || omap(&om.hi, d.out_hi, d.ldS, false) || omap(&om.lo, d.out_lo, d.ldS, false) ||
+        omap(&om.hi2, d.out2_hi, d.ldS2, false) || omap(&om.lo2, d.out2_lo, d.ldS2, false)) return -3;
+  }
   const size_t smem = (size_t)stages * stage_bytes + fixed;
   const long tiles = (long)((p.m_tiles + cg - 1) / cg) * p.n_tiles * cg;      // CTAs that have work
   const long max_ctas = g_num_sms / cg * cg;
@@ -1001,8 +1114,8 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
 #define RAMP_GEMM_LAUNCH(E, C)                                                                       \
   do {                                                                                               \
     cfg.blockDim = dim3(gemm_threads(C));                                                            \
-    if (cg == 2) RAMP_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<E, C, 2>, mAhi, mAlo, mBhi, mBlo, p));  \
-    else RAMP_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<E, C, 1>, mAhi, mAlo, mBhi, mBlo, p));          \
+    if (cg == 2) RAMP_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<E, C, 2>, mAhi, mAlo, mBhi, mBlo, om, p));  \
+    else RAMP_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<E, C, 1>, mAhi, mAlo, mBhi, mBlo, om, p));          \
   } while (0)
   switch (d.epi) {
     case EPI_PLAIN: if (cw == 16) RAMP_GEMM_LAUNCH(EPI_PLAIN, 16); else RAMP_GEMM_LAUNCH(EPI_PLAIN, 32); break;
