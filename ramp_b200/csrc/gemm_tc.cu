@@ -77,6 +77,7 @@ struct GemmParams {
   const float* ln_gamma; const float* ln_beta; float* ln_stats; const float* ln_x; const float* u;
   bf16* out2_hi; bf16* out2_lo; int ldS2;
   int tma_store;                              // 1: dense output rows -> the epilogue stores through TMA (see EpiMaps)
+  int stg_bufs;                               // staging tiles per epilogue warp (1..3; > 1 only with tma_store)
 };
 // Tensor maps of the outputs (fp32 copy, hi / lo planes, second hi / lo planes) for the TMA store path.  Used when the
 // tile's 128 accumulator rows are 128 consecutive output rows (o_L == L_out, o_stride == 1, o_off == 0: every launch of
@@ -131,6 +132,8 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read2() { asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 // ---- CTA-pair (cta_group::2) variants: M = 256 tile over two SMs of a TPC; each CTA stages its own 128 A rows and HALF of
@@ -300,8 +303,11 @@ __device__ __forceinline__ int stg_idx(int r, int k) {
 template <int CW>
 struct EpiCtx {
   static constexpr int G = CW / 4, RP = 32 / G, NP = G;   // groups per row, rows per pass, passes
-  float* stg;              // this warp's staging tile
-  float* stg_q;            // staging tile of group 0's warp for this lane quarter (+ 4 * 32 * CW floats per group)
+  mutable float* stg;      // this warp's current staging tile
+  float* stg0;             // its first staging tile (of nbuf, 32 x CW floats each)
+  float* stg_q;            // first staging tile of group 0's warp for this lane quarter (+ 4 * nbuf * 32 * CW floats per group)
+  int nbuf; mutable int cur;   // TMA store path: a bulk store leaves its tile busy until the TMA unit has read it, so the
+                           // warp rotates over nbuf tiles and only waits until at most nbuf - 1 stores are still reading
   const EpiMaps* maps;     // TMA store path: output tensor maps, else nullptr
   int row0;                // first output row of this warp's 32 accumulator rows (TMA store path)
   int lane, bar_id;
@@ -317,9 +323,16 @@ __device__ __forceinline__ void row_sync(int bar_id) { asm volatile("bar.sync %0
 template <int CW>
 __device__ __forceinline__ void stg_acquire(const EpiCtx<CW>& e) {
   if (e.maps) {
-    if (e.lane == 0) tma_store_wait_read();
+    // the current tile's last store is nbuf stores back: all but the newest nbuf - 1 groups must have been read
+    if (e.lane == 0) { if (e.nbuf == 1) tma_store_wait_read(); else if (e.nbuf == 2) tma_store_wait_read1(); else tma_store_wait_read2(); }
     __syncwarp();
   }
+}
+// after a bulk store was issued from the current tile: move on to the next one
+template <int CW>
+__device__ __forceinline__ void stg_rotate(const EpiCtx<CW>& e) {
+  e.cur = e.cur + 1 == e.nbuf ? 0 : e.cur + 1;
+  e.stg = e.stg0 + e.cur * (32 * CW);
 }
 template <int CW>
 __device__ __forceinline__ void chunk_store_f32(const EpiCtx<CW>& e, const float (&v)[CW], float* base, int ld, int col0,
@@ -338,6 +351,7 @@ __device__ __forceinline__ void chunk_store_f32(const EpiCtx<CW>& e, const float
       if (!(RAMP_GEMM_DIAG & 2)) tma_store_2d(map, smem_u32(e.stg), col0, e.row0);
       tma_store_commit();
     }
+    stg_rotate<CW>(e);
     return;
   }
   __syncwarp();
@@ -387,6 +401,7 @@ __device__ __forceinline__ void chunk_store_split(const EpiCtx<CW>& e, const flo
       }
       tma_store_commit();
     }
+    stg_rotate<CW>(e);
     return;
   }
 #pragma unroll
@@ -549,11 +564,14 @@ __device__ __forceinline__ void epi_geglu_bwd(const GemmParams& p, const EpiCtx<
 // idle at that point) and read all of them back: everyone combines them in the same order, so they agree to the bit.
 template <int CW, int NG>
 __device__ __forceinline__ void row_exchange(const EpiCtx<CW>& e, float2 mine, float2 (&all)[NG]) {
-  stg_acquire<CW>(e);
-  reinterpret_cast<float2*>(e.stg)[e.lane] = mine;
+  if (e.maps) {                                  // the exchange goes through tile 0 of every warp: nothing may still read it
+    if (e.lane == 0) tma_store_wait_read();
+    __syncwarp();
+  }
+  reinterpret_cast<float2*>(e.stg0)[e.lane] = mine;
   row_sync<NG>(e.bar_id);
 #pragma unroll
-  for (int g = 0; g < NG; ++g) all[g] = reinterpret_cast<const float2*>(e.stg_q + g * (4 * 32 * CW))[e.lane];
+  for (int g = 0; g < NG; ++g) all[g] = reinterpret_cast<const float2*>(e.stg_q + g * (4 * e.nbuf * 32 * CW))[e.lane];
   row_sync<NG>(e.bar_id);                        // nobody re-uses a staging tile before all have read it
 }
 // LayerNorm forward over the 256 channels of a row (eps 1e-5, layers_attention_mini.py:138-140); this thread drains
@@ -690,7 +708,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   const int b_tile_bytes = (p.BN / CG) * BK * 2;        // this CTA's share of the weight tile
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + b_tile_bytes);
   const uint32_t stg_base = smem_base + p.stages * stage_bytes;            // the epilogue warps' staging tiles
-  const uint32_t bar_base = stg_base + STG_BYTES;
+  const uint32_t bar_base = stg_base + p.stg_bufs * STG_BYTES;
   const uint32_t full0 = bar_base, empty0 = bar_base + 8 * p.stages;
   const uint32_t tfull0 = bar_base + 16 * p.stages, tempty0 = tfull0 + 16;  // 2 + 2 accumulator barriers
   const uint32_t tmem_slot = tempty0 + 16;
@@ -842,8 +860,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
       e.lane = lane;
       e.maps = p.tma_store ? &omaps : nullptr;
       e.bar_id = 1 + q;
-      e.stg = stg_all + (warp - EPI_W0) * (32 * CW);
-      e.stg_q = stg_all + ((warp - EPI_W0) & 3) * (32 * CW);
+      e.nbuf = p.stg_bufs; e.cur = 0;
+      e.stg0 = stg_all + (warp - EPI_W0) * (p.stg_bufs * 32 * CW);
+      e.stg = e.stg0;
+      e.stg_q = stg_all + ((warp - EPI_W0) & 3) * (p.stg_bufs * 32 * CW);
       const int cols = p.BN / p.ngroups;                      // tile columns this group drains
       const int c0 = group * cols, c1 = c0 + cols;
       const int r = q * 32 + lane;
@@ -914,6 +934,15 @@ static int g_pair = RAMP_GEMM_PAIR_DEFAULT;
 // RAMP_GEMM_TMA_STORE: 1 = launches whose tile rows are consecutive output rows store through TMA (bulk tensor stores of
 // the epilogue warps' staging tiles); 0 = every launch uses the LDS -> STG read-back path (round 1 / A/B runs)
 static int g_tma_store = 1;
+// RAMP_GEMM_STG_BUFS = "e0,e1,e2,e3,e4": staging tiles per epilogue warp wanted by each epilogue mode (TMA store path; each
+// extra tile costs 32 KB of the operand ring).  RAMP_GEMM_MIN_STAGES: operand stages that must remain.
+static int g_stg_want[5] = {1, 1, 2, 2, 2};
+static int g_min_stages = 2;
+// RAMP_GEMM_E1_CW: epilogue configuration of the GEGLU forward (16 = 16 warps x 16-column chunks, 32 = 8 warps x 32)
+static int g_e1_cw = 16;
+// a launch gets its mode's extra staging tiles only while its k-loop is short (iterations per tile <= limit): long k-loops
+// are tensor-bound and want the operand stages instead (profiles/r2_stg_bufs.txt)
+static int g_stg_max_iters[5] = {0, 1 << 30, 1 << 30, 4, 12};
 
 int gemm_init() {
   if (g_encode) return 0;
@@ -929,12 +958,23 @@ int gemm_init() {
 #define RAMP_GEMM_ATTR(E, C)                                                                                         \
   RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<E, C, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));      \
   RAMP_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<E, C, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-  RAMP_GEMM_ATTR(EPI_PLAIN, 32) RAMP_GEMM_ATTR(EPI_PLAIN, 16) RAMP_GEMM_ATTR(EPI_GEGLU_FWD, 16)
+  RAMP_GEMM_ATTR(EPI_PLAIN, 32) RAMP_GEMM_ATTR(EPI_PLAIN, 16) RAMP_GEMM_ATTR(EPI_GEGLU_FWD, 16) RAMP_GEMM_ATTR(EPI_GEGLU_FWD, 32)
   RAMP_GEMM_ATTR(EPI_GEGLU_BWD, 32) RAMP_GEMM_ATTR(EPI_LN_FWD, 32) RAMP_GEMM_ATTR(EPI_LN_BWD, 32)
 #undef RAMP_GEMM_ATTR
   if (const char* v = getenv("RAMP_GEMM_L2PROMO")) g_l2promo = atoi(v);
   if (const char* v = getenv("RAMP_GEMM_PAIR")) g_pair = atoi(v);
   if (const char* v = getenv("RAMP_GEMM_TMA_STORE")) g_tma_store = atoi(v);
+  if (const char* v = getenv("RAMP_GEMM_STG_BUFS")) {
+    int w[5];
+    if (sscanf(v, "%d,%d,%d,%d,%d", &w[0], &w[1], &w[2], &w[3], &w[4]) == 5)
+      for (int i = 0; i < 5; ++i) g_stg_want[i] = w[i] < 1 ? 1 : (w[i] > 3 ? 3 : w[i]);
+  }
+  if (const char* v = getenv("RAMP_GEMM_E1_CW")) g_e1_cw = atoi(v) == 32 ? 32 : 16;
+  if (const char* v = getenv("RAMP_GEMM_STG_ITERS")) {
+    int w[5];
+    if (sscanf(v, "%d,%d,%d,%d,%d", &w[0], &w[1], &w[2], &w[3], &w[4]) == 5) for (int i = 0; i < 5; ++i) g_stg_max_iters[i] = w[i];
+  }
+  if (const char* v = getenv("RAMP_GEMM_MIN_STAGES")) { g_min_stages = atoi(v); if (g_min_stages < 1) g_min_stages = 1; }
   g_encode = (EncodeTiledFn)fn;
   return 0;
 }
@@ -1030,13 +1070,19 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
     p.BN = 256;
   }
   p.n_tiles = d.Nout / p.BN;
-  const int cw = (d.epi == EPI_GEGLU_FWD || p.BN == 16) ? 16 : 32;     // epilogue configuration (see epi_warps)
+  const int cw = ((d.epi == EPI_GEGLU_FWD && g_e1_cw == 16) || p.BN == 16) ? 16 : 32;     // epilogue configuration (see epi_warps)
   p.ngroups = p.BN / cw < epi_warps(cw) / 4 ? p.BN / cw : epi_warps(cw) / 4;
   p.nplanes = d.precision == 3 ? 2 : 1;
   // CTA pairs: worth it where the weight tile is large (BN >= 128) and there are enough tile pairs to fill the pairs of SMs
   const int cg = (g_pair && p.BN >= 128 && (long)((p.m_tiles + 1) / 2) * p.n_tiles >= g_num_sms / 2) ? 2 : 1;
   const int stage_bytes = p.nplanes * (A_TILE_BYTES + (p.BN / cg) * BK * 2);
-  const int fixed = 1024 + STG_BYTES + 256;
+  // TMA store path (see EpiMaps): only where a tile's accumulator rows are consecutive output rows
+  p.tma_store = (g_tma_store && d.o_L == d.L_out && d.o_stride == 1 && d.o_off == 0 && BM % d.L_out == 0) ? 1 : 0;
+  // staging tiles per epilogue warp: as many as the mode wants (g_stg_want) while at least g_min_stages operand stages fit
+  int nbuf = (p.tma_store && p.ntaps * p.kblocks <= g_stg_max_iters[d.epi]) ? g_stg_want[d.epi] : 1;
+  while (nbuf > 1 && (g_max_smem - (1024 + nbuf * STG_BYTES + 256)) / stage_bytes < g_min_stages) --nbuf;
+  p.stg_bufs = nbuf;
+  const int fixed = 1024 + nbuf * STG_BYTES + 256;
   int stages = (g_max_smem - fixed) / stage_bytes;
   if (stages > 6) stages = 6;
   const long total_iters = (long)p.ntaps * p.kblocks * ((long)((p.m_tiles + cg - 1) / cg) * p.n_tiles + g_num_sms / cg - 1) / (g_num_sms / cg);
@@ -1073,7 +1119,6 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   // output tensor maps of the TMA store path: [rows = n_samples * L_out][ld] arrays, boxes of 32 rows x cw columns
   EpiMaps om;
   std::memset(&om, 0, sizeof(om));
-  p.tma_store = (g_tma_store && d.o_L == d.L_out && d.o_stride == 1 && d.o_off == 0 && BM % d.L_out == 0) ? 1 : 0;
   if (p.tma_store) {
     const uint64_t rows = (uint64_t)d.n_samples * d.L_out;
     const uint32_t box[2] = {(uint32_t)cw, 32u};
@@ -1119,7 +1164,7 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   } while (0)
   switch (d.epi) {
     case EPI_PLAIN: if (cw == 16) RAMP_GEMM_LAUNCH(EPI_PLAIN, 16); else RAMP_GEMM_LAUNCH(EPI_PLAIN, 32); break;
-    case EPI_GEGLU_FWD: RAMP_GEMM_LAUNCH(EPI_GEGLU_FWD, 16); break;
+    case EPI_GEGLU_FWD: if (cw == 16) RAMP_GEMM_LAUNCH(EPI_GEGLU_FWD, 16); else RAMP_GEMM_LAUNCH(EPI_GEGLU_FWD, 32); break;
     case EPI_GEGLU_BWD: RAMP_GEMM_LAUNCH(EPI_GEGLU_BWD, 32); break;
     case EPI_LN_FWD: RAMP_GEMM_LAUNCH(EPI_LN_FWD, 32); break;
     default: RAMP_GEMM_LAUNCH(EPI_LN_BWD, 32); break;
