@@ -11,7 +11,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "ramp_b200", "libramp_b200.so")
 KEYS = ["UTCHMMA", "UTCQMMA", "UTMALDG", "UTMASTG", "UBLKCP", "LDTM", "STTM", "UTCBAR", "SYNCS", "HMMA", "LDSM", "LDGSTS",
-        "FFMA", "FMNMX3", "MUFU", "F2FP", "LDG", "STG", "LDS", "STS", "BAR"]
+        "FFMA2", "FFMA", "FMNMX3", "MUFU", "F2FP", "LDG", "STG", "LDS", "STS", "BAR"]
 
 
 def main():

@@ -31,14 +31,25 @@ def _gemm(a, w, taps, L_out, a_pstride=1, bias=None, bias_tab=None, row2scene=No
     wh, wl = _split(w)
     o_L = o_L or L_out
     out_rows = out_rows or n * o_L
-    out = torch.zeros(out_rows, Nout, device=a.device)
-    oh = torch.zeros(out_rows, Nout, device=a.device, dtype=_hi_dtype()) if want_split else None
-    ol = torch.zeros(out_rows, Nout, device=a.device, dtype=_hi_dtype()) if want_split else None
+    # guard bands of 160 rows around every output (compute-sanitizer is closed on this pool): the kernel masks / the TMA
+    # unit clips the rows of a partial last tile, so the bands must come back untouched
+    G, SENT = 160, 12288.0
+
+    def banded(dtype):
+        buf = torch.full((G + out_rows + G, Nout), SENT, device=a.device, dtype=dtype)
+        buf[G:G + out_rows] = 0
+        return buf, buf[G:G + out_rows]
+    out_buf, out = banded(torch.float32)
+    oh_buf, oh = banded(_hi_dtype()) if want_split else (None, None)
+    ol_buf, ol = banded(_hi_dtype()) if want_split else (None, None)
     tp = (ctypes.c_int * (3 * len(taps)))(*[v for t in taps for v in t])
     check(lib().ramp_gemm(ptr(ah), ptr(al), n, L_in, ldA, K, a_pstride, L_out, len(taps), tp, ptr(wh), ptr(wl), Nout, Kw,
                           n_wt, ptr(bias), ptr(bias_tab), ptr(row2scene), ptr(residual), Nout, ptr(out), Nout,
                           ptr(oh), ptr(ol), Nout, o_L, o_stride, o_off, precision, stream_ptr()), "ramp_gemm")
     torch.cuda.synchronize()
+    for buf in (out_buf, oh_buf, ol_buf):
+        if buf is not None:
+            assert bool((buf[:G] == SENT).all()) and bool((buf[G + out_rows:] == SENT).all()), "write outside the output rows"
     ar = ah.double() + (al.double() if precision == 3 else 0)
     wr = wh.double() + (wl.double() if precision == 3 else 0)
     return out, (oh, ol), ar, wr

@@ -1,0 +1,63 @@
+"""The GEMM's run-time knobs must not change results: the TMA store path, the LDS -> STG read-back path,
+every staging-tile rotation depth, CTA pairs on / off and the 8-warp GEGLU-forward configuration give bit-identical score
+rows.  The library reads its environment once, so every setting runs in its own process."""
+import hashlib
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+CHILD = r"""
+import hashlib, sys, torch
+sys.path.insert(0, %r)
+from ramp_b200.unet import TemporalUnetInference
+from ramp_b200.testing import synthetic_state_dict
+dev = torch.device("cuda", 0)
+rows = 640                       # 320 M-tiles at L = 64: CTA pairs and the persistent tile walk are both exercised
+net = TemporalUnetInference(n_support_points=64, state_dim=4, max_rows=rows, max_scenes=3)
+net.load_state_dict(synthetic_state_dict(net, 0))
+net = net.to(dev)
+net.prepare(horizon=64, max_rows=rows, max_scenes=3)
+g = torch.Generator("cpu").manual_seed(3)
+net.set_scene_latents((torch.randn(3, net.context_dim, generator=g) * 0.5).to(dev))
+x = torch.randn(rows, 64, 4, generator=g).to(dev)
+r2s = (torch.arange(rows) %% 3).to(torch.int32).to(dev)
+eps = net.energy_grad_rows(x, 9, r2s)
+torch.cuda.synchronize()
+assert torch.isfinite(eps).all()
+print("HASH", hashlib.sha256(eps.cpu().numpy().tobytes()).hexdigest(), float(eps.abs().max()))
+""" % ROOT
+
+
+def _run(env_extra):
+    env = dict(os.environ)
+    for k in list(env):
+        if k.startswith("RAMP_GEMM_") or k == "RAMP_UNET_SPLIT":
+            del env[k]
+    env.update(env_extra)
+    out = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = [l for l in out.stdout.splitlines() if l.startswith("HASH")][-1].split()
+    return line[1], float(line[2])
+
+
+def test_knobs_do_not_change_the_rows(cuda):
+    base, mag = _run({})
+    assert mag > 1e-3
+    settings = [
+        {"RAMP_GEMM_TMA_STORE": "0"},
+        {"RAMP_GEMM_STG_BUFS": "3,3,3,3,3", "RAMP_GEMM_STG_ITERS": "99,99,99,99,99", "RAMP_GEMM_MIN_STAGES": "1"},
+        {"RAMP_GEMM_STG_BUFS": "1,1,1,1,1"},
+        {"RAMP_GEMM_PAIR": "0"},
+        {"RAMP_GEMM_E1_CW": "32"},
+        {"RAMP_UNET_SPLIT": "1"},
+    ]
+    for s in settings:
+        h, _ = _run(s)
+        assert h == base, "rows changed under %r" % (s,)
+    print("score rows bit-identical under %d knob settings (sha256 %s...)" % (len(settings), base[:12]))
