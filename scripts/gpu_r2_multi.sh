@@ -10,7 +10,7 @@ for N in $1; do
     timeout 900 python bench.py --workload sweep --gpus 1 --steps 1 --warmup 1 > ${O}_sweep_n1.json 2> ${O}_sweep_n1.err
   else
     timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT \
-        bench.py --workload sweep --gpus $N --steps 2 --warmup 1 > ${O}_sweep_n$N.json 2> ${O}_sweep_n$N.err
+        bench.py --workload sweep --gpus $N --steps ${STEPS:-2} --warmup 1 > ${O}_sweep_n$N.json 2> ${O}_sweep_n$N.err
   fi
   echo "sweep N=$N rc $?"; tail -c 1200 ${O}_sweep_n$N.json | python -c "
 import json,sys
