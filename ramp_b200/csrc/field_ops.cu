@@ -522,7 +522,8 @@ static int nn_dispatch(int R, int TILE, const float4* c4, const int* perm, int P
 #define RAMP_NN_CASE(r) \
   case r: return nn_launch<DIM, r, 512>(c4, perm, P, Ppad, q, Q, qstride, thr, od, oi, s);
   switch (R) {
-    RAMP_NN_CASE(1) RAMP_NN_CASE(2) RAMP_NN_CASE(4) RAMP_NN_CASE(6) RAMP_NN_CASE(8) RAMP_NN_CASE(10) RAMP_NN_CASE(12) RAMP_NN_CASE(16)
+    RAMP_NN_CASE(1) RAMP_NN_CASE(2) RAMP_NN_CASE(3) RAMP_NN_CASE(4) RAMP_NN_CASE(5) RAMP_NN_CASE(6) RAMP_NN_CASE(7) RAMP_NN_CASE(8)
+    RAMP_NN_CASE(9) RAMP_NN_CASE(10) RAMP_NN_CASE(12) RAMP_NN_CASE(14) RAMP_NN_CASE(16)
   }
 #undef RAMP_NN_CASE
   set_error("ramp_nn_query: unsupported register blocking");
@@ -531,14 +532,16 @@ static int nn_dispatch(int R, int TILE, const float4* c4, const int* perm, int P
 // The grid is one CTA per 128 R waypoints, each scanning the whole cloud, so an SM works through
 // ceil(CTAs / SMs) * R blocks of 128 waypoints.  The cost of one block depends little on R since the chunk bookkeeping left
 // the register file (more waypoints per thread amortise the shared-memory loads of a point pair over more FFMA2s, fewer
-// leave more CTAs resident), so the choice is mostly about filling whole waves.  Relative costs per block measured on B200
-// (profiles/r2_nn_sweep_ffma2.txt: 8192 x 64 waypoints, 1 M points, 512-point tiles; R = 1, 2 extrapolated); the launch
-// takes the R with the smallest ceil(CTAs / SMs) * R * cost[R].  1024-point tiles were 0-5 % slower at every R.
+// leave more CTAs resident), so the choice is mostly about filling whole waves: the launch takes the R with the smallest
+// ceil(CTAs / SMs) * R * cost[R].  cost[R] = ms per block measured on B200 at 8192 x 64 waypoints x 1 M points
+// (profiles/r2_nn_sweep_ffma2.txt, second sweep: all 13 instantiated R).  A model that charged a lone last CTA per SM as two
+// (the FP32 pipe needs several warps) was tried and did not predict the measurements - R = 7 (four co-resident CTAs per SM,
+// no tail) runs the 2-D sweep shape in 61.6 ms, R = 4 (six resident + a seventh) in 60.9 ms - so it is not in the formula.
 template <int DIM>
 static int nn_choose(int Q, int* R_out, int* TILE_out) {
-  static const int Rs[8] = {1, 2, 4, 6, 8, 10, 12, 16};
-  static const double cost2[8] = {3.60, 2.60, 2.171, 2.166, 2.121, 2.160, 2.105, 2.196};
-  static const double cost3[8] = {4.20, 3.00, 2.500, 2.466, 2.469, 2.451, 2.478, 2.496};
+  static const int Rs[13] = {1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 12, 14, 16};
+  static const double cost2[13] = {3.62, 2.30, 2.05, 2.175, 2.19, 2.165, 2.20, 2.125, 2.15, 2.16, 2.11, 2.25, 2.20};
+  static const double cost3[13] = {4.63, 2.81, 2.56, 2.50, 2.49, 2.47, 2.456, 2.47, 2.46, 2.47, 2.48, 2.52, 2.50};
   static int sms = 0;
   if (!sms) {
     int dev = 0;
@@ -546,12 +549,12 @@ static int nn_choose(int Q, int* R_out, int* TILE_out) {
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) sms = 148;
   }
   *TILE_out = 512;                                    // the only instantiated tile: 16 KB staged + 6-8 KB as pairs per CTA
-  if (const char* v = getenv("RAMP_NN_FORCE")) {      // "R,TILE" - tuning knob
+  if (const char* v = getenv("RAMP_NN_FORCE")) {      // "R" - tuning knob
     int r = 0, t = 0;
     if (sscanf(v, "%d,%d", &r, &t) >= 1) { *R_out = r; return 0; }
   }
   double best = 1e300;
-  for (int ri = 0; ri < 8; ++ri) {
+  for (int ri = 0; ri < 13; ++ri) {
     const long ctas = ((long)Q + NN_THREADS * Rs[ri] - 1) / (NN_THREADS * Rs[ri]);
     const double t = (double)((ctas + sms - 1) / sms) * Rs[ri] * (DIM == 2 ? cost2[ri] : cost3[ri]);
     if (t < best) { best = t; *R_out = Rs[ri]; }

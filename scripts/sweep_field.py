@@ -10,8 +10,9 @@ sys.path.insert(0, ".")
 from ramp_b200 import ops  # noqa: E402
 
 Bq = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+P_LOG2 = int(sys.argv[2]) if len(sys.argv) > 2 else 20
 dev = torch.device("cuda", 0)
-P, H = 1 << 20, 64
+P, H = 1 << P_LOG2, 64
 sms = torch.cuda.get_device_properties(0).multi_processor_count
 peak = sms * 128 * 2 * 1.965e9
 for dim in (2, 3):
@@ -23,7 +24,7 @@ for dim in (2, 3):
     d = torch.empty(Bq, H, device=dev)
     i = torch.empty(Bq, H, device=dev, dtype=torch.int32)
     ref = None
-    for force in [None] + [(r, t) for t in (512, 1024) for r in (4, 6, 8, 10, 12, 16)]:
+    for force in [None] + [(r, 512) for r in (1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 12, 14, 16)]:
         if force is None:
             os.environ.pop("RAMP_NN_FORCE", None)
         else:
