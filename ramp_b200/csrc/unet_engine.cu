@@ -21,7 +21,7 @@ UnetEngine::~UnetEngine() {
 int UnetEngine::ensure_side_streams() {
   if (fork_ev_) return 0;
   RAMP_CUDA_OK(cudaEventCreateWithFlags(&fork_ev_, cudaEventDisableTiming));
-  for (int i = 0; i < split_; ++i) {
+  for (int i = 0; i < 4; ++i) {      // a plan has at most 4 parts (plan_parts)
     RAMP_CUDA_OK(cudaStreamCreateWithFlags(&side_[i], cudaStreamNonBlocking));
     RAMP_CUDA_OK(cudaEventCreateWithFlags(&join_ev_[i], cudaEventDisableTiming));
   }
@@ -303,6 +303,12 @@ int UnetEngine::finalize(cudaStream_t s) {
   // streams (see unet_engine.cuh)
   if (const char* v = getenv("RAMP_UNET_SPLIT")) { split_ = atoi(v); if (split_ < 1) split_ = 1; if (split_ > 4) split_ = 4; }
   if (const char* v = getenv("RAMP_UNET_SPLIT_MIN")) { split_min_rows_ = atoi(v); if (split_min_rows_ < 32) split_min_rows_ = 32; }
+  if (const char* v = getenv("RAMP_UNET_SPLIT_ALIGN")) split_align_ = atoi(v) != 0;
+  {
+    int dev = 0;
+    RAMP_CUDA_OK(cudaGetDevice(&dev));
+    if (cudaDeviceGetAttribute(&sms_, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms_ < 1) sms_ = 148;
+  }
   // size the workspace with a dry run at max_rows (and, in split mode, as the parts it would be run as)
   dry_ = true; arena_off_ = 0;
   rc = run(nullptr, cfg_.max_rows, 1, 0.f, nullptr, nullptr, nullptr, s);
@@ -312,6 +318,14 @@ int UnetEngine::finalize(cudaStream_t s) {
     const int per = (cfg_.max_rows + split_ - 1) / split_ + 16;
     for (int p = 0; p < split_ && !rc; ++p) rc = run(nullptr, per, 1, 0.f, nullptr, nullptr, nullptr, s);
     if (arena_off_ > need) need = arena_off_;
+    if (!rc && split_align_) {       // wave-aligned parts (sizes depend on the caller's rows per trajectory: 2 % + 8 MB slack,
+      int rows[4];                   // and energy_grad falls back to one call if a plan does not fit)
+      const int np = plan_parts(cfg_.max_rows, 16, rows);
+      arena_off_ = 0;
+      for (int p = 0; p < np && !rc; ++p) rc = run(nullptr, rows[p] + 16, 1, 0.f, nullptr, nullptr, nullptr, s);
+      const size_t want = arena_off_ + arena_off_ / 50 + ((size_t)8 << 20);
+      if (want > need) need = want;
+    }
   }
   dry_ = false;
   if (rc) return rc;
@@ -329,6 +343,30 @@ int UnetEngine::set_scenes(const float* latents_dev, int n_scenes, cudaStream_t 
   return scene_constants((const SceneBlock*)scene_blocks_dev_, 16, latents_dev, n_scenes, cfg_.ctx_dim, s);
 }
 
+// Row counts of the parts a call of n_rows is run as (at most 4; whole multiples of `unit` rows except the last).
+int UnetEngine::plan_parts(int n_rows, int unit, int* rows) const {
+  int n = 0;
+  if (split_align_) {
+    const int nb = 128 / (cfg_.horizon / 8);             // samples per 128-row tile at the deepest level
+    const int W = sms_ * nb;                              // rows (samples) of one full wave of tiles there
+    const int k = n_rows / W;
+    if (k >= 1) {
+      const int np = split_ < k ? split_ : k;
+      int used = 0;
+      for (int i = 0; i < np && n < 3; ++i) {
+        const int w = k / np + (i < k % np ? 1 : 0);
+        const int r = (int)((long)w * W / unit * unit);
+        if (r > 0) { rows[n++] = r; used += r; }
+      }
+      if (n_rows - used > 0) rows[n++] = n_rows - used;
+      return n;
+    }
+  }
+  const int per = ((n_rows + split_ - 1) / split_ + unit - 1) / unit * unit;
+  for (int r0 = 0; r0 < n_rows && n < 4; r0 += per) rows[n++] = n_rows - r0 < per ? n_rows - r0 : per;
+  return n;
+}
+
 int UnetEngine::energy_grad(const float* x, int n_rows, int x_repeat, float t, const int* row2scene, float* eps_out,
                             float* f_out, cudaStream_t s) {
   RAMP_CHECK(finalized_, "energy_grad before finalize");
@@ -342,13 +380,22 @@ int UnetEngine::energy_grad(const float* x, int n_rows, int x_repeat, float t, c
   const int H = cfg_.horizon, D = cfg_.state_dim;
   int unit = x_repeat;
   while (unit % 16) unit += x_repeat;
-  int per = ((n_rows + split_ - 1) / split_ + unit - 1) / unit * unit;
+  int rows[4];
+  const int np = plan_parts(n_rows, unit, rows);
+  {                                    // the plan must fit the workspace (host arithmetic only); else one call
+    dry_ = true; arena_off_ = 0;
+    int drc = 0;
+    for (int p = 0; p < np && !drc; ++p) drc = run(nullptr, rows[p], x_repeat, 0.f, nullptr, nullptr, nullptr, s);
+    const size_t need = arena_off_;
+    dry_ = false; arena_off_ = 0;
+    if (drc || need + 256 > arena_bytes_) return run(x, n_rows, x_repeat, t, row2scene, eps_out, f_out, s);
+  }
   TRY_RC(time_cond(time_w_, t, (const CondBlock*)cond_blocks_dev_, 16, s));
   RAMP_CUDA_OK(cudaEventRecord(fork_ev_, s));
   skip_time_cond_ = true;
   int rc = 0, used = 0;
-  for (int p = 0, r0 = 0; p < split_ && r0 < n_rows && !rc; ++p, r0 += per, ++used) {
-    const int n = n_rows - r0 < per ? n_rows - r0 : per;
+  for (int p = 0, r0 = 0; p < np && r0 < n_rows && !rc; r0 += rows[p], ++p, ++used) {
+    const int n = rows[p];
     RAMP_CUDA_OK(cudaStreamWaitEvent(side_[p], fork_ev_, 0));
     rc = run(x + (size_t)(r0 / x_repeat) * H * D, n, x_repeat, t, row2scene ? row2scene + r0 : nullptr,
              eps_out ? eps_out + (size_t)r0 * H * D : nullptr, f_out ? f_out + (size_t)r0 * H * D : nullptr, side_[p]);

@@ -123,6 +123,11 @@ class UnetEngine {
   // from and joined back into the caller's stream with events.  Each launch of a dependent chain owns every SM with one
   // persistent CTA, so its last wave and its prologue leave SMs idle; the other part's launches fill them.
   int split_ = 2, split_min_rows_ = 2048; bool skip_time_cond_ = false;      // measured +1.4 % on the headline (profiles/r2_*)
+  // RAMP_UNET_SPLIT_ALIGN = 1: parts are whole WAVES of the deepest level's tiles (SMs x 128 / (H / 8) rows each, rounded down
+  // to whole trajectories) plus one small remainder part, instead of equal parts: 7168 rows are 448 tiles at L = 8 = 3 waves
+  // of 148 + 4 tiles, and those 4 cost every launch of the level a fourth wave (see plan_parts)
+  int split_align_ = 0, sms_ = 148;
+  int plan_parts(int n_rows, int unit, int* rows) const;
   cudaStream_t side_[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t fork_ev_ = nullptr, join_ev_[4] = {nullptr, nullptr, nullptr, nullptr};
   int ensure_side_streams();
