@@ -37,7 +37,7 @@ print("HASH", hashlib.sha256(eps.cpu().numpy().tobytes()).hexdigest(), float(eps
 def _run(env_extra):
     env = dict(os.environ)
     for k in list(env):
-        if k.startswith("RAMP_GEMM_") or k == "RAMP_UNET_SPLIT":
+        if k.startswith("RAMP_GEMM_") or k.startswith("RAMP_UNET_SPLIT"):
             del env[k]
     env.update(env_extra)
     out = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True, timeout=600)
@@ -56,6 +56,8 @@ def test_knobs_do_not_change_the_rows(cuda):
         {"RAMP_GEMM_PAIR": "0"},
         {"RAMP_GEMM_E1_CW": "32"},
         {"RAMP_UNET_SPLIT": "1"},
+        {"RAMP_UNET_SPLIT": "2", "RAMP_UNET_SPLIT_MIN": "256"},          # two parts of 320 rows on side streams
+        {"RAMP_UNET_SPLIT": "3", "RAMP_UNET_SPLIT_MIN": "256"},
     ]
     for s in settings:
         h, _ = _run(s)
