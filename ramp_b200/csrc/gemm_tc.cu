@@ -938,6 +938,9 @@ static int g_tma_store = 1;
 // extra tile costs 32 KB of the operand ring).  RAMP_GEMM_MIN_STAGES: operand stages that must remain.
 static int g_stg_want[5] = {1, 1, 2, 2, 2};
 static int g_min_stages = 2;
+// RAMP_GEMM_BN_MODEL: 1 = pick the tile width by the wave model in pick_bn, 0 = round 1's rule (largest tile that divides
+// Nout, smaller only while the grid would leave SMs idle)
+static int g_bn_model = 1;
 // RAMP_GEMM_E1_CW: epilogue configuration of the GEGLU forward (16 = 16 warps x 16-column chunks, 32 = 8 warps x 32)
 static int g_e1_cw = 16;
 // a launch gets its mode's extra staging tiles only while its k-loop is short (iterations per tile <= limit): long k-loops
@@ -969,6 +972,7 @@ int gemm_init() {
     if (sscanf(v, "%d,%d,%d,%d,%d", &w[0], &w[1], &w[2], &w[3], &w[4]) == 5)
       for (int i = 0; i < 5; ++i) g_stg_want[i] = w[i] < 1 ? 1 : (w[i] > 3 ? 3 : w[i]);
   }
+  if (const char* v = getenv("RAMP_GEMM_BN_MODEL")) g_bn_model = atoi(v) != 0;
   if (const char* v = getenv("RAMP_GEMM_E1_CW")) g_e1_cw = atoi(v) == 32 ? 32 : 16;
   if (const char* v = getenv("RAMP_GEMM_STG_ITERS")) {
     int w[5];
@@ -1027,14 +1031,29 @@ static int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t*
 
 
 static int pick_bn(int Nout, int m_tiles) {
-  // Largest tile that divides Nout; drop to smaller tiles only while the grid would leave SMs idle.
   const int cands[5] = {256, 128, 64, 32, 16};
-  int best = 0;
+  if (!g_bn_model) {
+    int best = 0;
+    for (int i = 0; i < 5; ++i) {
+      int bn = cands[i];
+      if (Nout % bn) continue;
+      if (!best) best = bn;
+      if ((long)m_tiles * (Nout / bn) >= g_num_sms || bn <= 64) return bn;
+    }
+    return best;
+  }
+  // A persistent CTA works through ceil(tiles / SMs) tiles, each costing its width (MMA and epilogue time are both
+  // proportional to BN) plus a fixed part (pipeline fill, first-tile latency: about 32 columns' worth).  The old rule shrank
+  // the tile until the grid covered the SMs and so turned 128 tiles of BN = 128 (one wave) into 256 tiles of BN = 64 (two
+  // waves, the A tile fetched twice as often): the small launches of a replan tick (1024 rows: 64 row tiles at L = 8) are
+  // mostly of that kind.  Wider tiles win ties.
+  int best = 0; long best_cost = 0;
   for (int i = 0; i < 5; ++i) {
-    int bn = cands[i];
+    const int bn = cands[i];
     if (Nout % bn) continue;
-    if (!best) best = bn;
-    if ((long)m_tiles * (Nout / bn) >= g_num_sms || bn <= 64) return bn;
+    const long tiles = (long)m_tiles * (Nout / bn);
+    const long cost = ((tiles + g_num_sms - 1) / g_num_sms) * (bn + 32);
+    if (!best || cost < best_cost) { best = bn; best_cost = cost; }
   }
   return best;
 }
