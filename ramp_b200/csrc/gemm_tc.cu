@@ -78,6 +78,8 @@ struct GemmParams {
   bf16* out2_hi; bf16* out2_lo; int ldS2;
   int tma_store;                              // 1: dense output rows -> the epilogue stores through TMA (see EpiMaps)
   int stg_bufs;                               // staging tiles per epilogue warp (1..3; > 1 only with tma_store)
+  int bk;                                     // k-block width in elements: 64 (128-byte rows, SWIZZLE_128B) or, for K <= 32,
+                                              // 32 (64-byte rows, SWIZZLE_64B: half the shared-memory fill per stage, twice the stages)
 };
 // Tensor maps of the outputs (fp32 copy, hi / lo planes, second hi / lo planes) for the TMA store path.  Used when the
 // tile's 128 accumulator rows are 128 consecutive output rows (o_L == L_out, o_stride == 1, o_off == 0: every launch of
@@ -205,13 +207,14 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 // K-major, SWIZZLE_128B operand tile: 8-row atoms of 1024 B (SBO), LBO unused, descriptor version 1.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+// sw64: rows of 64 B (k-block of 32 elements), 8-row atoms of 512 B, layout type SWIZZLE_64B (4)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr, bool sw64 = false) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
   d |= (uint64_t)1 << 16;
-  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)((sw64 ? 512 : 1024) >> 4) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)(sw64 ? 4 : 2) << 61;
   return d;
 }
 
@@ -705,8 +708,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cta_rank = CG == 2 ? (int)cluster_ctarank() : 0;
-  const int b_tile_bytes = (p.BN / CG) * BK * 2;        // this CTA's share of the weight tile
-  const int stage_bytes = p.nplanes * (A_TILE_BYTES + b_tile_bytes);
+  const int a_tile_bytes = BM * p.bk * 2;
+  const int b_tile_bytes = (p.BN / CG) * p.bk * 2;      // this CTA's share of the weight tile
+  const int stage_bytes = p.nplanes * (a_tile_bytes + b_tile_bytes);
   const uint32_t stg_base = smem_base + p.stages * stage_bytes;            // the epilogue warps' staging tiles
   const uint32_t bar_base = stg_base + p.stg_bufs * STG_BYTES;
   const uint32_t full0 = bar_base, empty0 = bar_base + 8 * p.stages;
@@ -770,21 +774,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
             const int brow = p.tap_wrow[t] + tile_n * p.BN + cta_rank * (p.BN / CG);
             if constexpr (CG == 2) {
               // the leader's barrier collects the bytes of both CTAs; only the leader arrives on it
-              if (cta_rank == 0) mbar_expect_tx(fb, (uint32_t)(2 * p.nplanes * (A_TILE_BYTES + b_tile_bytes)));
-              tma_load_4d_pair(st, &mapAhi, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3);
-              uint32_t off = A_TILE_BYTES;
-              if (p.nplanes == 2) { tma_load_4d_pair(st + off, &mapAlo, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3); off += A_TILE_BYTES; }
-              tma_load_2d_pair(st + off, &mapBhi, fb, kb * BK, brow);
+              if (cta_rank == 0) mbar_expect_tx(fb, (uint32_t)(2 * p.nplanes * (a_tile_bytes + b_tile_bytes)));
+              tma_load_4d_pair(st, &mapAhi, fb, kb * p.bk, p.tap_par[t], p.tap_joff[t], c3);
+              uint32_t off = a_tile_bytes;
+              if (p.nplanes == 2) { tma_load_4d_pair(st + off, &mapAlo, fb, kb * p.bk, p.tap_par[t], p.tap_joff[t], c3); off += a_tile_bytes; }
+              tma_load_2d_pair(st + off, &mapBhi, fb, kb * p.bk, brow);
               off += b_tile_bytes;
-              if (p.nplanes == 2) tma_load_2d_pair(st + off, &mapBlo, fb, kb * BK, brow);
+              if (p.nplanes == 2) tma_load_2d_pair(st + off, &mapBlo, fb, kb * p.bk, brow);
             } else {
-              mbar_expect_tx(fb, (uint32_t)(p.nplanes * (p.nb * p.L_out * BK * 2 + b_tile_bytes)));
-              tma_load_4d(st, &mapAhi, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3);
-              uint32_t off = A_TILE_BYTES;
-              if (p.nplanes == 2) { tma_load_4d(st + off, &mapAlo, fb, kb * BK, p.tap_par[t], p.tap_joff[t], c3); off += A_TILE_BYTES; }
-              tma_load_2d(st + off, &mapBhi, fb, kb * BK, brow);
+              mbar_expect_tx(fb, (uint32_t)(p.nplanes * (p.nb * p.L_out * p.bk * 2 + b_tile_bytes)));
+              tma_load_4d(st, &mapAhi, fb, kb * p.bk, p.tap_par[t], p.tap_joff[t], c3);
+              uint32_t off = a_tile_bytes;
+              if (p.nplanes == 2) { tma_load_4d(st + off, &mapAlo, fb, kb * p.bk, p.tap_par[t], p.tap_joff[t], c3); off += a_tile_bytes; }
+              tma_load_2d(st + off, &mapBhi, fb, kb * p.bk, brow);
               off += b_tile_bytes;
-              if (p.nplanes == 2) tma_load_2d(st + off, &mapBlo, fb, kb * BK, brow);
+              if (p.nplanes == 2) tma_load_2d(st + off, &mapBlo, fb, kb * p.bk, brow);
             }
           }
         }
@@ -802,6 +806,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
 #else
       const uint32_t idesc_lh = idesc0 | (1u << 7) | (1u << 10), idesc_hl = idesc_lh, idesc_hh = idesc_lh;   // all bf16
 #endif
+      const int ksteps = p.bk / 16;
+      const bool sw64 = p.bk == 32;
       int it = 0, lt = 0;
       for (int tile = unit0; tile < total_tiles; tile += unit_step, ++lt) {
         const int buf = lt & 1;
@@ -815,27 +821,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapAhi, const __grid_constant
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t st = smem_base + s * stage_bytes;
           const uint32_t a_hi = st;
-          const uint32_t a_lo = st + A_TILE_BYTES;
-          const uint32_t b_hi = st + p.nplanes * A_TILE_BYTES;
+          const uint32_t a_lo = st + a_tile_bytes;
+          const uint32_t b_hi = st + p.nplanes * a_tile_bytes;
           const uint32_t b_lo = b_hi + b_tile_bytes;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
+            if (k >= ksteps) break;
             const uint32_t ko = k * 32;   // 16 bf16 = 32 B inside the 128 B swizzle row
             const uint32_t first = (i == 0 && k == 0) ? 0u : 1u;
             if constexpr (CG == 2) {
               if (p.nplanes == 2) {
-                umma_f16_pair(dacc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc_lh, first);
-                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc_hl, 1u);
-                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, 1u);
+                umma_f16_pair(dacc, umma_desc_sw128(a_lo + ko, sw64), umma_desc_sw128(b_hi + ko, sw64), idesc_lh, first);
+                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko, sw64), umma_desc_sw128(b_lo + ko, sw64), idesc_hl, 1u);
+                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko, sw64), umma_desc_sw128(b_hi + ko, sw64), idesc_hh, 1u);
               } else {
-                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, first);
+                umma_f16_pair(dacc, umma_desc_sw128(a_hi + ko, sw64), umma_desc_sw128(b_hi + ko, sw64), idesc_hh, first);
               }
             } else if (p.nplanes == 2) {
-              umma_bf16(dacc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc_lh, first);
-              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc_hl, 1u);
-              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, 1u);
+              umma_bf16(dacc, umma_desc_sw128(a_lo + ko, sw64), umma_desc_sw128(b_hi + ko, sw64), idesc_lh, first);
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko, sw64), umma_desc_sw128(b_lo + ko, sw64), idesc_hl, 1u);
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko, sw64), umma_desc_sw128(b_hi + ko, sw64), idesc_hh, 1u);
             } else {
-              umma_bf16(dacc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc_hh, first);
+              umma_bf16(dacc, umma_desc_sw128(a_hi + ko, sw64), umma_desc_sw128(b_hi + ko, sw64), idesc_hh, first);
             }
           }
           if constexpr (CG == 2) umma_commit_pair(empty0 + 8 * s); else umma_commit(empty0 + 8 * s);   // frees the smem stage (of both CTAs) when these MMAs retire
@@ -941,6 +948,11 @@ static int g_min_stages = 2;
 // RAMP_GEMM_BN_MODEL: 1 = pick the tile width by the wave model in pick_bn, 0 = round 1's rule (largest tile that divides
 // Nout, smaller only while the grid would leave SMs idle)
 static int g_bn_model = 1;
+// RAMP_GEMM_BK32: 1 = contractions with K <= 32 (the 16- / 32-channel convolutions, proj_in at C = 32) use 32-wide k-blocks:
+// 64-byte operand rows (SWIZZLE_64B), half the shared-memory fill per stage and up to ten stages in flight.  Those launches
+// are bound by the TMA fill of five taps per tile, not by the MMAs: 32-channel k5 convolution at L = 32 76.6 -> 57.0 us,
+// 16 -> 32 channels at L = 64 136 -> 98 us (profiles/r2_bk32_ab.txt)
+static int g_bk32 = 1;
 // RAMP_GEMM_E1_CW: epilogue configuration of the GEGLU forward (16 = 16 warps x 16-column chunks, 32 = 8 warps x 32)
 static int g_e1_cw = 16;
 // a launch gets its mode's extra staging tiles only while its k-loop is short (iterations per tile <= limit): long k-loops
@@ -973,6 +985,7 @@ int gemm_init() {
       for (int i = 0; i < 5; ++i) g_stg_want[i] = w[i] < 1 ? 1 : (w[i] > 3 ? 3 : w[i]);
   }
   if (const char* v = getenv("RAMP_GEMM_BN_MODEL")) g_bn_model = atoi(v) != 0;
+  if (const char* v = getenv("RAMP_GEMM_BK32")) g_bk32 = atoi(v) != 0;
   if (const char* v = getenv("RAMP_GEMM_E1_CW")) g_e1_cw = atoi(v) == 32 ? 32 : 16;
   if (const char* v = getenv("RAMP_GEMM_STG_ITERS")) {
     int w[5];
@@ -1071,7 +1084,8 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   GemmParams p;
   std::memset(&p, 0, sizeof(p));
   p.n_samples = d.n_samples; p.L_out = d.L_out; p.nb = BM / d.L_out;
-  p.ntaps = d.ntaps; p.kblocks = (d.K + BK - 1) / BK;
+  p.bk = (g_bk32 && d.K <= 32) ? 32 : BK;
+  p.ntaps = d.ntaps; p.kblocks = (d.K + p.bk - 1) / p.bk;
   p.m_tiles = (d.n_samples + p.nb - 1) / p.nb;
   p.BN = pick_bn(d.Nout, p.m_tiles);
   p.epi = d.epi;
@@ -1094,7 +1108,7 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   p.nplanes = d.precision == 3 ? 2 : 1;
   // CTA pairs: worth it where the weight tile is large (BN >= 128) and there are enough tile pairs to fill the pairs of SMs
   const int cg = (g_pair && p.BN >= 128 && (long)((p.m_tiles + 1) / 2) * p.n_tiles >= g_num_sms / 2) ? 2 : 1;
-  const int stage_bytes = p.nplanes * (A_TILE_BYTES + (p.BN / cg) * BK * 2);
+  const int stage_bytes = p.nplanes * (BM * p.bk * 2 + (p.BN / cg) * p.bk * 2);
   // TMA store path (see EpiMaps): only where a tile's accumulator rows are consecutive output rows
   p.tma_store = (g_tma_store && d.o_L == d.L_out && d.o_stride == 1 && d.o_off == 0 && BM % d.L_out == 0) ? 1 : 0;
   // staging tiles per epilogue warp: as many as the mode wants (g_stg_want) while at least g_min_stages operand stages fit
@@ -1103,7 +1117,8 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
   p.stg_bufs = nbuf;
   const int fixed = 1024 + nbuf * STG_BYTES + 256;
   int stages = (g_max_smem - fixed) / stage_bytes;
-  if (stages > 6) stages = 6;
+  const int max_stages = p.bk == 32 ? 10 : 6;
+  if (stages > max_stages) stages = max_stages;
   const long total_iters = (long)p.ntaps * p.kblocks * ((long)((p.m_tiles + cg - 1) / cg) * p.n_tiles + g_num_sms / cg - 1) / (g_num_sms / cg);
   if (stages > total_iters) stages = (int)total_iters;
   RAMP_CHECK(stages >= 1, "gemm: tile does not fit shared memory");
@@ -1121,19 +1136,20 @@ int gemm_launch(const GemmDesc& d, cudaStream_t stream) {
              "gemm: output / residual leading dimensions must keep 16-byte alignment");
 
   CUtensorMap mAhi, mAlo, mBhi, mBlo;
+  const CUtensorMapSwizzle op_sw = p.bk == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
   {
     uint64_t dims[4] = {(uint64_t)d.K, (uint64_t)d.a_pstride, (uint64_t)(d.L_in / d.a_pstride), (uint64_t)d.n_samples};
     uint64_t str[3] = {(uint64_t)d.ldA * 2, (uint64_t)d.a_pstride * d.ldA * 2, (uint64_t)d.L_in * d.ldA * 2};
-    uint32_t box[4] = {(uint32_t)BK, 1u, (uint32_t)d.L_out, (uint32_t)p.nb};
-    if (make_map(&mAhi, d.a_hi, 4, dims, str, box)) return -3;
-    if (p.nplanes == 2) { if (make_map(&mAlo, d.a_lo, 4, dims, str, box)) return -3; } else mAlo = mAhi;
+    uint32_t box[4] = {(uint32_t)p.bk, 1u, (uint32_t)d.L_out, (uint32_t)p.nb};
+    if (make_map(&mAhi, d.a_hi, 4, dims, str, box, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, op_sw)) return -3;
+    if (p.nplanes == 2) { if (make_map(&mAlo, d.a_lo, 4, dims, str, box, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, op_sw)) return -3; } else mAlo = mAhi;
   }
   {
     uint64_t dims[2] = {(uint64_t)d.K, (uint64_t)d.n_wtaps * d.Nout};
     uint64_t str[1] = {(uint64_t)d.Kw * 2};
-    uint32_t box[2] = {(uint32_t)BK, (uint32_t)(p.BN / cg)};      // a CTA of a pair stages half of the tile's weight rows
-    if (make_map(&mBhi, d.w_hi, 2, dims, str, box)) return -3;
-    if (p.nplanes == 2) { if (make_map(&mBlo, d.w_lo, 2, dims, str, box)) return -3; } else mBlo = mBhi;
+    uint32_t box[2] = {(uint32_t)p.bk, (uint32_t)(p.BN / cg)};      // a CTA of a pair stages half of the tile's weight rows
+    if (make_map(&mBhi, d.w_hi, 2, dims, str, box, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, op_sw)) return -3;
+    if (p.nplanes == 2) { if (make_map(&mBlo, d.w_lo, 2, dims, str, box, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, op_sw)) return -3; } else mBlo = mBhi;
   }
   // output tensor maps of the TMA store path: [rows = n_samples * L_out][ld] arrays, boxes of 32 rows x cw columns
   EpiMaps om;

@@ -56,6 +56,7 @@ def test_knobs_do_not_change_the_rows(cuda):
         {"RAMP_GEMM_PAIR": "0"},
         {"RAMP_GEMM_E1_CW": "32"},
         {"RAMP_GEMM_BN_MODEL": "0"},
+        {"RAMP_GEMM_BK32": "0"},
         {"RAMP_UNET_SPLIT": "1"},
         {"RAMP_UNET_SPLIT": "2", "RAMP_UNET_SPLIT_MIN": "256"},          # two parts of 320 rows on side streams
         {"RAMP_UNET_SPLIT": "3", "RAMP_UNET_SPLIT_MIN": "256"},
