@@ -68,3 +68,17 @@ def test_ops_fail_loudly_without_cuda():
     net = TemporalUnetInference(n_support_points=64, state_dim=4)
     with pytest.raises(RampError):
         net.prepare()
+
+
+def test_every_environment_knob_is_documented():
+    """INTEGRATION.md §4 lists every environment variable the library reads (grep of getenv("RAMP_...") in csrc/)."""
+    import glob
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    names = set()
+    for f in glob.glob(os.path.join(root, "ramp_b200", "csrc", "*.cu*")):
+        names |= set(re.findall(r'getenv\("(RAMP_[A-Z0-9_]+)"\)', open(f).read()))
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    assert names, "no knobs found: the grep is broken"
+    missing = sorted(n for n in names if n not in doc)
+    assert not missing, "undocumented knobs: %s" % missing
